@@ -1,0 +1,365 @@
+/*
+ * rve_b200.h — C-ABI of the B200-native render-prep path (drop-in boundary).
+ *
+ * One header, plain C: POD layouts that are byte-identical to the reference's
+ * push-constant / storage-buffer structs, and the entry points a reference
+ * maintainer would bind instead of "bind + SetComputeBytes + DispatchCompute"
+ * on the six compute pipelines of RenderEngine::Draw.
+ *
+ * Every declaration cites the reference interface it replaces
+ * (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - all functions return 0 on success, a negative rve_status on failure,
+ *     never throw across the boundary; rve_last_error_string() describes the
+ *     last failure of the calling thread (reference: Debug::Fatal aborts,
+ *     include/RavEngine/Debug.hpp — we return codes instead).
+ *   - every rve_* compute call is an asynchronous enqueue on the context's
+ *     stream (the reference's in-order queue, src/RenderEngine.cpp:304-307),
+ *     exactly like ICommandBuffer::DispatchCompute
+ *     (deps/RGL/include/RGL/CommandBuffer.hpp:99-184). Push-constant structs
+ *     are copied at enqueue time.
+ *   - mat4 is column-major 16 x f32 (glm / GLSL): m[col*4 + row].
+ *   - buffer sizes/offsets are 64-bit (the reference uses u32,
+ *     deps/RGL/include/RGL/Buffer.hpp:22,75); instance ids stay u32.
+ */
+#ifndef RVE_B200_H
+#define RVE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define RVE_API __attribute__((visibility("default")))
+#else
+#define RVE_API
+#endif
+
+/* ------------------------------------------------------------------ */
+/* status codes                                                        */
+/* ------------------------------------------------------------------ */
+typedef enum rve_status {
+    RVE_OK = 0,
+    RVE_ERR_INVALID_ARGUMENT = -1,
+    RVE_ERR_OUT_OF_MEMORY = -2,
+    RVE_ERR_CUDA = -3,
+    RVE_ERR_BAD_HANDLE = -4,
+    RVE_ERR_NO_DEVICE = -5,
+    RVE_ERR_UNSUPPORTED = -6
+} rve_status;
+
+/* ------------------------------------------------------------------ */
+/* POD layouts (bit-identical to the reference)                        */
+/* ------------------------------------------------------------------ */
+#pragma pack(push, 1)
+
+/* RGL::IndirectIndexedCommand — deps/RGL/include/RGL/CommandBuffer.hpp:55-61
+ * (consumed by vkCmdDrawIndexedIndirect with stride 20,
+ *  deps/RGL/src/VkCommandBuffer.cpp:790-799). */
+typedef struct RveIndirectIndexedCommand {
+    uint32_t indexCount;
+    uint32_t instanceCount;
+    uint32_t indexStart;
+    uint32_t baseVertex;
+    uint32_t baseInstance;
+} RveIndirectIndexedCommand;
+
+/* CullingUBO — include/RavEngine/RenderEngine.hpp:224-230,
+ * shaders/defaultcull.csh:19-25 (push constants, scalar layout, 88 B). */
+typedef struct RveCullingUBO {
+    float viewProj[16];
+    float camPos[3];
+    uint32_t numCubos;
+    uint32_t cameraRenderLayers;
+    uint32_t singleInstanceModeAndShadowMode; /* bit0 single-instance (skinned), bit1 shadow pass */
+} RveCullingUBO;
+
+/* CullingUBOinstance ("CUBO") — include/RavEngine/RenderEngine.hpp:212-222,
+ * shaders/defaultcull.csh:7-17 (binding 0, scalar array, 36 B each). */
+typedef struct RveCullingUBOinstance {
+    uint32_t indirectBufferOffset;
+    uint32_t numObjects;
+    uint32_t cullingBufferOffset;
+    float radius;
+    uint32_t numLODs;
+    uint32_t idOutputBufferBindlessHandle;
+    uint32_t entityIDInputBufferBindlessHandle;
+    uint32_t indirectOutputBufferBindlessHandle;
+    uint32_t lodDistanceBufferBindlessHandle;
+} RveCullingUBOinstance;
+
+/* SkinningUBO — include/RavEngine/RenderEngine.hpp:178-185,
+ * shaders/skinning_cs.csh:83-90 (24 B). */
+typedef struct RveSkinningUBO {
+    uint32_t numObjects;
+    uint32_t numVertices;
+    uint32_t numBones;
+    uint32_t boneReadOffset;
+    uint32_t vertexWriteOffset;
+    uint32_t vertexReadOffset;
+} RveSkinningUBO;
+
+/* SkinningPrepareUBO — include/RavEngine/RenderEngine.hpp:232-240,
+ * shaders/skinned_mesh_drawcall.csh:1-9 (28 B). */
+typedef struct RveSkinningPrepareUBO {
+    uint32_t indexBufferOffset;
+    uint32_t vertexBufferOffset;
+    uint32_t nIndicesInThisMesh;
+    uint32_t nVerticesInThisMesh;
+    uint32_t nTotalObjects;
+    uint32_t drawCallBufferOffset;
+    uint32_t baseInstanceOffset;
+} RveSkinningPrepareUBO;
+
+/* GridBuildUBO — include/RavEngine/RenderEngine.hpp:103-112 (pack(1), 92 B),
+ * shaders/cluster_build_grid.csh:8-14. */
+typedef struct RveGridBuildUBO {
+    float invProj[16];
+    uint32_t gridSize[3];
+    float zNear;
+    uint32_t screenDim[2];
+    float zFar;
+} RveGridBuildUBO;
+
+/* GridAssignUBO — include/RavEngine/RenderEngine.hpp:114-117 (72 B),
+ * shaders/cluster_assign_lights.csh:22-26. */
+typedef struct RveGridAssignUBO {
+    float viewMat[16];
+    uint32_t pointLightCount;
+    uint32_t spotLightCount;
+} RveGridAssignUBO;
+
+/* PyramidCopyUBO — include/RavEngine/RenderEngine.hpp:89-91,
+ * shaders/depthpyramidcopy.fsh:1-3. */
+typedef struct RvePyramidCopyUBO {
+    uint32_t size;
+} RvePyramidCopyUBO;
+
+#define RVE_CLUSTER_MAX_POINTS 16 /* shaders/cluster_defs.h:1 */
+#define RVE_CLUSTER_MAX_SPOTS 16  /* shaders/cluster_defs.h:2 */
+#define RVE_LIGHT_MIN_INFLUENCE 0.01f /* shaders/cluster_defs.h:3 */
+
+/* Cluster — shaders/cluster_shared.glsl:3-11 (scalar layout, 160 B). */
+typedef struct RveCluster {
+    float minPoint[3];
+    float maxPoint[3];
+    uint32_t pointLightCount;
+    uint32_t spotLightCount;
+    uint32_t pointLightIndices[RVE_CLUSTER_MAX_POINTS];
+    uint32_t spotLightIndices[RVE_CLUSTER_MAX_SPOTS];
+} RveCluster;
+
+/* PointLight — shaders/cluster_shared.glsl:14-25, upload struct
+ * include/RavEngine/World.hpp:393-405 (scalar layout, 512 B). */
+typedef struct RvePointLight {
+    float viewMats[6][16];
+    float projMat[16];
+    float position[3];
+    float color[3];
+    float intensity;
+    int32_t castsShadows;
+    uint32_t shadowRenderLayers;
+    uint32_t illuminationLayers;
+    uint32_t shadowmapBindlessIndices[6];
+} RvePointLight;
+
+/* SpotLight — shaders/cluster_shared.glsl:27-38, upload struct
+ * include/RavEngine/World.hpp:406-416 (scalar layout, 168 B). */
+typedef struct RveSpotLight {
+    float lightViewProj[16];
+    float worldTransform[16];
+    float color[3];
+    float intensity;
+    float coneAngle;
+    float penumbraAngle;
+    int32_t castsShadows;
+    uint32_t shadowmapBindlessIndex;
+    uint32_t shadowRenderLayers;
+    uint32_t illuminationLayers;
+} RveSpotLight;
+
+/* VertexJointBinding — shaders/skinning_cs.csh:66-75,
+ * include/RavEngine/Skeleton.hpp:50-60 (std430, 32 B). */
+typedef struct RveJointInfluence {
+    uint32_t joint_index;
+    float influence;
+} RveJointInfluence;
+typedef struct RveVertexJointBinding {
+    RveJointInfluence weights[4];
+} RveVertexJointBinding;
+
+#pragma pack(pop)
+
+/* per-object attribute bits — include/RavEngine/Layer.hpp:8-13 */
+#define RVE_ATTR_FRUSTUM_CULL 0x1u
+#define RVE_ATTR_OCCLUSION_CULL 0x2u
+#define RVE_ATTR_CASTS_SHADOWS 0x4u
+/* CullingUBO.singleInstanceModeAndShadowMode bits — defaultcull.csh:186-187 */
+#define RVE_CULL_SINGLE_INSTANCE 0x1u
+#define RVE_CULL_SHADOW_MODE 0x2u
+
+#ifdef __cplusplus
+static_assert(sizeof(RveIndirectIndexedCommand) == 20, "layout");
+static_assert(sizeof(RveCullingUBO) == 88, "layout");
+static_assert(sizeof(RveCullingUBOinstance) == 36, "layout");
+static_assert(sizeof(RveSkinningUBO) == 24, "layout");
+static_assert(sizeof(RveSkinningPrepareUBO) == 28, "layout");
+static_assert(sizeof(RveGridBuildUBO) == 92, "layout");
+static_assert(sizeof(RveGridAssignUBO) == 72, "layout");
+static_assert(sizeof(RveCluster) == 160, "layout");
+static_assert(sizeof(RvePointLight) == 512, "layout");
+static_assert(sizeof(RveSpotLight) == 168, "layout");
+static_assert(sizeof(RveVertexJointBinding) == 32, "layout");
+#endif
+
+/* ------------------------------------------------------------------ */
+/* context                                                             */
+/* ------------------------------------------------------------------ */
+typedef struct rve_ctx rve_ctx;
+
+/* One context per (thread, device) = the reference's single device + single
+ * in-order queue (src/RenderEngine.cpp:304-307). `cuda_stream` may be NULL
+ * (the context creates its own non-blocking stream) or an existing
+ * cudaStream_t to enqueue on. */
+RVE_API int rve_ctx_create(int device_ordinal, void* cuda_stream, rve_ctx** out_ctx);
+RVE_API int rve_ctx_destroy(rve_ctx* ctx);
+/* ICommandBuffer::BlockUntilCompleted — src/RenderEngine_Draw.cpp:471,2680 */
+RVE_API int rve_ctx_synchronize(rve_ctx* ctx);
+RVE_API void* rve_ctx_stream(rve_ctx* ctx);
+RVE_API const char* rve_last_error_string(void);
+RVE_API const char* rve_version(void);
+/* number of SMs of the context's device (grid sizing information) */
+RVE_API int rve_ctx_sm_count(rve_ctx* ctx);
+/* how many kernels this context has launched so far (bench.py "gpu_launches") */
+RVE_API uint64_t rve_ctx_launch_count(rve_ctx* ctx);
+
+/* ------------------------------------------------------------------ */
+/* buffers — RGL::IBuffer (deps/RGL/include/RGL/Buffer.hpp:50-81)      */
+/* ------------------------------------------------------------------ */
+/* A buffer handle IS its bindless index: the value a CUBO carries in its
+ * *BindlessHandle fields (IBuffer::GetReadonlyBindlessGPUHandle /
+ * GetReadwriteBindlessGPUHandle, deps/RGL/src/VkBuffer.cpp:67-88,150-157).
+ * The library keeps a device-side pointer table so the cull kernel resolves
+ * cubo.*BindlessHandle like the shader does (defaultcull.csh:56-59). */
+typedef uint32_t rve_buffer;
+#define RVE_BUFFER_INVALID 0xFFFFFFFFu
+
+/* IDevice::CreateBuffer (Private access). Zero-initialised. */
+RVE_API int rve_buffer_create(rve_ctx* ctx, size_t bytes, rve_buffer* out);
+/* Register device memory the caller owns (e.g. a torch tensor) as a buffer. */
+RVE_API int rve_buffer_wrap(rve_ctx* ctx, void* device_ptr, size_t bytes, rve_buffer* out);
+/* Deferred to stream order (reference: gcBuffers queue, src/RenderEngine.cpp:2428-2442). */
+RVE_API int rve_buffer_destroy(rve_ctx* ctx, rve_buffer buf);
+/* IBuffer::SetBufferData / UpdateBufferData + staging CopyBufferToBuffer. */
+RVE_API int rve_buffer_upload(rve_ctx* ctx, rve_buffer buf, size_t dst_offset, const void* host_src, size_t bytes);
+RVE_API int rve_buffer_download(rve_ctx* ctx, rve_buffer buf, size_t src_offset, void* host_dst, size_t bytes);
+/* ICommandBuffer::CopyBufferToBuffer — deps/RGL/include/RGL/CommandBuffer.hpp */
+RVE_API int rve_buffer_copy(rve_ctx* ctx, rve_buffer src, size_t src_offset, rve_buffer dst, size_t dst_offset, size_t bytes);
+RVE_API int rve_buffer_fill_zero(rve_ctx* ctx, rve_buffer buf, size_t offset, size_t bytes);
+RVE_API void* rve_buffer_device_ptr(rve_ctx* ctx, rve_buffer buf);
+RVE_API size_t rve_buffer_size(rve_ctx* ctx, rve_buffer buf);
+RVE_API uint32_t rve_buffer_bindless_index(rve_ctx* ctx, rve_buffer buf);
+
+/* ------------------------------------------------------------------ */
+/* a-1 depth pyramid                                                   */
+/* ------------------------------------------------------------------ */
+/* DepthPyramid::DepthPyramid(width) — src/DepthPyramid.cpp:8-28:
+ * dim = 2^floor(log2(min(width,1024))), numLevels = 1+log2(dim), R32F mip
+ * chain. Ours: one linear f32 buffer, level L starts at texel offset
+ * 4*(dim^2 - (dim>>L)^2)/3, row-major (dim>>L)^2 texels. */
+typedef uint32_t rve_pyramid;
+RVE_API int rve_depth_pyramid_create(rve_ctx* ctx, uint32_t width, rve_pyramid* out);
+RVE_API int rve_depth_pyramid_destroy(rve_ctx* ctx, rve_pyramid pyr);
+RVE_API int rve_depth_pyramid_info(rve_ctx* ctx, rve_pyramid pyr, uint32_t* dim, uint32_t* num_levels, rve_buffer* texels);
+/* generatePyramid — src/RenderEngine_Draw.cpp:2475-2514: depthpyramidcopy.fsh
+ * (mip 0, min-reduction sample of the w x h f32 depth buffer) followed by
+ * depthpyramid.csh for mips 1..N-1. Whole chain in one call. */
+RVE_API int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height);
+
+/* ------------------------------------------------------------------ */
+/* a-2 cull + LOD + indirect compaction — shaders/defaultcull.csh      */
+/* ------------------------------------------------------------------ */
+/* Replaces the encode at src/RenderEngine_Draw.cpp:1380-1405 (static) and
+ * :1186-1215 (skinned): bindings Cubo=0, modelMatrix=1, renderLayer=2,
+ * perObject=7, depthPyramid=8 (+sampler 9), bindless sets 3-6
+ * (include/RavEngine/RenderEngine.hpp:95-102), push constants = CullingUBO,
+ * DispatchCompute(num_groups_x,1,1, 64,1,1): num_groups_x*64 invocations, those
+ * past sum(cubo.numObjects) exit (defaultcull.csh:150-164).
+ * Indirect buffers must have been initialised by the caller (instanceCount=0),
+ * as the reference does with CopyBufferToBuffer from its staging table. */
+RVE_API int rve_cull(rve_ctx* ctx, const RveCullingUBO* ubo, rve_buffer cubos,
+                     rve_buffer model_matrices, rve_buffer render_layers,
+                     rve_buffer per_object_flags, rve_pyramid pyramid,
+                     uint32_t num_groups_x);
+
+/* ------------------------------------------------------------------ */
+/* a-3 skinning — shaders/skinning_cs.csh                              */
+/* ------------------------------------------------------------------ */
+/* Replaces src/RenderEngine_Draw.cpp:577-630: out bindings 0-4
+ * (pos,normal,tangent,bitangent vec3; uv vec2), in bindings 10-14, pose 20,
+ * weights 21; DispatchCompute(ceil(nObj/8), ceil(nVerts/32),1, 8,32,1). */
+RVE_API int rve_skin(rve_ctx* ctx, const RveSkinningUBO* ubo,
+                     const rve_buffer out_streams[5], const rve_buffer in_streams[5],
+                     rve_buffer pose, rve_buffer weights);
+
+/* ------------------------------------------------------------------ */
+/* a-4 skinned draw-call prep — shaders/skinned_mesh_drawcall.csh      */
+/* ------------------------------------------------------------------ */
+/* Replaces src/RenderEngine_Draw.cpp:546-574 (binding 0 = indirect buffer). */
+RVE_API int rve_skinned_drawcall_prepare(rve_ctx* ctx, const RveSkinningPrepareUBO* ubo, rve_buffer indirect);
+
+/* ------------------------------------------------------------------ */
+/* a-5 / a-6 clustered lights                                          */
+/* ------------------------------------------------------------------ */
+/* cluster_build_grid.csh, encode src/RenderEngine_Draw.cpp:935-950:
+ * DispatchCompute(gridSize.x, gridSize.y, gridSize.z, 1,1,1). */
+RVE_API int rve_cluster_build(rve_ctx* ctx, const RveGridBuildUBO* ubo, rve_buffer clusters);
+/* cluster_assign_lights.csh, encode src/RenderEngine_Draw.cpp:953-970:
+ * DispatchCompute(numClusters/128,1,1, 128,1,1); bindings 0 clusters,
+ * 1 point lights, 2 spot lights. num_clusters = invocations (groups*128). */
+RVE_API int rve_cluster_assign(rve_ctx* ctx, const RveGridAssignUBO* ubo, rve_buffer clusters,
+                               rve_buffer point_lights, rve_buffer spot_lights, uint32_t num_clusters);
+
+/* ------------------------------------------------------------------ */
+/* 8(e) multi-GPU helpers (instance-range sharding)                    */
+/* ------------------------------------------------------------------ */
+/* After every rank culled its shard into rank-local slices and the per-slot
+ * counts were all-gathered (NCCL, done by the host plumbing), compute on the
+ * device: offsets[r][s] = sum_{q<r} counts[q][s] and total[s] = sum_q counts[q][s].
+ * counts_all: u32[world][num_slots]; offsets_out: u32[world][num_slots];
+ * totals_out: u32[num_slots]. */
+RVE_API int rve_shard_offsets(rve_ctx* ctx, rve_buffer counts_all, uint32_t world, uint32_t num_slots,
+                              rve_buffer offsets_out, rve_buffer totals_out);
+/* Gather this rank's instanceCount fields (stride 20 B) of `num_slots`
+ * commands into a dense u32 array (the all-gather payload). */
+RVE_API int rve_gather_instance_counts(rve_ctx* ctx, rve_buffer indirect, uint32_t first_slot, uint32_t num_slots,
+                                       rve_buffer counts_out, size_t counts_offset_bytes);
+
+/* ------------------------------------------------------------------ */
+/* synthetic scene generation on the device (bench / C5)  */
+/* ------------------------------------------------------------------ */
+/* Fills transforms (T*R*S), layers, flags and identity ids for `count`
+ * instances whose global indices start at `first_index`, procedurally from
+ * (seed, global index) so a 1 B-instance scene needs no host->device copy.
+ * The oracle has the same generator (oracle: orc_gen_instances). */
+typedef struct RveSceneGenParams {
+    uint64_t seed;
+    float extent_xy;     /* positions uniform in [-extent_xy, extent_xy]^2 */
+    float extent_z;      /* ... x [-extent_z, extent_z] (engine Y up: y uses extent_z) */
+    float scale_min, scale_max;
+    float frac_layer_zero;   /* fraction of instances with layer mask 0 */
+    float frac_no_cull_bits; /* fraction with frustum+occlusion bits cleared */
+    uint32_t id_base;        /* entity id written = id_base + local index */
+} RveSceneGenParams;
+RVE_API int rve_gen_instances(rve_ctx* ctx, const RveSceneGenParams* p, uint64_t first_index, uint32_t count,
+                              rve_buffer model_matrices, rve_buffer render_layers, rve_buffer per_object_flags,
+                              rve_buffer entity_ids);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RVE_B200_H */

@@ -1,0 +1,265 @@
+// ctx.cu — context, buffer table ("bindless" handles) and error plumbing of the C-ABI.
+// Replaces the RGL objects the render-prep path touches: IDevice/ICommandQueue
+// (src/RenderEngine.cpp:304-307) and IBuffer (deps/RGL/include/RGL/Buffer.hpp:50-81).
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "internal.h"
+
+namespace rve {
+
+static thread_local std::string g_last_error;
+
+int set_error(int code, const char* fmt, ...) {
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+    if (e == cudaSuccess) return 0;
+    const int code = (e == cudaErrorMemoryAllocation) ? RVE_ERR_OUT_OF_MEMORY : RVE_ERR_CUDA;
+    return set_error(code, "CUDA error %d (%s) in %s", int(e), cudaGetErrorString(e), what);
+}
+
+BufferRec* get_buffer(rve_ctx* ctx, rve_buffer h, const char* role) {
+    if (h >= ctx->buffers.size() || !ctx->buffers[h].live) {
+        set_error(RVE_ERR_BAD_HANDLE, "invalid buffer handle %u for '%s'", h, role);
+        return nullptr;
+    }
+    return &ctx->buffers[h];
+}
+
+PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h) {
+    if (h >= ctx->pyramids.size() || !ctx->pyramids[h].live) {
+        set_error(RVE_ERR_BAD_HANDLE, "invalid pyramid handle %u", h);
+        return nullptr;
+    }
+    return &ctx->pyramids[h];
+}
+
+int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes) {
+    if (bytes <= *cap) return 0;
+    size_t ncap = *cap ? *cap : 4096;
+    while (ncap < bytes) ncap *= 2;
+    void* np = nullptr;
+    RVE_CUDA(cudaMallocAsync(&np, ncap, ctx->stream));
+    if (*ptr) RVE_CUDA(cudaFreeAsync(*ptr, ctx->stream));
+    *ptr = np;
+    *cap = ncap;
+    return 0;
+}
+
+int sync_table(rve_ctx* ctx) {
+    if (!ctx->table_dirty) return 0;
+    const size_t n = ctx->buffers.size();
+    if (n > ctx->d_table_cap) {
+        size_t ncap = ctx->d_table_cap ? ctx->d_table_cap : 256;
+        while (ncap < n) ncap *= 2;
+        void** np = nullptr;
+        RVE_CUDA(cudaMallocAsync(reinterpret_cast<void**>(&np), ncap * sizeof(void*), ctx->stream));
+        if (ctx->d_table) RVE_CUDA(cudaFreeAsync(ctx->d_table, ctx->stream));
+        ctx->d_table = np;
+        ctx->d_table_cap = ncap;
+    }
+    if (n) {
+        std::vector<void*> host(n);
+        for (size_t i = 0; i < n; ++i) host[i] = ctx->buffers[i].live ? ctx->buffers[i].ptr : nullptr;
+        // pageable source: the runtime stages it before returning, so `host` may die afterwards
+        RVE_CUDA(cudaMemcpyAsync(ctx->d_table, host.data(), n * sizeof(void*), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    ctx->table_dirty = false;
+    return 0;
+}
+
+static int alloc_slot(rve_ctx* ctx, void* ptr, size_t bytes, bool owned, rve_buffer* out) {
+    uint32_t slot;
+    if (!ctx->free_slots.empty()) {
+        slot = ctx->free_slots.back();
+        ctx->free_slots.pop_back();
+    } else {
+        slot = uint32_t(ctx->buffers.size());
+        ctx->buffers.emplace_back();
+    }
+    ctx->buffers[slot] = BufferRec{ptr, bytes, owned, true};
+    ctx->table_dirty = true;
+    *out = slot;
+    return 0;
+}
+
+}  // namespace rve
+
+using namespace rve;
+
+extern "C" {
+
+const char* rve_last_error_string(void) { return g_last_error.c_str(); }
+const char* rve_version(void) { return "rve_b200 0.1 (sm_100a)"; }
+
+int rve_ctx_create(int device_ordinal, void* cuda_stream, rve_ctx** out_ctx) {
+    if (!out_ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "out_ctx is null");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return set_error(RVE_ERR_NO_DEVICE, "no CUDA device available (%s); this library has no CPU fallback",
+                         cudaGetErrorString(e));
+    if (device_ordinal < 0 || device_ordinal >= count)
+        return set_error(RVE_ERR_INVALID_ARGUMENT, "device ordinal %d out of range [0,%d)", device_ordinal, count);
+    DeviceGuard g(device_ordinal);
+    auto* ctx = new rve_ctx();
+    ctx->device = device_ordinal;
+    if (cuda_stream) {
+        ctx->stream = static_cast<cudaStream_t>(cuda_stream);
+    } else {
+        int rc = check_cuda(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking), "cudaStreamCreate");
+        if (rc) {
+            delete ctx;
+            return rc;
+        }
+        ctx->owns_stream = true;
+    }
+    cudaDeviceProp prop{};
+    int rc = check_cuda(cudaGetDeviceProperties(&prop, device_ordinal), "cudaGetDeviceProperties");
+    if (rc) {
+        delete ctx;
+        return rc;
+    }
+    ctx->sm_count = prop.multiProcessorCount;
+    *out_ctx = ctx;
+    return 0;
+}
+
+int rve_ctx_destroy(rve_ctx* ctx) {
+    if (!ctx) return 0;
+    DeviceGuard g(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto& b : ctx->buffers)
+        if (b.live && b.owned && b.ptr) cudaFree(b.ptr);
+    if (ctx->d_table) cudaFree(ctx->d_table);
+    if (ctx->d_cubo_start) cudaFree(ctx->d_cubo_start);
+    if (ctx->d_lights) cudaFree(ctx->d_lights);
+    if (ctx->d_slices) cudaFree(ctx->d_slices);
+    if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return 0;
+}
+
+int rve_ctx_synchronize(rve_ctx* ctx) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    RVE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+void* rve_ctx_stream(rve_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
+int rve_ctx_sm_count(rve_ctx* ctx) { return ctx ? ctx->sm_count : 0; }
+uint64_t rve_ctx_launch_count(rve_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int rve_buffer_create(rve_ctx* ctx, size_t bytes, rve_buffer* out) {
+    if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    void* p = nullptr;
+    const size_t alloc = bytes ? bytes : 16;
+    RVE_CUDA(cudaMalloc(&p, alloc));
+    int rc = check_cuda(cudaMemsetAsync(p, 0, alloc, ctx->stream), "cudaMemsetAsync");
+    if (rc) {
+        cudaFree(p);
+        return rc;
+    }
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return alloc_slot(ctx, p, bytes, true, out);
+}
+
+int rve_buffer_wrap(rve_ctx* ctx, void* device_ptr, size_t bytes, rve_buffer* out) {
+    if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    if (!device_ptr && bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "null device pointer with non-zero size");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return alloc_slot(ctx, device_ptr, bytes, false, out);
+}
+
+int rve_buffer_destroy(rve_ctx* ctx, rve_buffer buf) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    BufferRec* b = get_buffer(ctx, buf, "destroy");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    // stream-ordered release: work already enqueued may still read the memory
+    if (b->owned && b->ptr) RVE_CUDA(cudaFreeAsync(b->ptr, ctx->stream));
+    *b = BufferRec{};
+    ctx->free_slots.push_back(buf);
+    ctx->table_dirty = true;
+    return 0;
+}
+
+int rve_buffer_upload(rve_ctx* ctx, rve_buffer buf, size_t dst_offset, const void* host_src, size_t bytes) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    BufferRec* b = get_buffer(ctx, buf, "upload");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    if (dst_offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "upload out of range");
+    if (!bytes) return 0;
+    RVE_CUDA(cudaMemcpyAsync(static_cast<char*>(b->ptr) + dst_offset, host_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
+int rve_buffer_download(rve_ctx* ctx, rve_buffer buf, size_t src_offset, void* host_dst, size_t bytes) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    BufferRec* b = get_buffer(ctx, buf, "download");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    if (src_offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "download out of range");
+    if (!bytes) return 0;
+    RVE_CUDA(cudaMemcpyAsync(host_dst, static_cast<const char*>(b->ptr) + src_offset, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    RVE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+int rve_buffer_copy(rve_ctx* ctx, rve_buffer src, size_t src_offset, rve_buffer dst, size_t dst_offset, size_t bytes) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    BufferRec* s = get_buffer(ctx, src, "copy src");
+    BufferRec* d = get_buffer(ctx, dst, "copy dst");
+    if (!s || !d) return RVE_ERR_BAD_HANDLE;
+    if (src_offset + bytes > s->bytes || dst_offset + bytes > d->bytes)
+        return set_error(RVE_ERR_INVALID_ARGUMENT, "copy out of range");
+    if (!bytes) return 0;
+    RVE_CUDA(cudaMemcpyAsync(static_cast<char*>(d->ptr) + dst_offset, static_cast<const char*>(s->ptr) + src_offset, bytes,
+                             cudaMemcpyDeviceToDevice, ctx->stream));
+    return 0;
+}
+
+int rve_buffer_fill_zero(rve_ctx* ctx, rve_buffer buf, size_t offset, size_t bytes) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    BufferRec* b = get_buffer(ctx, buf, "fill");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    if (offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "fill out of range");
+    if (!bytes) return 0;
+    RVE_CUDA(cudaMemsetAsync(static_cast<char*>(b->ptr) + offset, 0, bytes, ctx->stream));
+    return 0;
+}
+
+void* rve_buffer_device_ptr(rve_ctx* ctx, rve_buffer buf) {
+    if (!ctx) return nullptr;
+    BufferRec* b = get_buffer(ctx, buf, "device_ptr");
+    return b ? b->ptr : nullptr;
+}
+
+size_t rve_buffer_size(rve_ctx* ctx, rve_buffer buf) {
+    if (!ctx) return 0;
+    BufferRec* b = get_buffer(ctx, buf, "size");
+    return b ? b->bytes : 0;
+}
+
+uint32_t rve_buffer_bindless_index(rve_ctx* ctx, rve_buffer buf) {
+    if (!ctx) return RVE_BUFFER_INVALID;
+    BufferRec* b = get_buffer(ctx, buf, "bindless_index");
+    return b ? buf : RVE_BUFFER_INVALID;
+}
+
+}  // extern "C"

@@ -1,0 +1,111 @@
+// internal.h — shared by the translation units of librve_b200.so (not part of the ABI)
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/rve_b200.h"
+
+namespace rve {
+
+struct BufferRec {
+    void* ptr = nullptr;
+    size_t bytes = 0;
+    bool owned = false;
+    bool live = false;
+};
+
+struct PyramidRec {
+    uint32_t dim = 0, levels = 0;
+    rve_buffer texels = RVE_BUFFER_INVALID;
+    rve_buffer counter = RVE_BUFFER_INVALID;  // u32 "blocks done" ticket for the fused build
+    bool live = false;
+};
+
+}  // namespace rve
+
+struct rve_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool owns_stream = false;
+    int sm_count = 0;
+    uint64_t launches = 0;
+
+    std::mutex mu;  // guards the tables (destroy may come from another thread)
+    std::vector<rve::BufferRec> buffers;
+    std::vector<uint32_t> free_slots;
+    std::vector<rve::PyramidRec> pyramids;
+
+    // device mirror of buffers[i].ptr — the "bindless descriptor array"
+    void** d_table = nullptr;
+    size_t d_table_cap = 0;
+    bool table_dirty = true;
+
+    // scratch: cubo prefix sums for rve_cull (grown on demand)
+    uint32_t* d_cubo_start = nullptr;
+    size_t d_cubo_start_cap = 0;
+    // scratch: view-space light records for rve_cluster_assign
+    float4* d_lights = nullptr;
+    size_t d_lights_cap = 0;
+    // scratch: cluster slice depth table
+    float* d_slices = nullptr;
+    size_t d_slices_cap = 0;
+};
+
+namespace rve {
+
+int set_error(int code, const char* fmt, ...);
+int check_cuda(cudaError_t e, const char* what);
+// resolves a handle; returns nullptr (and sets the error) when invalid
+BufferRec* get_buffer(rve_ctx* ctx, rve_buffer h, const char* role);
+PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h);
+// makes sure the device pointer table reflects the host table (enqueued on the stream)
+int sync_table(rve_ctx* ctx);
+int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes);
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+#define RVE_CUDA(expr)                                        \
+    do {                                                      \
+        int _rc = rve::check_cuda((expr), #expr);             \
+        if (_rc != 0) return _rc;                             \
+    } while (0)
+
+#define RVE_REQUIRE(cond, msg)                                              \
+    do {                                                                    \
+        if (!(cond)) return rve::set_error(RVE_ERR_INVALID_ARGUMENT, "%s", msg); \
+    } while (0)
+
+// ---- device helpers: GLSL min/max semantics (see oracle.cpp header) ----
+#ifdef __CUDACC__
+__device__ __forceinline__ float gmin(float x, float y) { return (y < x) ? y : x; }
+__device__ __forceinline__ float gmax(float x, float y) { return (x < y) ? y : x; }
+
+// 128-bit read-only load that does not allocate in L1 (streamed once)
+__device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint64_t pyr_level_offset(uint32_t dim, uint32_t level) {
+    const uint64_t d0 = dim, dl = dim >> level;
+    return 4ull * (d0 * d0 - dl * dl) / 3ull;
+}
+#endif
+
+}  // namespace rve

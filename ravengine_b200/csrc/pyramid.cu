@@ -1,0 +1,198 @@
+// pyramid.cu — Hi-Z depth pyramid.
+// Replaces generatePyramid (src/RenderEngine_Draw.cpp:2475-2514): one raster pass of
+// depthpyramidcopy.fsh (mip 0) + one depthpyramid.csh dispatch per further mip (10 launches
+// with barriers for 1024^2) by ONE launch: every CTA produces a 32x32 tile of mip 0 from
+// the depth buffer, reduces it through shared memory down to a single texel (mips 0..5),
+// and the last CTA to finish (ticket counter) reduces the remaining 32x32 image (mips 6..10).
+//
+// Sampler model = oracle.cpp sample_min(): min over the clamped 2x2 bilinear footprint
+// floor(u*W-0.5)+{0,1} (src/RenderEngine.cpp:323-331, reduction mode Minimum).
+#include "internal.h"
+
+namespace rve {
+
+constexpr int kPyrThreads = 256;
+constexpr int kPyrTile = 32;
+
+__device__ __forceinline__ void footprint(float x, uint32_t n, uint32_t& i0, uint32_t& i1) {
+    const float fx = floorf(x);
+    if (!(fx >= 0.0f)) {
+        i0 = 0;
+        i1 = 0;
+    } else if (fx >= float(n - 1)) {
+        i0 = n - 1;
+        i1 = n - 1;
+    } else {
+        i0 = uint32_t(fx);
+        i1 = i0 + 1;
+    }
+}
+
+__device__ __forceinline__ float sample_min_src(const float* __restrict__ img, uint32_t w, uint32_t h, float u, float v) {
+    const float x = u * float(w) - 0.5f;
+    const float y = v * float(h) - 0.5f;
+    uint32_t x0, x1, y0, y1;
+    footprint(x, w, x0, x1);
+    footprint(y, h, y0, y1);
+    const float a = __ldg(img + uint64_t(y0) * w + x0);
+    const float b = __ldg(img + uint64_t(y0) * w + x1);
+    const float c = __ldg(img + uint64_t(y1) * w + x0);
+    const float d = __ldg(img + uint64_t(y1) * w + x1);
+    return gmin(gmin(a, b), gmin(c, d));
+}
+
+// reduce `lv` (n x n, shared) into `out` (n/2 x n/2, shared) and global level
+__device__ __forceinline__ void reduce_level(const float* lv, float* out, uint32_t n_out, float* __restrict__ gdst,
+                                             uint32_t g_dim_out, uint32_t gx0, uint32_t gy0) {
+    const uint32_t n_in = n_out * 2;
+    for (uint32_t i = threadIdx.x; i < n_out * n_out; i += blockDim.x) {
+        const uint32_t x = i % n_out, y = i / n_out;
+        const float a = lv[(2 * y) * n_in + 2 * x];
+        const float b = lv[(2 * y) * n_in + 2 * x + 1];
+        const float c = lv[(2 * y + 1) * n_in + 2 * x];
+        const float d = lv[(2 * y + 1) * n_in + 2 * x + 1];
+        const float m = gmin(gmin(a, b), gmin(c, d));
+        out[i] = m;
+        gdst[uint64_t(gy0 + y) * g_dim_out + (gx0 + x)] = m;
+    }
+}
+
+__global__ void __launch_bounds__(kPyrThreads)
+pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, float* __restrict__ pyr, uint32_t dim,
+                     uint32_t levels, uint32_t tile, uint32_t* __restrict__ ticket) {
+    // all in-tile levels back to back: tile^2 + (tile/2)^2 + ... + 1 <= 1365 floats
+    __shared__ float s_lv[(4 * kPyrTile * kPyrTile) / 3 + 2];
+    __shared__ bool s_last;
+
+    const uint32_t tiles_per_row = dim / tile;
+    const uint32_t tx0 = (blockIdx.x % tiles_per_row) * tile;
+    const uint32_t ty0 = (blockIdx.x / tiles_per_row) * tile;
+
+    // mip 0 — depthpyramidcopy.fsh: texcoord = gl_FragCoord.xy / targetDim (pixel centres)
+    for (uint32_t i = threadIdx.x; i < tile * tile; i += blockDim.x) {
+        const uint32_t lx = i % tile, ly = i / tile;
+        const uint32_t x = tx0 + lx, y = ty0 + ly;
+        const float u = (float(x) + 0.5f) / float(dim);
+        const float v = (float(y) + 0.5f) / float(dim);
+        const float m = sample_min_src(depth, w, h, u, v);
+        s_lv[i] = m;
+        pyr[uint64_t(y) * dim + x] = m;
+    }
+    __syncthreads();
+
+    // mips 1..log2(tile) from shared memory — depthpyramid.csh
+    uint32_t in_off = 0, n = tile, level = 1;
+    while (n > 1 && level < levels) {
+        const uint32_t n_out = n / 2;
+        const uint32_t out_off = in_off + n * n;
+        reduce_level(s_lv + in_off, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level,
+                     tx0 >> level, ty0 >> level);
+        __syncthreads();
+        in_off = out_off;
+        n = n_out;
+        ++level;
+    }
+    if (level >= levels) return;  // dim <= tile: the single CTA did the whole chain
+
+    // remaining levels: the last CTA to arrive reduces the (dim/tile)^2 image of level log2(tile)
+    __threadfence();
+    if (threadIdx.x == 0) {
+        const uint32_t t = atomicAdd(ticket, 1u);
+        s_last = (t == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+
+    const uint32_t r = dim / tile;  // <= 32
+    const float* src = pyr + pyr_level_offset(dim, level - 1);
+    for (uint32_t i = threadIdx.x; i < r * r; i += blockDim.x) s_lv[i] = __ldcg(src + i);
+    __syncthreads();
+    in_off = 0;
+    n = r;
+    while (n > 1 && level < levels) {
+        const uint32_t n_out = n / 2;
+        const uint32_t out_off = in_off + n * n;
+        reduce_level(s_lv + in_off, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level, 0, 0);
+        __syncthreads();
+        in_off = out_off;
+        n = n_out;
+        ++level;
+    }
+    if (threadIdx.x == 0) *ticket = 0;  // re-arm for the next build on this stream
+}
+
+}  // namespace rve
+
+using namespace rve;
+
+extern "C" {
+
+int rve_depth_pyramid_create(rve_ctx* ctx, uint32_t width, rve_pyramid* out) {
+    if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(width >= 1, "pyramid width must be >= 1");
+    // src/DepthPyramid.cpp:10-17
+    const uint32_t w = width < 1024 ? width : 1024;
+    uint32_t dim = 1, l = 0;
+    while (dim * 2 <= w) {
+        dim *= 2;
+        ++l;
+    }
+    PyramidRec rec;
+    rec.dim = dim;
+    rec.levels = 1 + l;
+    const size_t texels = (4ull * dim * dim - 1) / 3;
+    int rc = rve_buffer_create(ctx, texels * sizeof(float), &rec.texels);  // zero = "far" in reverse-Z: nothing occluded
+    if (rc) return rc;
+    rc = rve_buffer_create(ctx, sizeof(uint32_t), &rec.counter);
+    if (rc) return rc;
+    rec.live = true;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ctx->pyramids.push_back(rec);
+    *out = rve_pyramid(ctx->pyramids.size() - 1);
+    return 0;
+}
+
+int rve_depth_pyramid_destroy(rve_ctx* ctx, rve_pyramid pyr) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    PyramidRec* p = get_pyramid(ctx, pyr);
+    if (!p) return RVE_ERR_BAD_HANDLE;
+    rve_buffer_destroy(ctx, p->texels);
+    rve_buffer_destroy(ctx, p->counter);
+    p->live = false;
+    return 0;
+}
+
+int rve_depth_pyramid_info(rve_ctx* ctx, rve_pyramid pyr, uint32_t* dim, uint32_t* num_levels, rve_buffer* texels) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    PyramidRec* p = get_pyramid(ctx, pyr);
+    if (!p) return RVE_ERR_BAD_HANDLE;
+    if (dim) *dim = p->dim;
+    if (num_levels) *num_levels = p->levels;
+    if (texels) *texels = p->texels;
+    return 0;
+}
+
+int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    PyramidRec* p = get_pyramid(ctx, pyr);
+    if (!p) return RVE_ERR_BAD_HANDLE;
+    BufferRec* d = get_buffer(ctx, depth, "depth");
+    if (!d) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE(width >= 1 && height >= 1, "depth buffer must be at least 1x1");
+    RVE_REQUIRE(size_t(width) * height * sizeof(float) <= d->bytes, "depth buffer smaller than width*height floats");
+    BufferRec* t = get_buffer(ctx, p->texels, "pyramid texels");
+    BufferRec* c = get_buffer(ctx, p->counter, "pyramid ticket");
+    if (!t || !c) return RVE_ERR_BAD_HANDLE;
+    const uint32_t tile = p->dim < uint32_t(kPyrTile) ? p->dim : uint32_t(kPyrTile);
+    const uint32_t blocks = (p->dim / tile) * (p->dim / tile);
+    pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height,
+                                                                  static_cast<float*>(t->ptr), p->dim, p->levels, tile,
+                                                                  static_cast<uint32_t*>(c->ptr));
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"
