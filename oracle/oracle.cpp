@@ -510,8 +510,10 @@ void orc_cluster_build(const RveGridBuildUBO* ubo_p, RveCluster* clusters) {
         for (uint32_t gy = 0; gy < ubo.gridSize[1]; ++gy)
             for (uint32_t gx = 0; gx < ubo.gridSize[0]; ++gx) {
                 const uint32_t tileIndex = gx + (gy * ubo.gridSize[0]) + (gz * ubo.gridSize[0] * ubo.gridSize[1]);
-                const float tileSizeX = float(ubo.screenDim[0]) / float(ubo.gridSize[0]);
-                const float tileSizeY = float(ubo.screenDim[1]) / float(ubo.gridSize[1]);
+                // vec2 tileSize = ubo.screenDimensions / ubo.gridSize.xy: uvec2 / uvec2 is an INTEGER
+                // division in GLSL, converted to float afterwards (cluster_build_grid.csh:48)
+                const float tileSizeX = float(ubo.screenDim[0] / ubo.gridSize[0]);
+                const float tileSizeY = float(ubo.screenDim[1] / ubo.gridSize[1]);
                 const vec3 minPoint_viewSpace = screenToView(float(gx) * tileSizeX, float(gy) * tileSizeY);
                 const vec3 maxPoint_viewSpace = screenToView(float(gx + 1) * tileSizeX, float(gy + 1) * tileSizeY);
                 // pow() differs between GPU vendors and libm; the slice depths are evaluated

@@ -1,0 +1,129 @@
+"""ctypes mirror of include/rve_b200.h (struct layouts + function prototypes).
+
+The library is loaded from the in-tree build (ravengine_b200/librve_b200.so). There is no
+CPU fallback: if the library is missing or no CUDA device exists, calls fail loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+LIB_PATH = Path(__file__).resolve().parent / "librve_b200.so"
+
+u32, u64, f32, i32 = C.c_uint32, C.c_uint64, C.c_float, C.c_int32
+
+
+class IndirectIndexedCommand(C.Structure):
+    _pack_ = 1
+    _fields_ = [("indexCount", u32), ("instanceCount", u32), ("indexStart", u32), ("baseVertex", u32), ("baseInstance", u32)]
+
+
+class CullingUBO(C.Structure):
+    _pack_ = 1
+    _fields_ = [("viewProj", f32 * 16), ("camPos", f32 * 3), ("numCubos", u32), ("cameraRenderLayers", u32),
+                ("singleInstanceModeAndShadowMode", u32)]
+
+
+class CullingUBOinstance(C.Structure):
+    _pack_ = 1
+    _fields_ = [("indirectBufferOffset", u32), ("numObjects", u32), ("cullingBufferOffset", u32), ("radius", f32),
+                ("numLODs", u32), ("idOutputBufferBindlessHandle", u32), ("entityIDInputBufferBindlessHandle", u32),
+                ("indirectOutputBufferBindlessHandle", u32), ("lodDistanceBufferBindlessHandle", u32)]
+
+
+class SkinningUBO(C.Structure):
+    _pack_ = 1
+    _fields_ = [("numObjects", u32), ("numVertices", u32), ("numBones", u32), ("boneReadOffset", u32),
+                ("vertexWriteOffset", u32), ("vertexReadOffset", u32)]
+
+
+class SkinningPrepareUBO(C.Structure):
+    _pack_ = 1
+    _fields_ = [("indexBufferOffset", u32), ("vertexBufferOffset", u32), ("nIndicesInThisMesh", u32),
+                ("nVerticesInThisMesh", u32), ("nTotalObjects", u32), ("drawCallBufferOffset", u32),
+                ("baseInstanceOffset", u32)]
+
+
+class GridBuildUBO(C.Structure):
+    _pack_ = 1
+    _fields_ = [("invProj", f32 * 16), ("gridSize", u32 * 3), ("zNear", f32), ("screenDim", u32 * 2), ("zFar", f32)]
+
+
+class GridAssignUBO(C.Structure):
+    _pack_ = 1
+    _fields_ = [("viewMat", f32 * 16), ("pointLightCount", u32), ("spotLightCount", u32)]
+
+
+class SceneGenParams(C.Structure):
+    _fields_ = [("seed", u64), ("extent_xy", f32), ("extent_z", f32), ("scale_min", f32), ("scale_max", f32),
+                ("frac_layer_zero", f32), ("frac_no_cull_bits", f32), ("id_base", u32)]
+
+
+assert C.sizeof(IndirectIndexedCommand) == 20
+assert C.sizeof(CullingUBO) == 88
+assert C.sizeof(CullingUBOinstance) == 36
+assert C.sizeof(SkinningUBO) == 24
+assert C.sizeof(SkinningPrepareUBO) == 28
+assert C.sizeof(GridBuildUBO) == 92
+assert C.sizeof(GridAssignUBO) == 72
+
+CLUSTER_BYTES = 160
+POINT_LIGHT_BYTES = 512
+SPOT_LIGHT_BYTES = 168
+
+# every symbol include/rve_b200.h declares: name -> (restype, argtypes)
+VP = C.c_void_p
+PROTOTYPES = {
+    "rve_ctx_create": (C.c_int, [C.c_int, VP, C.POINTER(VP)]),
+    "rve_ctx_destroy": (C.c_int, [VP]),
+    "rve_ctx_synchronize": (C.c_int, [VP]),
+    "rve_ctx_stream": (VP, [VP]),
+    "rve_last_error_string": (C.c_char_p, []),
+    "rve_version": (C.c_char_p, []),
+    "rve_ctx_sm_count": (C.c_int, [VP]),
+    "rve_ctx_launch_count": (u64, [VP]),
+    "rve_buffer_create": (C.c_int, [VP, C.c_size_t, C.POINTER(u32)]),
+    "rve_buffer_wrap": (C.c_int, [VP, VP, C.c_size_t, C.POINTER(u32)]),
+    "rve_buffer_destroy": (C.c_int, [VP, u32]),
+    "rve_buffer_upload": (C.c_int, [VP, u32, C.c_size_t, VP, C.c_size_t]),
+    "rve_buffer_download": (C.c_int, [VP, u32, C.c_size_t, VP, C.c_size_t]),
+    "rve_buffer_copy": (C.c_int, [VP, u32, C.c_size_t, u32, C.c_size_t, C.c_size_t]),
+    "rve_buffer_fill_zero": (C.c_int, [VP, u32, C.c_size_t, C.c_size_t]),
+    "rve_buffer_device_ptr": (VP, [VP, u32]),
+    "rve_buffer_size": (C.c_size_t, [VP, u32]),
+    "rve_buffer_bindless_index": (u32, [VP, u32]),
+    "rve_depth_pyramid_create": (C.c_int, [VP, u32, C.POINTER(u32)]),
+    "rve_depth_pyramid_destroy": (C.c_int, [VP, u32]),
+    "rve_depth_pyramid_info": (C.c_int, [VP, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]),
+    "rve_depth_pyramid_build": (C.c_int, [VP, u32, u32, u32, u32]),
+    "rve_cull": (C.c_int, [VP, C.POINTER(CullingUBO), u32, u32, u32, u32, u32, u32]),
+    "rve_skin": (C.c_int, [VP, C.POINTER(SkinningUBO), C.POINTER(u32), C.POINTER(u32), u32, u32]),
+    "rve_skinned_drawcall_prepare": (C.c_int, [VP, C.POINTER(SkinningPrepareUBO), u32]),
+    "rve_cluster_build": (C.c_int, [VP, C.POINTER(GridBuildUBO), u32]),
+    "rve_cluster_assign": (C.c_int, [VP, C.POINTER(GridAssignUBO), u32, u32, u32, u32]),
+    "rve_shard_offsets": (C.c_int, [VP, u32, u32, u32, u32, u32]),
+    "rve_gather_instance_counts": (C.c_int, [VP, u32, u32, u32, u32, C.c_size_t]),
+    "rve_gen_instances": (C.c_int, [VP, C.POINTER(SceneGenParams), u64, u32, u32, u32, u32, u32]),
+}
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    """Load librve_b200.so (building it in-tree first if nvcc is available and it is stale)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not LIB_PATH.exists():
+        from .build import build_native
+
+        build_native()
+    if not LIB_PATH.exists():
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -m ravengine_b200.build` (no CPU fallback exists)")
+    lib = C.CDLL(str(LIB_PATH))
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError = ABI mismatch, fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib

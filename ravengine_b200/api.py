@@ -1,0 +1,170 @@
+"""Thin Python host layer over the C-ABI (ctypes). torch is used only for device memory,
+streams and torch.distributed — every compute call goes to librve_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import _abi
+from ._abi import (CullingUBO, CullingUBOinstance, GridAssignUBO, GridBuildUBO, SceneGenParams, SkinningPrepareUBO,
+                   SkinningUBO)
+
+
+class RveError(RuntimeError):
+    pass
+
+
+def _check(lib, rc: int) -> None:
+    if rc != 0:
+        raise RveError(f"rve error {rc}: {lib.rve_last_error_string().decode()}")
+
+
+@dataclass
+class Pyramid:
+    handle: int
+    dim: int
+    levels: int
+    texels: "Buffer"
+
+
+class Buffer:
+    """RGL::IBuffer stand-in: `handle` doubles as the bindless index a CUBO stores."""
+
+    def __init__(self, ctx: "Context", handle: int, nbytes: int, keepalive=None):
+        self.ctx, self.handle, self.nbytes, self._keepalive = ctx, handle, nbytes, keepalive
+
+    @property
+    def bindless(self) -> int:
+        return self.handle
+
+    @property
+    def ptr(self) -> int:
+        return self.ctx.lib.rve_buffer_device_ptr(self.ctx.h, self.handle)
+
+    def upload(self, arr: np.ndarray, offset: int = 0) -> "Buffer":
+        arr = np.ascontiguousarray(arr)
+        _check(self.ctx.lib, self.ctx.lib.rve_buffer_upload(self.ctx.h, self.handle, offset, arr.ctypes.data, arr.nbytes))
+        # pageable upload is staged before the call returns; pinned callers must keep `arr` alive
+        return self
+
+    def download(self, dtype=np.uint8, offset: int = 0, nbytes: int | None = None) -> np.ndarray:
+        nbytes = self.nbytes - offset if nbytes is None else nbytes
+        out = np.empty(nbytes // np.dtype(dtype).itemsize, dtype=dtype)
+        _check(self.ctx.lib, self.ctx.lib.rve_buffer_download(self.ctx.h, self.handle, offset, out.ctypes.data, out.nbytes))
+        return out
+
+    def zero(self, offset: int = 0, nbytes: int | None = None) -> None:
+        nbytes = self.nbytes - offset if nbytes is None else nbytes
+        _check(self.ctx.lib, self.ctx.lib.rve_buffer_fill_zero(self.ctx.h, self.handle, offset, nbytes))
+
+    def destroy(self) -> None:
+        _check(self.ctx.lib, self.ctx.lib.rve_buffer_destroy(self.ctx.h, self.handle))
+        self._keepalive = None
+
+
+class Context:
+    """One device + one in-order stream (the reference's device/queue pair)."""
+
+    def __init__(self, device: int = 0, stream: int | None = None):
+        self.lib = _abi.load_library()
+        h = C.c_void_p()
+        _check(self.lib, self.lib.rve_ctx_create(device, C.c_void_p(stream) if stream else None, C.byref(h)))
+        self.h = h
+        self.device = device
+
+    def close(self) -> None:
+        if self.h:
+            self.lib.rve_ctx_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- plumbing ----
+    def synchronize(self) -> None:
+        _check(self.lib, self.lib.rve_ctx_synchronize(self.h))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.rve_ctx_stream(self.h) or 0)
+
+    @property
+    def sm_count(self) -> int:
+        return self.lib.rve_ctx_sm_count(self.h)
+
+    @property
+    def launch_count(self) -> int:
+        return int(self.lib.rve_ctx_launch_count(self.h))
+
+    # ---- buffers ----
+    def create_buffer(self, nbytes: int) -> Buffer:
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rve_buffer_create(self.h, nbytes, C.byref(out)))
+        return Buffer(self, out.value, nbytes)
+
+    def buffer_from_numpy(self, arr: np.ndarray) -> Buffer:
+        arr = np.ascontiguousarray(arr)
+        return self.create_buffer(max(arr.nbytes, 16)).upload(arr)
+
+    def wrap_tensor(self, t) -> Buffer:
+        """Register a CUDA torch tensor's storage as a buffer (no copy)."""
+        assert t.is_cuda and t.is_contiguous()
+        nbytes = t.numel() * t.element_size()
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rve_buffer_wrap(self.h, C.c_void_p(t.data_ptr()), nbytes, C.byref(out)))
+        return Buffer(self, out.value, nbytes, keepalive=t)
+
+    def copy(self, src: Buffer, dst: Buffer, nbytes: int, src_off: int = 0, dst_off: int = 0) -> None:
+        _check(self.lib, self.lib.rve_buffer_copy(self.h, src.handle, src_off, dst.handle, dst_off, nbytes))
+
+    # ---- stages ----
+    def create_pyramid(self, width: int) -> Pyramid:
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rve_depth_pyramid_create(self.h, width, C.byref(out)))
+        dim, lv, tex = C.c_uint32(), C.c_uint32(), C.c_uint32()
+        _check(self.lib, self.lib.rve_depth_pyramid_info(self.h, out.value, C.byref(dim), C.byref(lv), C.byref(tex)))
+        nbytes = self.lib.rve_buffer_size(self.h, tex.value)
+        return Pyramid(out.value, dim.value, lv.value, Buffer(self, tex.value, nbytes))
+
+    def build_pyramid(self, pyr: Pyramid, depth: Buffer, width: int, height: int) -> None:
+        _check(self.lib, self.lib.rve_depth_pyramid_build(self.h, pyr.handle, depth.handle, width, height))
+
+    def cull(self, ubo: CullingUBO, cubos: Buffer, model: Buffer, layers: Buffer, flags: Buffer, pyr: Pyramid,
+             num_groups_x: int) -> None:
+        _check(self.lib, self.lib.rve_cull(self.h, C.byref(ubo), cubos.handle, model.handle, layers.handle, flags.handle,
+                                           pyr.handle, num_groups_x))
+
+    def skin(self, ubo: SkinningUBO, outs: list[Buffer], ins: list[Buffer], pose: Buffer, weights: Buffer) -> None:
+        o = (C.c_uint32 * 5)(*[b.handle for b in outs])
+        i = (C.c_uint32 * 5)(*[b.handle for b in ins])
+        _check(self.lib, self.lib.rve_skin(self.h, C.byref(ubo), o, i, pose.handle, weights.handle))
+
+    def skinned_drawcall_prepare(self, ubo: SkinningPrepareUBO, indirect: Buffer) -> None:
+        _check(self.lib, self.lib.rve_skinned_drawcall_prepare(self.h, C.byref(ubo), indirect.handle))
+
+    def cluster_build(self, ubo: GridBuildUBO, clusters: Buffer) -> None:
+        _check(self.lib, self.lib.rve_cluster_build(self.h, C.byref(ubo), clusters.handle))
+
+    def cluster_assign(self, ubo: GridAssignUBO, clusters: Buffer, points: Buffer | None, spots: Buffer | None,
+                       num_clusters: int) -> None:
+        inv = 0xFFFFFFFF
+        _check(self.lib, self.lib.rve_cluster_assign(self.h, C.byref(ubo), clusters.handle,
+                                                     points.handle if points else inv, spots.handle if spots else inv,
+                                                     num_clusters))
+
+    def gen_instances(self, params: SceneGenParams, first_index: int, count: int, model: Buffer, layers: Buffer,
+                      flags: Buffer, ids: Buffer) -> None:
+        _check(self.lib, self.lib.rve_gen_instances(self.h, C.byref(params), first_index, count, model.handle,
+                                                    layers.handle, flags.handle, ids.handle))
+
+    def shard_offsets(self, counts_all: Buffer, world: int, slots: int, offsets: Buffer, totals: Buffer) -> None:
+        _check(self.lib, self.lib.rve_shard_offsets(self.h, counts_all.handle, world, slots, offsets.handle, totals.handle))
+
+    def gather_instance_counts(self, indirect: Buffer, first_slot: int, slots: int, out: Buffer, out_off: int = 0) -> None:
+        _check(self.lib, self.lib.rve_gather_instance_counts(self.h, indirect.handle, first_slot, slots, out.handle, out_off))

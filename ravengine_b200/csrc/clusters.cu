@@ -1,0 +1,233 @@
+// clusters.cu — clustered light grid build (shaders/cluster_build_grid.csh:16-79)
+// and light assignment (8a-6, shaders/cluster_assign_lights.csh:28-88).
+//
+// The reference bins with 27 CTAs x 128 threads, one thread per cluster walking all lights
+// serially through a 512-B-stride struct array. Here the lights are first reduced once to
+// 16-B view-space records (centre, radius^2), then one WARP owns a cluster: 32 lights are
+// tested per step (lane = light), hits are appended in index order with ballot/popc, and the
+// warp stops as soon as 16 lights are found — the result is, as in the shader, the <=16
+// lowest-index intersecting lights in ascending order. Eight clusters per CTA share each
+// light tile through shared memory.
+#include <cmath>
+
+#include "internal.h"
+
+namespace rve {
+
+constexpr int kAssignThreads = 256;
+constexpr int kAssignWarps = kAssignThreads / 32;
+constexpr int kLightTile = 1024;
+
+__global__ void cluster_build_kernel(const RveGridBuildUBO u, const float* __restrict__ slices,
+                                     RveCluster* __restrict__ clusters, uint32_t numClusters) {
+    const uint32_t tileIndex = blockIdx.x * blockDim.x + threadIdx.x;
+    if (tileIndex >= numClusters) return;
+    const uint32_t gx = tileIndex % u.gridSize[0];
+    const uint32_t gy = (tileIndex / u.gridSize[0]) % u.gridSize[1];
+    const uint32_t gz = tileIndex / (u.gridSize[0] * u.gridSize[1]);
+    // uvec2 / uvec2: integer division, then conversion (cluster_build_grid.csh:48)
+    const float tileSizeX = float(u.screenDim[0] / u.gridSize[0]);
+    const float tileSizeY = float(u.screenDim[1] / u.gridSize[1]);
+
+    // screenToView (cluster_build_grid.csh:16-26): ndc = (s/dim*2-1, 0, 1); view = invProj*ndc; /= w
+    auto screenToView = [&](float sx, float sy, float& vx, float& vy, float& vz) {
+        const float nx = sx / float(u.screenDim[0]) * 2.0f - 1.0f;
+        const float ny = sy / float(u.screenDim[1]) * 2.0f - 1.0f;
+        // ((col0*nx + col1*ny) + col2*0) + col3*1
+        float v[4];
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+            v[r] = ((u.invProj[0 + r] * nx + u.invProj[4 + r] * ny) + u.invProj[8 + r] * 0.0f) + u.invProj[12 + r] * 1.0f;
+        vx = v[0] / v[3];
+        vy = v[1] / v[3];
+        vz = v[2] / v[3];
+    };
+    float mnx, mny, mnz, mxx, mxy, mxz;
+    screenToView(float(gx) * tileSizeX, float(gy) * tileSizeY, mnx, mny, mnz);
+    screenToView(float(gx + 1) * tileSizeX, float(gy + 1) * tileSizeY, mxx, mxy, mxz);
+    const float tileNear = slices[gz], tileFar = slices[gz + 1];
+
+    // lineIntersectionWithZPlane(eye=0, end, zDistance): direction = end - 0; normal = (0,0,-1)
+    //   t = (zDistance - dot(normal, 0)) / dot(normal, direction);  result = 0 + t*direction
+    auto isect = [](float ex, float ey, float ez, float zDistance, float& ox, float& oy, float& oz) {
+        const float dx = ex - 0.0f, dy = ey - 0.0f, dz = ez - 0.0f;
+        const float dotNS = (0.0f * 0.0f + 0.0f * 0.0f) + (-1.0f) * 0.0f;
+        const float dotND = (0.0f * dx + 0.0f * dy) + (-1.0f) * dz;
+        const float t = (zDistance - dotNS) / dotND;
+        ox = 0.0f + dx * t;
+        oy = 0.0f + dy * t;
+        oz = 0.0f + dz * t;
+    };
+    float a[3], b[3], c[3], d[3];
+    isect(mnx, mny, mnz, tileNear, a[0], a[1], a[2]);  // minPointNear
+    isect(mnx, mny, mnz, tileFar, b[0], b[1], b[2]);   // minPointFar
+    isect(mxx, mxy, mxz, tileNear, c[0], c[1], c[2]);  // maxPointNear
+    isect(mxx, mxy, mxz, tileFar, d[0], d[1], d[2]);   // maxPointFar
+    RveCluster* cl = clusters + tileIndex;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        cl->minPoint[k] = gmin(a[k], b[k]);
+        cl->maxPoint[k] = gmax(c[k], d[k]);
+    }
+}
+
+// light -> (view-space centre, radius^2); stride/offsets select point or spot layout
+__global__ void light_prepare_kernel(const unsigned char* __restrict__ lights, uint32_t count, uint32_t stride,
+                                     uint32_t posOffset, uint32_t intensityOffset, bool originFromMatrix,
+                                     const RveGridAssignUBO u, float4* __restrict__ out) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    const unsigned char* L = lights + uint64_t(i) * stride;
+    const float* pp = reinterpret_cast<const float*>(L + posOffset);
+    float px = __ldg(pp), py = __ldg(pp + 1), pz = __ldg(pp + 2);
+    if (originFromMatrix) {  // (worldTransform * vec4(0,0,0,1)).xyz: 0 + col3
+        px = 0.0f + px;
+        py = 0.0f + py;
+        pz = 0.0f + pz;
+    }
+    const float intensity = __ldg(reinterpret_cast<const float*>(L + intensityOffset));
+    const float* m = u.viewMat;
+    float4 r;
+    r.x = ((m[0] * px + m[4] * py) + m[8] * pz) + m[12] * 1.0f;
+    r.y = ((m[1] * px + m[5] * py) + m[9] * pz) + m[13] * 1.0f;
+    r.z = ((m[2] * px + m[6] * py) + m[10] * pz) + m[14] * 1.0f;
+    const float radius = sqrtf(intensity / RVE_LIGHT_MIN_INFLUENCE);  // cluster_shared.glsl:41-44
+    r.w = radius * radius;
+    out[i] = r;
+}
+
+// one warp per cluster; kinds processed one after the other (points, then spots)
+__global__ void __launch_bounds__(kAssignThreads)
+cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, const float4* __restrict__ pointRec,
+                      uint32_t pointCount, const float4* __restrict__ spotRec, uint32_t spotCount) {
+    __shared__ float4 s_tile[kLightTile];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t index = blockIdx.x * kAssignWarps + warp;
+    const bool have = index < numClusters;
+    float mn[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
+    if (have) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            mn[k] = clusters[index].minPoint[k];
+            mx[k] = clusters[index].maxPoint[k];
+        }
+    }
+    for (int kind = 0; kind < 2; ++kind) {
+        const float4* rec = kind ? spotRec : pointRec;
+        const uint32_t count = kind ? spotCount : pointCount;
+        const uint32_t cap = kind ? RVE_CLUSTER_MAX_SPOTS : RVE_CLUSTER_MAX_POINTS;
+        uint32_t* outIdx = have ? (kind ? clusters[index].spotLightIndices : clusters[index].pointLightIndices) : nullptr;
+        uint32_t found = 0;  // warp-uniform
+        for (uint32_t base = 0; base < count; base += kLightTile) {
+            // stop when every cluster of the CTA is full
+            if (__syncthreads_and(!have || found >= cap)) break;
+            const uint32_t n = min(uint32_t(kLightTile), count - base);
+            for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_tile[i] = __ldg(rec + base + i);
+            __syncthreads();
+            if (have) {
+                for (uint32_t j = 0; j < n && found < cap; j += 32) {
+                    bool hit = false;
+                    if (j + lane < n) {
+                        const float4 L = s_tile[j + lane];
+                        // sphereAABBIntersection (cluster_assign_lights.csh:28-35)
+                        const float qx = gmin(gmax(L.x, mn[0]), mx[0]) - L.x;
+                        const float qy = gmin(gmax(L.y, mn[1]), mx[1]) - L.y;
+                        const float qz = gmin(gmax(L.z, mn[2]), mx[2]) - L.z;
+                        hit = ((qx * qx + qy * qy) + qz * qz) <= L.w;
+                    }
+                    const uint32_t ballot = __ballot_sync(0xffffffffu, hit);
+                    if (hit) {
+                        const uint32_t pos = found + __popc(ballot & ((1u << lane) - 1u));
+                        if (pos < cap) outIdx[pos] = base + j + lane;
+                    }
+                    found = min(cap, found + uint32_t(__popc(ballot)));
+                }
+            }
+        }
+        if (have && lane == 0) {
+            if (kind) clusters[index].spotLightCount = found;
+            else clusters[index].pointLightCount = found;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace rve
+
+using namespace rve;
+
+extern "C" {
+
+int rve_cluster_build(rve_ctx* ctx, const RveGridBuildUBO* ubo, rve_buffer clusters) {
+    if (!ctx || !ubo) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    const uint64_t n64 = uint64_t(ubo->gridSize[0]) * ubo->gridSize[1] * ubo->gridSize[2];
+    if (n64 == 0) return 0;
+    RVE_REQUIRE(n64 <= 0x7FFFFFFFull, "cluster grid too large");
+    BufferRec* b = get_buffer(ctx, clusters, "clusters");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE(n64 * sizeof(RveCluster) <= b->bytes, "cluster buffer too small");
+    // slice depths zFar*pow(zNear/zFar, k/gridZ) (cluster_build_grid.csh:58-61): evaluated once
+    // with the host libm (GPU pow is vendor-specific; the oracle uses the same libm)
+    const uint32_t gz = ubo->gridSize[2];
+    std::vector<float> slices(gz + 1);
+    for (uint32_t k = 0; k <= gz; ++k) slices[k] = ubo->zFar * std::pow(ubo->zNear / ubo->zFar, float(k) / float(gz));
+    int rc = ensure_scratch(ctx, reinterpret_cast<void**>(&ctx->d_slices), &ctx->d_slices_cap, slices.size() * sizeof(float));
+    if (rc) return rc;
+    RVE_CUDA(cudaMemcpyAsync(ctx->d_slices, slices.data(), slices.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    const uint32_t n = uint32_t(n64), threads = 128;
+    cluster_build_kernel<<<(n + threads - 1) / threads, threads, 0, ctx->stream>>>(*ubo, ctx->d_slices,
+                                                                                 static_cast<RveCluster*>(b->ptr), n);
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int rve_cluster_assign(rve_ctx* ctx, const RveGridAssignUBO* ubo, rve_buffer clusters, rve_buffer point_lights,
+                       rve_buffer spot_lights, uint32_t num_clusters) {
+    if (!ctx || !ubo) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    if (num_clusters == 0) return 0;
+    BufferRec* b = get_buffer(ctx, clusters, "clusters");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE(uint64_t(num_clusters) * sizeof(RveCluster) <= b->bytes, "cluster buffer too small");
+    const unsigned char* pl = nullptr;
+    const unsigned char* sl = nullptr;
+    if (ubo->pointLightCount) {
+        BufferRec* p = get_buffer(ctx, point_lights, "point lights");
+        if (!p) return RVE_ERR_BAD_HANDLE;
+        RVE_REQUIRE(uint64_t(ubo->pointLightCount) * sizeof(RvePointLight) <= p->bytes, "point light buffer too small");
+        pl = static_cast<const unsigned char*>(p->ptr);
+    }
+    if (ubo->spotLightCount) {
+        BufferRec* s = get_buffer(ctx, spot_lights, "spot lights");
+        if (!s) return RVE_ERR_BAD_HANDLE;
+        RVE_REQUIRE(uint64_t(ubo->spotLightCount) * sizeof(RveSpotLight) <= s->bytes, "spot light buffer too small");
+        sl = static_cast<const unsigned char*>(s->ptr);
+    }
+    const size_t total = size_t(ubo->pointLightCount) + ubo->spotLightCount;
+    int rc = ensure_scratch(ctx, reinterpret_cast<void**>(&ctx->d_lights), &ctx->d_lights_cap, (total + 1) * sizeof(float4));
+    if (rc) return rc;
+    float4* prec = ctx->d_lights;
+    float4* srec = ctx->d_lights + ubo->pointLightCount;
+    const uint32_t threads = 256;
+    if (ubo->pointLightCount) {
+        light_prepare_kernel<<<(ubo->pointLightCount + threads - 1) / threads, threads, 0, ctx->stream>>>(
+            pl, ubo->pointLightCount, uint32_t(sizeof(RvePointLight)), uint32_t(offsetof(RvePointLight, position)),
+            uint32_t(offsetof(RvePointLight, intensity)), false, *ubo, prec);
+        ctx->launches++;
+    }
+    if (ubo->spotLightCount) {
+        light_prepare_kernel<<<(ubo->spotLightCount + threads - 1) / threads, threads, 0, ctx->stream>>>(
+            sl, ubo->spotLightCount, uint32_t(sizeof(RveSpotLight)), uint32_t(offsetof(RveSpotLight, worldTransform) + 48),
+            uint32_t(offsetof(RveSpotLight, intensity)), true, *ubo, srec);
+        ctx->launches++;
+    }
+    cluster_assign_kernel<<<(num_clusters + kAssignWarps - 1) / kAssignWarps, kAssignThreads, 0, ctx->stream>>>(
+        static_cast<RveCluster*>(b->ptr), num_clusters, prec, ubo->pointLightCount, srec, ubo->spotLightCount);
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // extern "C"
