@@ -1,0 +1,103 @@
+/*
+ * rve_shim.h — host-side mirror of the reference's per-frame encode blocks for the render-prep
+ * path, as a C API over rve_b200.h. Each function reproduces one lambda of RenderEngine::Draw
+ * (src/RenderEngine_Draw.cpp): the same table construction (CUBO table, indirect-init table,
+ * offsets, dispatch sizes), the same buffer (re)allocation rules, then the rve_* call that
+ * replaces "bind + SetComputeBytes + DispatchCompute". The data it walks is a stand-in for
+ * World::RenderData (include/RavEngine/World.hpp:329-449).
+ */
+#ifndef RVE_SHIM_H
+#define RVE_SHIM_H
+
+#include "rve_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rvs_world rvs_world;
+
+/* material kinds, used like filterRenderData(lightingFilter, materialInstance)
+ * (src/RenderEngine_Draw.cpp:1232, 1080): a pass keeps a material iff (kind & pass_mask) != 0 */
+#define RVS_MAT_LIT_OPAQUE 0x1u
+#define RVS_MAT_UNLIT_OPAQUE 0x2u
+#define RVS_MAT_LIT_TRANSPARENT 0x4u
+#define RVS_MAT_UNLIT_TRANSPARENT 0x8u
+#define RVS_MAT_ALL 0xFu
+
+/* flags for rvs_world_create */
+#define RVS_QUIRK_INDIRECT_SLOT 0x1u /* write the indirect-init entry at (meshID + lodID) exactly like
+                                        src/RenderEngine_Draw.cpp:1314 (collides when a material holds several
+                                        multi-LOD collections); default: running LOD offset = what the shader reads */
+
+RVE_API int rvs_world_create(rve_ctx* ctx, uint32_t flags, rvs_world** out);
+RVE_API int rvs_world_destroy(rvs_world* w);
+
+/* World::RenderData::worldTransforms / renderLayers / perObjectAttributes private buffers
+ * (include/RavEngine/World.hpp:440-446), indexed by entity id. */
+RVE_API int rvs_world_set_entity_buffers(rvs_world* w, rve_buffer model_matrices, rve_buffer render_layers,
+                                         rve_buffer per_object_flags);
+
+/* MeshCollectionStatic (include/RavEngine/MeshCollection.hpp:24-59): bounding radius, per-LOD
+ * distance thresholds (uploaded to a device buffer like lodDistances.GetPrivateBuffer()) and the
+ * per-LOD mesh ranges in the shared arena (totalIndices, getIndexRangeStart, getVertexRangeStart). */
+RVE_API int rvs_mesh_collection_create(rvs_world* w, float radius, uint32_t num_lods, const float* lod_distances,
+                                       const uint32_t* index_counts, const uint32_t* index_starts,
+                                       const uint32_t* base_vertices, uint32_t* out_mesh);
+
+/* staticMeshRenderData: ordered map material -> MDIICommand{commands[]} (World.hpp:339-349).
+ * Materials are visited in creation order. */
+RVE_API int rvs_material_create(rvs_world* w, uint32_t kind, uint32_t* out_material);
+/* one command = (mesh collection, dense entity-id list); ids live in a device buffer
+ * (command.entities.GetPrivateBuffer()). */
+RVE_API int rvs_material_add_command(rvs_world* w, uint32_t material, uint32_t mesh, rve_buffer entity_ids,
+                                     uint32_t entity_count);
+/* update DenseSize()/buffer of an existing command */
+RVE_API int rvs_material_set_command_entities(rvs_world* w, uint32_t material, uint32_t command_index,
+                                              rve_buffer entity_ids, uint32_t entity_count);
+
+/* cullTheRenderData(staticMeshRenderData) — src/RenderEngine_Draw.cpp:1221-1407. */
+RVE_API int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
+                            uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid);
+/* drawcommand.cullingBuffer / indirectBuffer of a material after rvs_cull_static */
+RVE_API int rvs_material_outputs(rvs_world* w, uint32_t material, rve_buffer* culling_buffer, rve_buffer* indirect_buffer,
+                                 uint32_t* num_lods_total, uint32_t* num_entities_total);
+/* the world's CUBO buffer and the numCubos / totalEntities of the last static cull (for inspection) */
+RVE_API int rvs_last_cull_info(rvs_world* w, rve_buffer* cubo_buffer, uint32_t* num_cubos, uint32_t* total_entities);
+
+/* ---- skinned path ---- */
+/* MeshAssetSkinned: vertex/index ranges in the shared arena, radius, weights buffer */
+RVE_API int rvs_skinned_mesh_create(rvs_world* w, uint32_t num_verts, uint32_t num_indices, uint32_t index_start,
+                                    uint32_t vertex_start, float radius, rve_buffer weights, uint32_t* out_mesh);
+RVE_API int rvs_skinned_material_create(rvs_world* w, uint32_t kind, uint32_t* out_material);
+/* MDIICommandSkinned::command (World.hpp:351-362). `palettes` = entity_count * num_bones mat4 in
+ * entities.GetReverseMap() order; caller-owned host memory read at rvs_pose_skeletal_meshes time
+ * (AnimatorComponent::GetSkinningMats, src/RenderEngine_Draw.cpp:611-619). */
+RVE_API int rvs_skinned_material_add_command(rvs_world* w, uint32_t material, uint32_t mesh, uint32_t num_bones,
+                                             rve_buffer entity_ids, uint32_t entity_count, const float* palettes);
+/* sharedPosition/Normal/Tangent/Bitangent/UV0 buffers of the mesh arena (src/RenderEngine_Allocate.cpp:168-177) */
+RVE_API int rvs_world_set_mesh_arena(rvs_world* w, const rve_buffer in_streams[5]);
+/* prepareSkeletalMeshBuffers — :479-544 (pow2 growth of shared skinned streams, palette buffer,
+ * per-material indirect + culling buffers). Returns skeletalMeshesExist in *exist. */
+RVE_API int rvs_prepare_skeletal_mesh_buffers(rvs_world* w, uint32_t* exist);
+/* poseSkeletalMeshes — :577-630 (palette upload + one rve_skin per command) */
+RVE_API int rvs_pose_skeletal_meshes(rvs_world* w);
+/* prepareSkeletalCullingBuffer — :546-574 (one rve_skinned_drawcall_prepare per command) */
+RVE_API int rvs_prepare_skeletal_culling_buffer(rvs_world* w);
+/* cullSkeletalMeshes — :1067-1218 (single-instance mode; dispatch sized by the LAST command, :1214) */
+RVE_API int rvs_cull_skeletal(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
+                              uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid);
+RVE_API int rvs_skinned_outputs(rvs_world* w, rve_buffer out_streams[5], rve_buffer* pose_buffer);
+RVE_API int rvs_skinned_material_outputs(rvs_world* w, uint32_t material, rve_buffer* culling_buffer,
+                                         rve_buffer* indirect_buffer, uint32_t* num_entities_total);
+
+/* ---- clustered lights: renderFromPerspective<includeLighting> prologue, :928-974 ---- */
+RVE_API int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[16], const uint32_t grid_size[3],
+                           const uint32_t screen_dim[2], float z_near, float z_far, rve_buffer point_lights,
+                           uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count,
+                           rve_buffer* out_cluster_buffer);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
