@@ -237,6 +237,17 @@ RVE_API int rve_ctx_sm_count(rve_ctx* ctx);
 /* how many kernels this context has launched so far (bench.py "gpu_launches") */
 RVE_API uint64_t rve_ctx_launch_count(rve_ctx* ctx);
 
+/* Per-kernel device timing (bench.py roofline): while enabled, the dominant kernel of each
+ * stage is bracketed by CUDA events on the context's stream. kernel: 0 = cull, 1 = depth pyramid,
+ * 2 = skinning, 3 = cluster assign. rve_ctx_profile_read synchronises, returns the summed
+ * milliseconds and launch count since the last read, and clears them. */
+#define RVE_PROF_CULL 0
+#define RVE_PROF_PYRAMID 1
+#define RVE_PROF_SKIN 2
+#define RVE_PROF_CLUSTER_ASSIGN 3
+RVE_API int rve_ctx_set_profiling(rve_ctx* ctx, int enabled);
+RVE_API int rve_ctx_profile_read(rve_ctx* ctx, int kernel, double* total_ms, uint32_t* launches);
+
 /* ------------------------------------------------------------------ */
 /* buffers — RGL::IBuffer (deps/RGL/include/RGL/Buffer.hpp:50-81)      */
 /* ------------------------------------------------------------------ */

@@ -82,6 +82,8 @@ PROTOTYPES = {
     "rve_version": (C.c_char_p, []),
     "rve_ctx_sm_count": (C.c_int, [VP]),
     "rve_ctx_launch_count": (u64, [VP]),
+    "rve_ctx_set_profiling": (C.c_int, [VP, C.c_int]),
+    "rve_ctx_profile_read": (C.c_int, [VP, C.c_int, C.POINTER(C.c_double), C.POINTER(u32)]),
     "rve_buffer_create": (C.c_int, [VP, C.c_size_t, C.POINTER(u32)]),
     "rve_buffer_wrap": (C.c_int, [VP, VP, C.c_size_t, C.POINTER(u32)]),
     "rve_buffer_destroy": (C.c_int, [VP, u32]),
@@ -105,6 +107,33 @@ PROTOTYPES = {
     "rve_gather_instance_counts": (C.c_int, [VP, u32, u32, u32, u32, C.c_size_t]),
     "rve_gen_instances": (C.c_int, [VP, C.POINTER(SceneGenParams), u64, u32, u32, u32, u32, u32]),
 }
+
+FP = C.POINTER(f32)
+UP = C.POINTER(u32)
+# include/rve_shim.h
+PROTOTYPES.update({
+    "rvs_world_create": (C.c_int, [VP, u32, C.POINTER(VP)]),
+    "rvs_world_destroy": (C.c_int, [VP]),
+    "rvs_world_set_entity_buffers": (C.c_int, [VP, u32, u32, u32]),
+    "rvs_mesh_collection_create": (C.c_int, [VP, f32, u32, FP, UP, UP, UP, UP]),
+    "rvs_material_create": (C.c_int, [VP, u32, UP]),
+    "rvs_material_add_command": (C.c_int, [VP, u32, u32, u32, u32]),
+    "rvs_material_set_command_entities": (C.c_int, [VP, u32, u32, u32, u32]),
+    "rvs_cull_static": (C.c_int, [VP, FP, FP, u32, u32, u32, u32]),
+    "rvs_material_outputs": (C.c_int, [VP, u32, UP, UP, UP, UP]),
+    "rvs_last_cull_info": (C.c_int, [VP, UP, UP, UP]),
+    "rvs_skinned_mesh_create": (C.c_int, [VP, u32, u32, u32, u32, f32, u32, UP]),
+    "rvs_skinned_material_create": (C.c_int, [VP, u32, UP]),
+    "rvs_skinned_material_add_command": (C.c_int, [VP, u32, u32, u32, u32, u32, VP]),
+    "rvs_world_set_mesh_arena": (C.c_int, [VP, UP]),
+    "rvs_prepare_skeletal_mesh_buffers": (C.c_int, [VP, UP]),
+    "rvs_pose_skeletal_meshes": (C.c_int, [VP]),
+    "rvs_prepare_skeletal_culling_buffer": (C.c_int, [VP]),
+    "rvs_cull_skeletal": (C.c_int, [VP, FP, FP, u32, u32, u32, u32]),
+    "rvs_skinned_outputs": (C.c_int, [VP, UP, UP]),
+    "rvs_skinned_material_outputs": (C.c_int, [VP, u32, UP, UP, UP]),
+    "rvs_bin_lights": (C.c_int, [VP, FP, FP, UP, UP, f32, f32, u32, u32, u32, u32, UP]),
+})
 
 _lib = None
 

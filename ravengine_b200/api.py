@@ -102,6 +102,15 @@ class Context:
     def launch_count(self) -> int:
         return int(self.lib.rve_ctx_launch_count(self.h))
 
+    def set_profiling(self, on: bool) -> None:
+        _check(self.lib, self.lib.rve_ctx_set_profiling(self.h, 1 if on else 0))
+
+    def profile_read(self, kernel: int) -> tuple[float, int]:
+        """(total ms, launches) of kernel 0 cull / 1 pyramid / 2 skinning / 3 cluster assign since the last read."""
+        ms, n = C.c_double(), C.c_uint32()
+        _check(self.lib, self.lib.rve_ctx_profile_read(self.h, kernel, C.byref(ms), C.byref(n)))
+        return ms.value, n.value
+
     # ---- buffers ----
     def create_buffer(self, nbytes: int) -> Buffer:
         out = C.c_uint32()

@@ -10,7 +10,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "librve_b200.so"
-SOURCES = ["ctx.cu", "pyramid.cu", "cull.cu", "skinning.cu", "clusters.cu", "scenegen.cu", "frame.cu"]
+SOURCES = ["ctx.cu", "pyramid.cu", "cull.cu", "skinning.cu", "clusters.cu", "scenegen.cu", "frame.cu", "frame_cull.cu", "frame_skinned.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -33,7 +33,7 @@ def needs_build() -> bool:
     if not LIB.exists():
         return True
     t = LIB.stat().st_mtime
-    deps = [CSRC / s for s in SOURCES] + [CSRC / "internal.h", HERE.parent / "include" / "rve_b200.h", Path(__file__)]
+    deps = [CSRC / s for s in SOURCES] + [CSRC / "internal.h", CSRC / "frame_internal.h", HERE.parent / "include" / "rve_shim.h", HERE.parent / "include" / "rve_b200.h", Path(__file__)]
     return any(d.exists() and d.stat().st_mtime > t for d in deps)
 
 

@@ -223,6 +223,7 @@ int rve_cluster_assign(rve_ctx* ctx, const RveGridAssignUBO* ubo, rve_buffer clu
             uint32_t(offsetof(RveSpotLight, intensity)), true, *ubo, srec);
         ctx->launches++;
     }
+    ProfScope prof(ctx, RVE_PROF_CLUSTER_ASSIGN);
     cluster_assign_kernel<<<(num_clusters + kAssignWarps - 1) / kAssignWarps, kAssignThreads, 0, ctx->stream>>>(
         static_cast<RveCluster*>(b->ptr), num_clusters, prec, ubo->pointLightCount, srec, ubo->spotLightCount);
     ctx->launches++;

@@ -156,6 +156,30 @@ int rve_ctx_synchronize(rve_ctx* ctx) {
     return 0;
 }
 
+int rve_ctx_set_profiling(rve_ctx* ctx, int enabled) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    ctx->profiling = enabled != 0;
+    return 0;
+}
+
+int rve_ctx_profile_read(rve_ctx* ctx, int kernel, double* total_ms, uint32_t* launches) {
+    if (!ctx || kernel < 0 || kernel > 3) return set_error(RVE_ERR_INVALID_ARGUMENT, "bad profile query");
+    DeviceGuard g(ctx->device);
+    RVE_CUDA(cudaStreamSynchronize(ctx->stream));
+    double sum = 0;
+    for (auto& pr : ctx->prof[kernel]) {
+        float ms = 0;
+        RVE_CUDA(cudaEventElapsedTime(&ms, pr.a, pr.b));
+        sum += ms;
+        cudaEventDestroy(pr.a);
+        cudaEventDestroy(pr.b);
+    }
+    if (total_ms) *total_ms = sum;
+    if (launches) *launches = uint32_t(ctx->prof[kernel].size());
+    ctx->prof[kernel].clear();
+    return 0;
+}
+
 void* rve_ctx_stream(rve_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
 int rve_ctx_sm_count(rve_ctx* ctx) { return ctx ? ctx->sm_count : 0; }
 uint64_t rve_ctx_launch_count(rve_ctx* ctx) { return ctx ? ctx->launches : 0; }

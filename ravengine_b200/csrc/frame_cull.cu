@@ -1,0 +1,148 @@
+// frame_cull.cu — cullTheRenderData (src/RenderEngine_Draw.cpp:1221-1407) and the clustered-light
+// prologue of renderFromPerspective (:928-974), restated over the rve_* C-ABI. Host C++ only.
+#include <cmath>
+#include <cstring>
+
+#include "frame_internal.h"
+#include "internal.h"
+
+using namespace rve;
+using namespace rvs;
+
+extern "C" {
+
+int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
+                    uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid) {
+    if (!w || !view_proj || !cam_pos) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    rve_ctx* ctx = w->ctx;
+    // :1223-1229
+    RveCullingUBO globalCubo{};
+    std::memcpy(globalCubo.viewProj, view_proj, 64);
+    std::memcpy(globalCubo.camPos, cam_pos, 12);
+    globalCubo.numCubos = 0;
+    globalCubo.cameraRenderLayers = camera_layers;
+    globalCubo.singleInstanceModeAndShadowMode = shadow_pass ? RVE_CULL_SHADOW_MODE : 0u;
+
+    // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch
+    uint32_t totalEntities = 0;
+    for (auto& m : w->materials) {
+        if (!(m.kind & pass_mask)) continue;
+        for (auto& c : m.commands) {
+            globalCubo.numCubos += uint32_t(w->meshes[c.mesh].lods.size());
+            totalEntities += c.count;
+        }
+    }
+    w->lastNumCubos = globalCubo.numCubos;
+    w->lastTotalEntities = totalEntities;
+    if (globalCubo.numCubos == 0) return 0;  // :1245-1247
+
+    // :1249-1251 cuboBuffer + staging (entries past the written ones are zero here; stale in the reference)
+    int rc = realloc_buffer(w, &w->cuboBuffer, &w->cuboBytes, globalCubo.numCubos, sizeof(RveCullingUBOinstance));
+    if (rc) return rc;
+    std::vector<RveCullingUBOinstance> cuboStaging(globalCubo.numCubos);
+    std::memset(cuboStaging.data(), 0, cuboStaging.size() * sizeof(RveCullingUBOinstance));
+
+    uint32_t cuboIdx = 0;
+    std::vector<RveIndirectIndexedCommand> indirectStaging;
+    for (auto& m : w->materials) {
+        if (!(m.kind & pass_mask)) continue;
+        // :1265-1286 prepass
+        uint32_t numLODs = 0, numEntities = 0;
+        for (auto& c : m.commands) {
+            numLODs += uint32_t(w->meshes[c.mesh].lods.size());
+            numEntities += c.count;
+        }
+        m.numLODs = numLODs;
+        m.numEntities = numEntities;
+        // :1288-1291
+        const size_t cullingbufferTotalSlots = size_t(numEntities) * numLODs;
+        RVE_REQUIRE(cullingbufferTotalSlots <= 0xFFFFFFFFull, "culling buffer exceeds 2^32 slots (u32 indices in the CUBO layout)");
+        rc = realloc_buffer(w, &m.cullingBuffer, &m.cullingBytes, cullingbufferTotalSlots, sizeof(uint32_t));
+        if (rc) return rc;
+        rc = realloc_buffer(w, &m.indirectBuffer, &m.indirectBytes, numLODs, sizeof(RveIndirectIndexedCommand));
+        if (rc) return rc;
+        if (numLODs == 0) continue;
+
+        // :1295-1320 initial populate of the drawcall buffer: one command per mesh per LOD
+        indirectStaging.assign(numLODs, RveIndirectIndexedCommand{0, 0, 0, 0, 0});
+        {
+            uint32_t meshID = 0, baseInstance = 0, lodBase = 0;
+            for (auto& c : m.commands) {
+                const MeshCollection& mesh = w->meshes[c.mesh];
+                for (uint32_t lodID = 0; lodID < mesh.lods.size(); lodID++) {
+                    const LODMesh& lm = mesh.lods[lodID];
+                    const RveIndirectIndexedCommand initData{lm.indexCount, 0, lm.indexStart, lm.baseVertex, baseInstance};
+                    baseInstance += c.count;
+                    // reference writes slot (meshID + lodID) (:1314); the shader reads cubo.indirectBufferOffset + lod
+                    const uint32_t slot = (w->flags & RVS_QUIRK_INDIRECT_SLOT) ? (meshID + lodID) : (lodBase + lodID);
+                    if (slot < numLODs) indirectStaging[slot] = initData;
+                }
+                lodBase += uint32_t(mesh.lods.size());
+                meshID++;
+            }
+        }
+        // :1321-1329 CopyBufferToBuffer(indirectStagingBuffer -> indirectBuffer)
+        rc = rve_buffer_upload(ctx, m.indirectBuffer, 0, indirectStaging.data(), numLODs * sizeof(RveIndirectIndexedCommand));
+        if (rc) return rc;
+
+        // :1334-1362 one CUBO per command; offsets restart per material
+        RveCullingUBOinstance cubo{};
+        cubo.indirectBufferOffset = 0;
+        for (auto& c : m.commands) {
+            const MeshCollection& mesh = w->meshes[c.mesh];
+            const uint32_t lodsForThisMesh = uint32_t(mesh.lods.size());
+            cubo.numObjects = c.count;
+            cubo.radius = mesh.radius;
+            cubo.numLODs = lodsForThisMesh;
+            cubo.idOutputBufferBindlessHandle = rve_buffer_bindless_index(ctx, m.cullingBuffer);
+            cubo.indirectOutputBufferBindlessHandle = rve_buffer_bindless_index(ctx, m.indirectBuffer);
+            cubo.lodDistanceBufferBindlessHandle = rve_buffer_bindless_index(ctx, mesh.lodDistances);
+            cubo.entityIDInputBufferBindlessHandle = rve_buffer_bindless_index(ctx, c.entityIds);
+            cuboStaging[cuboIdx++] = cubo;
+            cubo.indirectBufferOffset += lodsForThisMesh;
+            cubo.cullingBufferOffset += lodsForThisMesh * c.count;
+        }
+    }
+    // :1367-1375 copy to the cubo buffer
+    rc = rve_buffer_upload(ctx, w->cuboBuffer, 0, cuboStaging.data(), cuboStaging.size() * sizeof(RveCullingUBOinstance));
+    if (rc) return rc;
+    // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
+    const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));
+    return rve_cull(ctx, &globalCubo, w->cuboBuffer, w->model, w->layers, w->flagsBuf, pyramid, groups);
+}
+
+int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[16], const uint32_t grid_size[3],
+                   const uint32_t screen_dim[2], float z_near, float z_far, rve_buffer point_lights,
+                   uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count,
+                   rve_buffer* out_cluster_buffer) {
+    if (!w || !inv_proj || !view_mat || !grid_size || !screen_dim) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    const uint64_t n = uint64_t(grid_size[0]) * grid_size[1] * grid_size[2];
+    RVE_REQUIRE(n > 0 && n < 0x7FFFFFFFull, "bad cluster grid");
+    // lightClusterBuffer: numClusters * sizeof(Cluster) (src/RenderEngine.cpp:839-845)
+    if (w->clusterBytes != n * sizeof(RveCluster)) {
+        int rc = realloc_buffer(w, &w->clusterBuffer, &w->clusterBytes, n, sizeof(RveCluster));
+        if (rc) return rc;
+    }
+    if (out_cluster_buffer) *out_cluster_buffer = w->clusterBuffer;
+    // :930 — only when there is at least one point or spot light
+    if (point_light_count == 0 && spot_light_count == 0) return 0;
+    // :935-950 build the grid
+    RveGridBuildUBO g{};
+    std::memcpy(g.invProj, inv_proj, 64);
+    std::memcpy(g.gridSize, grid_size, 12);
+    g.zNear = z_near;
+    g.screenDim[0] = screen_dim[0];
+    g.screenDim[1] = screen_dim[1];
+    g.zFar = z_far;
+    int rc = rve_cluster_build(w->ctx, &g, w->clusterBuffer);
+    if (rc) return rc;
+    // :953-970 assign lights; the reference dispatches numClusters/128 groups of 128
+    RveGridAssignUBO a{};
+    std::memcpy(a.viewMat, view_mat, 64);
+    a.pointLightCount = point_light_count;
+    a.spotLightCount = spot_light_count;
+    const uint32_t invocations = uint32_t(n / 128) * 128;
+    return rve_cluster_assign(w->ctx, &a, w->clusterBuffer, point_lights, spot_lights, invocations);
+}
+
+}  // extern "C"

@@ -34,6 +34,12 @@ struct rve_ctx {
     int sm_count = 0;
     uint64_t launches = 0;
 
+    bool profiling = false;
+    struct ProfPair {
+        cudaEvent_t a, b;
+    };
+    std::vector<ProfPair> prof[4];
+
     std::mutex mu;  // guards the tables (destroy may come from another thread)
     std::vector<rve::BufferRec> buffers;
     std::vector<uint32_t> free_slots;
@@ -65,6 +71,24 @@ PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h);
 // makes sure the device pointer table reflects the host table (enqueued on the stream)
 int sync_table(rve_ctx* ctx);
 int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes);
+
+// RAII: brackets a kernel launch with events when ctx->profiling
+struct ProfScope {
+    rve_ctx* ctx;
+    int tag;
+    cudaEvent_t b = nullptr;
+    ProfScope(rve_ctx* c, int t) : ctx(c), tag(t) {
+        if (!ctx->profiling) return;
+        cudaEvent_t a;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, ctx->stream);
+        ctx->prof[tag].push_back({a, b});
+    }
+    ~ProfScope() {
+        if (b) cudaEventRecord(b, ctx->stream);
+    }
+};
 
 struct DeviceGuard {
     int prev = -1;

@@ -187,9 +187,12 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     if (!t || !c) return RVE_ERR_BAD_HANDLE;
     const uint32_t tile = p->dim < uint32_t(kPyrTile) ? p->dim : uint32_t(kPyrTile);
     const uint32_t blocks = (p->dim / tile) * (p->dim / tile);
-    pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height,
-                                                                  static_cast<float*>(t->ptr), p->dim, p->levels, tile,
-                                                                  static_cast<uint32_t*>(c->ptr));
+    {
+        ProfScope prof(ctx, RVE_PROF_PYRAMID);
+        pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height,
+                                                                      static_cast<float*>(t->ptr), p->dim, p->levels, tile,
+                                                                      static_cast<uint32_t*>(c->ptr));
+    }
     ctx->launches++;
     RVE_CUDA(cudaGetLastError());
     return 0;

@@ -212,6 +212,7 @@ int rve_skin(rve_ctx* ctx, const RveSkinningUBO* ubo, const rve_buffer out_strea
     p.vertsPerCta = vertsPerCta;
     dim3 grid((ubo->numVertices + vertsPerCta - 1) / vertsPerCta, (ubo->numObjects + group - 1) / group);
     RVE_REQUIRE(grid.y <= 65535, "too many object groups for one dispatch (numObjects/8 > 65535)");
+    ProfScope prof(ctx, RVE_PROF_SKIN);
     if (shared) {
         const size_t smem = palBytes * group;
         if (smem > 48 * 1024)
