@@ -20,9 +20,22 @@ LIB_TF = HERE / "_ref" / "liboracle_tf.so"
 VP, u32, u64, f32 = C.c_void_p, C.c_uint32, C.c_uint64, C.c_float
 
 
+def _cpu_has_fma() -> bool:
+    try:
+        return " fma " in Path("/proc/cpuinfo").read_text()
+    except OSError:
+        return False
+
+
 def build(force: bool = False) -> None:
-    if force or not LIB.exists() or LIB.stat().st_mtime < (HERE / "oracle.cpp").stat().st_mtime:
+    stale = not LIB.exists() or LIB.stat().st_mtime < max((HERE / f).stat().st_mtime for f in ("oracle.cpp", "oracle.h", "Makefile"))
+    if force or stale:
         subprocess.run(["make", "-C", str(HERE)], check=True, capture_output=True)
+    if not _cpu_has_fma():  # a prebuilt -mfma library would fault here: rebuild with libm's fmaf (same bits)
+        marker = HERE / ".nofma_built"
+        if not marker.exists():
+            subprocess.run(["make", "-C", str(HERE), "-B", "FMA="], check=True, capture_output=True)
+            marker.write_text("built without -mfma\n")
 
 
 _libs: dict[bool, C.CDLL] = {}

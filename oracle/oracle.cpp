@@ -9,14 +9,30 @@
  * Matrix Operations"):
  *   min(x,y)  = y < x ? y : x          max(x,y) = x < y ? y : x
  *   clamp(x,a,b) = min(max(x,a),b)
- *   dot(a,b)  = ((a.x*b.x + a.y*b.y) + a.z*b.z) [+ a.w*b.w]   (left to right)
- *   length(v) = sqrt(dot(v,v))
- *   mat*vec   = ((col0*v.x + col1*v.y) + col2*v.z) [+ col3*v.w]
- * The evaluation ORDER of dot / mat*vec is not fixed by GLSL; the order above
- * is our definition, used identically by the CUDA kernels. Build with
- * -ffp-contract=off so no multiply-add is fused.
  *
- * Two definitional choices where the reference's result depends on GPU
+ * ARITHMETIC CONTRACT (shared bit for bit with the CUDA kernels; DESIGN.md
+ * "Arithmetic contract"). GLSL fixes neither the evaluation order of dot /
+ * mat*vec nor whether a*b+c is fused (no `precise` qualifier in the shaders,
+ * no NoContraction in the SPIR-V), and Vulkan only asks 2.5 ULP of a division,
+ * so every GPU the reference runs on contracts to FMA and divides by
+ * reciprocal-multiply. This restatement pins ONE such evaluation, the one a
+ * shader compiler emits, with explicit fused multiply-adds:
+ *   dot(a,b)  = fma(a.w,b.w, fma(a.z,b.z, fma(a.y,b.y, a.x*b.x)))   (x first)
+ *   length(v) = sqrt(dot(v,v))                       (correctly rounded sqrt)
+ *   mat*vec   = t=col0*v.x; t=fma(col1,v.y,t); t=fma(col2,v.z,t); t=fma(col3,v.w,t)
+ *   v / s     = v * (1/s) for a vector v and scalar s (1/s correctly rounded)
+ *   a*b + c   = fma(a,b,c) where the shader writes exactly that shape
+ *               (u*W - 0.5 in the sampler, total += w*M in skinning)
+ * Nothing else is fused: build with -ffp-contract=off so the compiler adds no
+ * contraction of its own; fma() is the C99 correctly-rounded one (hardware
+ * FMA3 when built with -mfma, libm otherwise - same bits either way).
+ * Products with a literal 0/1 vector component are folded to their exact
+ * value: (model*vec4(0,0,0,1)).xyz == model[3].xyz and
+ * mat3(model)*vec3(0,0,r) == model[2].xyz*r (equal up to the sign of zero for
+ * finite matrices; the sign of a zero never reaches a comparison).
+ * Parity is claimed for inputs that produce no NaN.
+ *
+ * Two further definitional choices where the reference's result depends on GPU
  * hardware (SURVEY.md 7 "hard parts" 1-2), both documented in DESIGN.md:
  *   - ceil(log2(x)) (defaultcull.csh:231) is evaluated exactly from the float
  *     exponent (no libm);
@@ -59,9 +75,16 @@ inline vec3 operator-(vec3 a, vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}
 inline vec3 operator*(vec3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
 inline vec4 operator*(vec4 a, float s) { return {a.x * s, a.y * s, a.z * s, a.w * s}; }
 inline vec4 operator+(vec4 a, vec4 b) { return {a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w}; }
-inline float dot(vec3 a, vec3 b) { return (a.x * b.x + a.y * b.y) + a.z * b.z; }
-inline float dot(vec4 a, vec4 b) { return ((a.x * b.x + a.y * b.y) + a.z * b.z) + a.w * b.w; }
+inline float fma_(float a, float b, float c) { return __builtin_fmaf(a, b, c); }
+inline float rcp_(float s) { return 1.0f / s; }
+inline float dot(vec3 a, vec3 b) { return fma_(a.z, b.z, fma_(a.y, b.y, a.x * b.x)); }
+inline float dot(vec4 a, vec4 b) { return fma_(a.w, b.w, fma_(a.z, b.z, fma_(a.y, b.y, a.x * b.x))); }
 inline float length(vec3 v) { return std::sqrt(dot(v, v)); }
+inline vec3 fma3(vec3 a, float s, vec3 c) { return {fma_(a.x, s, c.x), fma_(a.y, s, c.y), fma_(a.z, s, c.z)}; }
+inline vec4 fma4(vec4 a, float s, vec4 c) { return {fma_(a.x, s, c.x), fma_(a.y, s, c.y), fma_(a.z, s, c.z), fma_(a.w, s, c.w)}; }
+// vector / scalar = vector * (1/scalar)
+inline vec3 vdiv(vec3 v, float s) { return v * rcp_(s); }
+inline vec4 vdiv(vec4 v, float s) { return v * rcp_(s); }
 inline vec3 vmin(vec3 a, vec3 b) { return {gmin(a.x, b.x), gmin(a.y, b.y), gmin(a.z, b.z)}; }
 inline vec3 vmax(vec3 a, vec3 b) { return {gmax(a.x, b.x), gmax(a.y, b.y), gmax(a.z, b.z)}; }
 
@@ -77,10 +100,10 @@ inline mat4 load_mat4(const float* p) {
     return r;
 }
 inline vec4 mul(const mat4& M, vec4 v) {
-    return ((M.col(0) * v.x + M.col(1) * v.y) + M.col(2) * v.z) + M.col(3) * v.w;
+    return fma4(M.col(3), v.w, fma4(M.col(2), v.z, fma4(M.col(1), v.y, M.col(0) * v.x)));
 }
 // mat3(M) * v
-inline vec3 mul3(const mat4& M, vec3 v) { return (M.col3(0) * v.x + M.col3(1) * v.y) + M.col3(2) * v.z; }
+inline vec3 mul3(const mat4& M, vec3 v) { return fma3(M.col3(2), v.z, fma3(M.col3(1), v.y, M.col3(0) * v.x)); }
 
 // ---- parallel-for over chunks ------------------------------------------------
 void parallel_chunks(uint64_t num_chunks, int nthreads, const std::function<void(uint64_t)>& fn) {
@@ -142,8 +165,8 @@ inline void footprint(float x, uint32_t n, uint32_t& i0, uint32_t& i1) {
 }
 
 inline float sample_min(const float* img, uint32_t w, uint32_t h, float u, float v) {
-    const float x = u * float(w) - 0.5f;
-    const float y = v * float(h) - 0.5f;
+    const float x = fma_(u, float(w), -0.5f);
+    const float y = fma_(v, float(h), -0.5f);
     uint32_t x0, x1, y0, y1;
     footprint(x, w, x0, x1);
     footprint(y, h, y0, y1);
@@ -183,8 +206,7 @@ ClipBoundingBoxResult projectWorldSpaceSphere(vec3 center, float r, const mat4& 
     ClipBoundingBoxResult result{1, 0, 1, 0, 0};
     for (int i = 0; i < 8; i++) {
         vec4 p = mul(viewProj, vec4{boxCorners[i].x, boxCorners[i].y, boxCorners[i].z, 1.0f});
-        const float w = p.w;
-        p = {p.x / w, p.y / w, p.z / w, p.w / w};
+        p = vdiv(p, p.w);  // projected /= projected.w
         result.minX = gmin(p.x, result.minX);
         result.maxX = gmax(p.x, result.maxX);
         result.minY = gmin(p.y, result.minY);
@@ -206,7 +228,7 @@ void MakeFrustumPlanes(const mat4& vp, vec4 planes[6]) {
     for (int i = 0; i < 4; ++i) p[5][i] = M(i, 3) - M(i, 2);
     for (int i = 0; i < 6; ++i) {
         const float len = length(vec3{planes[i].x, planes[i].y, planes[i].z});
-        planes[i] = {planes[i].x / len, planes[i].y / len, planes[i].z / len, planes[i].w / len};
+        planes[i] = vdiv(planes[i], len);
     }
 }
 
@@ -269,14 +291,12 @@ void cull_invocation(const CullArgs& a, uint32_t gid) {
     vec4 planes[6];
     MakeFrustumPlanes(viewProj, planes);
 
-    vec3 radvecs[3] = {{0, 0, cubo.radius}, {0, cubo.radius, 0}, {cubo.radius, 0, 0}};
+    // modelNoTranslate * vec3(0,0,r) etc. folded to column * r, (model * vec4(0,0,0,1)).xyz to
+    // column 3 (exact values of those products, see the arithmetic contract above)
+    vec3 radvecs[3] = {model.col3(2) * cubo.radius, model.col3(1) * cubo.radius, model.col3(0) * cubo.radius};
     float radius = 0;
-    for (int i = 0; i < 3; i++) {
-        radvecs[i] = mul3(model, radvecs[i]);
-        radius = gmax(radius, length(radvecs[i]));
-    }
-    const vec4 c4 = mul(model, vec4{0, 0, 0, 1});
-    const vec3 center{c4.x, c4.y, c4.z};
+    for (int i = 0; i < 3; i++) radius = gmax(radius, length(radvecs[i]));
+    const vec3 center = model.col3(3);
 
     bool isOnCamera = skipFrustumCulling ? true : (CullSphere(planes, center, radius) > 0);
 
@@ -430,7 +450,7 @@ void orc_skin(const RveSkinningUBO* ubo, float* out_pos, float* out_nrm, float* 
                 const uint32_t joint_idx = wv.weights[i].joint_index;
                 const float weight = wv.weights[i].influence;
                 const float* posed = pose + uint64_t(bone_begin + joint_idx) * 16;
-                for (int k = 0; k < 16; ++k) total[k] += weight * posed[k];
+                for (int k = 0; k < 16; ++k) total[k] = fma_(weight, posed[k], total[k]);  // totalmtx += weight * posed_mtx
             }
             const mat4 M = load_mat4(total);
             const uint64_t writeOffset = uint64_t(vertID) + uint64_t(objID) * u.numVertices + u.vertexWriteOffset;
@@ -494,8 +514,7 @@ void orc_cluster_build(const RveGridBuildUBO* ubo_p, RveCluster* clusters) {
     auto screenToView = [&](float sx, float sy) -> vec3 {
         const vec4 ndc{sx / float(ubo.screenDim[0]) * 2.0f - 1.0f, sy / float(ubo.screenDim[1]) * 2.0f - 1.0f, 0.0f, 1.0f};
         vec4 v = mul(invProj, ndc);
-        const float w = v.w;
-        v = {v.x / w, v.y / w, v.z / w, v.w / w};
+        v = vdiv(v, v.w);  // view / view.w
         return {v.x, v.y, v.z};
     };
     // cluster_build_grid.csh:29-38
@@ -503,7 +522,7 @@ void orc_cluster_build(const RveGridBuildUBO* ubo_p, RveCluster* clusters) {
         const vec3 direction = endPoint - startPoint;
         const vec3 normal{0.0f, 0.0f, -1.0f};
         const float t = (zDistance - dot(normal, startPoint)) / dot(normal, direction);
-        return startPoint + direction * t;
+        return fma3(direction, t, startPoint);  // startPoint + t * direction
     };
     const vec3 eyePos{0, 0, 0};
     for (uint32_t gz = 0; gz < ubo.gridSize[2]; ++gz)
@@ -567,7 +586,7 @@ void orc_cluster_assign(const RveGridAssignUBO* ubo_p, RveCluster* clusters, con
             }
             for (uint32_t i = 0; i < ubo.spotLightCount; ++i) {
                 const mat4 wt = load_mat4(spots[i].worldTransform);
-                const vec4 wpos = mul(wt, vec4{0, 0, 0, 1});
+                const vec3 wpos = wt.col3(3);  // (worldTransform * vec4(0,0,0,1)).xyz, folded (arithmetic contract)
                 const vec4 c4 = mul(viewMatrix, vec4{wpos.x, wpos.y, wpos.z, 1.0f});
                 const float radius = getPointLightRadius(spots[i].intensity);
                 // the shader has no capacity check here (cluster_assign_lights.csh:80-83; writes

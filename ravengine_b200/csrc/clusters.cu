@@ -33,14 +33,16 @@ __global__ void cluster_build_kernel(const RveGridBuildUBO u, const float* __res
     auto screenToView = [&](float sx, float sy, float& vx, float& vy, float& vz) {
         const float nx = sx / float(u.screenDim[0]) * 2.0f - 1.0f;
         const float ny = sy / float(u.screenDim[1]) * 2.0f - 1.0f;
-        // ((col0*nx + col1*ny) + col2*0) + col3*1
+        // mat*vec of the arithmetic contract: t = col0*nx; fma(col1,ny,t); fma(col2,0,t); fma(col3,1,t)
         float v[4];
 #pragma unroll
         for (int r = 0; r < 4; ++r)
-            v[r] = ((u.invProj[0 + r] * nx + u.invProj[4 + r] * ny) + u.invProj[8 + r] * 0.0f) + u.invProj[12 + r] * 1.0f;
-        vx = v[0] / v[3];
-        vy = v[1] / v[3];
-        vz = v[2] / v[3];
+            v[r] = __fmaf_rn(u.invProj[12 + r], 1.0f,
+                             __fmaf_rn(u.invProj[8 + r], 0.0f, __fmaf_rn(u.invProj[4 + r], ny, u.invProj[0 + r] * nx)));
+        const float iw = __frcp_rn(v[3]);  // viewCoord /= viewCoord.w == viewCoord * (1/w)
+        vx = v[0] * iw;
+        vy = v[1] * iw;
+        vz = v[2] * iw;
     };
     float mnx, mny, mnz, mxx, mxy, mxz;
     screenToView(float(gx) * tileSizeX, float(gy) * tileSizeY, mnx, mny, mnz);
@@ -51,12 +53,12 @@ __global__ void cluster_build_kernel(const RveGridBuildUBO u, const float* __res
     //   t = (zDistance - dot(normal, 0)) / dot(normal, direction);  result = 0 + t*direction
     auto isect = [](float ex, float ey, float ez, float zDistance, float& ox, float& oy, float& oz) {
         const float dx = ex - 0.0f, dy = ey - 0.0f, dz = ez - 0.0f;
-        const float dotNS = (0.0f * 0.0f + 0.0f * 0.0f) + (-1.0f) * 0.0f;
-        const float dotND = (0.0f * dx + 0.0f * dy) + (-1.0f) * dz;
+        const float dotNS = __fmaf_rn(-1.0f, 0.0f, __fmaf_rn(0.0f, 0.0f, 0.0f * 0.0f));
+        const float dotND = __fmaf_rn(-1.0f, dz, __fmaf_rn(0.0f, dy, 0.0f * dx));
         const float t = (zDistance - dotNS) / dotND;
-        ox = 0.0f + dx * t;
-        oy = 0.0f + dy * t;
-        oz = 0.0f + dz * t;
+        ox = __fmaf_rn(dx, t, 0.0f);  // startPoint + t * direction
+        oy = __fmaf_rn(dy, t, 0.0f);
+        oz = __fmaf_rn(dz, t, 0.0f);
     };
     float a[3], b[3], c[3], d[3];
     isect(mnx, mny, mnz, tileNear, a[0], a[1], a[2]);  // minPointNear
@@ -66,8 +68,9 @@ __global__ void cluster_build_kernel(const RveGridBuildUBO u, const float* __res
     RveCluster* cl = clusters + tileIndex;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        cl->minPoint[k] = gmin(a[k], b[k]);
-        cl->maxPoint[k] = gmax(c[k], d[k]);
+        // GLSL min/max spelled out: these floats are compared byte for byte (sign of zero included)
+        cl->minPoint[k] = (b[k] < a[k]) ? b[k] : a[k];
+        cl->maxPoint[k] = (c[k] < d[k]) ? d[k] : c[k];
     }
 }
 
@@ -80,17 +83,13 @@ __global__ void light_prepare_kernel(const unsigned char* __restrict__ lights, u
     const unsigned char* L = lights + uint64_t(i) * stride;
     const float* pp = reinterpret_cast<const float*>(L + posOffset);
     float px = __ldg(pp), py = __ldg(pp + 1), pz = __ldg(pp + 2);
-    if (originFromMatrix) {  // (worldTransform * vec4(0,0,0,1)).xyz: 0 + col3
-        px = 0.0f + px;
-        py = 0.0f + py;
-        pz = 0.0f + pz;
-    }
+    (void)originFromMatrix;  // (worldTransform * vec4(0,0,0,1)).xyz is column 3 itself (arithmetic contract)
     const float intensity = __ldg(reinterpret_cast<const float*>(L + intensityOffset));
     const float* m = u.viewMat;
     float4 r;
-    r.x = ((m[0] * px + m[4] * py) + m[8] * pz) + m[12] * 1.0f;
-    r.y = ((m[1] * px + m[5] * py) + m[9] * pz) + m[13] * 1.0f;
-    r.z = ((m[2] * px + m[6] * py) + m[10] * pz) + m[14] * 1.0f;
+    r.x = __fmaf_rn(m[12], 1.0f, __fmaf_rn(m[8], pz, __fmaf_rn(m[4], py, m[0] * px)));
+    r.y = __fmaf_rn(m[13], 1.0f, __fmaf_rn(m[9], pz, __fmaf_rn(m[5], py, m[1] * px)));
+    r.z = __fmaf_rn(m[14], 1.0f, __fmaf_rn(m[10], pz, __fmaf_rn(m[6], py, m[2] * px)));
     const float radius = sqrtf(intensity / RVE_LIGHT_MIN_INFLUENCE);  // cluster_shared.glsl:41-44
     r.w = radius * radius;
     out[i] = r;
@@ -133,7 +132,7 @@ cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, c
                         const float qx = gmin(gmax(L.x, mn[0]), mx[0]) - L.x;
                         const float qy = gmin(gmax(L.y, mn[1]), mx[1]) - L.y;
                         const float qz = gmin(gmax(L.z, mn[2]), mx[2]) - L.z;
-                        hit = ((qx * qx + qy * qy) + qz * qz) <= L.w;
+                        hit = dot3(qx, qy, qz, qx, qy, qz) <= L.w;
                     }
                     const uint32_t ballot = __ballot_sync(0xffffffffu, hit);
                     if (hit) {

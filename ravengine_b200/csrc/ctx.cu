@@ -142,6 +142,7 @@ int rve_ctx_destroy(rve_ctx* ctx) {
         if (b.live && b.owned && b.ptr) cudaFree(b.ptr);
     if (ctx->d_table) cudaFree(ctx->d_table);
     if (ctx->d_cubo_start) cudaFree(ctx->d_cubo_start);
+    if (ctx->d_cubo_res) cudaFree(ctx->d_cubo_res);
     if (ctx->d_lights) cudaFree(ctx->d_lights);
     if (ctx->d_slices) cudaFree(ctx->d_slices);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);

@@ -53,6 +53,9 @@ struct rve_ctx {
     // scratch: cubo prefix sums for rve_cull (grown on demand)
     uint32_t* d_cubo_start = nullptr;
     size_t d_cubo_start_cap = 0;
+    void* d_cubo_res = nullptr;  // resolved CUBO records (cull.cu CuboRes)
+    size_t d_cubo_res_cap = 0;
+    int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
     // scratch: view-space light records for rve_cluster_assign
     float4* d_lights = nullptr;
     size_t d_lights_cap = 0;
@@ -113,10 +116,17 @@ struct DeviceGuard {
         if (!(cond)) return rve::set_error(RVE_ERR_INVALID_ARGUMENT, "%s", msg); \
     } while (0)
 
-// ---- device helpers: GLSL min/max semantics (see oracle.cpp header) ----
+// ---- device helpers ----
+// Arithmetic contract shared with oracle/oracle.cpp (see its header and DESIGN.md): the library is
+// compiled with -fmad=false so ptxas never fuses on its own; every fused multiply-add is an
+// explicit __fmaf_rn in the same place the oracle has one. min/max: the oracle states GLSL's
+// (y<x?y:x); fminf/fmaxf (one FMNMX) give the same value for every non-NaN input.
 #ifdef __CUDACC__
-__device__ __forceinline__ float gmin(float x, float y) { return (y < x) ? y : x; }
-__device__ __forceinline__ float gmax(float x, float y) { return (x < y) ? y : x; }
+__device__ __forceinline__ float gmin(float x, float y) { return fminf(x, y); }
+__device__ __forceinline__ float gmax(float x, float y) { return fmaxf(x, y); }
+__device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, float by, float bz) {
+    return __fmaf_rn(az, bz, __fmaf_rn(ay, by, ax * bx));
+}
 
 // 128-bit read-only load that does not allocate in L1 (streamed once)
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {

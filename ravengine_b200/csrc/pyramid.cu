@@ -29,8 +29,8 @@ __device__ __forceinline__ void footprint(float x, uint32_t n, uint32_t& i0, uin
 }
 
 __device__ __forceinline__ float sample_min_src(const float* __restrict__ img, uint32_t w, uint32_t h, float u, float v) {
-    const float x = u * float(w) - 0.5f;
-    const float y = v * float(h) - 0.5f;
+    const float x = __fmaf_rn(u, float(w), -0.5f);  // arithmetic contract: u*W - 0.5 is one fma
+    const float y = __fmaf_rn(v, float(h), -0.5f);
     uint32_t x0, x1, y0, y1;
     footprint(x, w, x0, x1);
     footprint(y, h, y0, y1);

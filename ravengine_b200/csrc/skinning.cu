@@ -52,9 +52,9 @@ struct Blend {
     float4 r0, r1, r2;
 };
 
-__device__ __forceinline__ float4 fma4_noncontracted(float4 acc, float w, float4 m) {
-    // totalmtx += weight * posed_mtx (skinning_cs.csh:115), component-wise, mul then add
-    return make_float4(acc.x + w * m.x, acc.y + w * m.y, acc.z + w * m.z, acc.w + w * m.w);
+__device__ __forceinline__ float4 fma4(float4 acc, float w, float4 m) {
+    // totalmtx += weight * posed_mtx (skinning_cs.csh:115): one fma per component (arithmetic contract)
+    return make_float4(__fmaf_rn(w, m.x, acc.x), __fmaf_rn(w, m.y, acc.y), __fmaf_rn(w, m.z, acc.z), __fmaf_rn(w, m.w, acc.w));
 }
 
 template <bool kSharedPalette>
@@ -115,20 +115,20 @@ __global__ void __launch_bounds__(kSkinThreads) skin_kernel(const SkinParams p) 
                     b = make_float4(c0.y, c1.y, c2.y, c3.y);
                     c = make_float4(c0.z, c1.z, c2.z, c3.z);
                 }
-                M.r0 = fma4_noncontracted(M.r0, ws[i], a);
-                M.r1 = fma4_noncontracted(M.r1, ws[i], b);
-                M.r2 = fma4_noncontracted(M.r2, ws[i], c);
+                M.r0 = fma4(M.r0, ws[i], a);
+                M.r1 = fma4(M.r1, ws[i], b);
+                M.r2 = fma4(M.r2, ws[i], c);
             }
             const uint64_t writeOffset = uint64_t(vertID) + uint64_t(obj0 + o) * p.u.numVertices + p.u.vertexWriteOffset;
-            // (totalmtx * vec4(pos,1)).xyz = ((col0*x + col1*y) + col2*z) + col3
+            // (totalmtx * vec4(pos,1)).xyz: t = col0*x; fma(col1,y,t); fma(col2,z,t); fma(col3,1,t) = t + col3
             Vec3 op;
-            op.x = ((M.r0.x * pos.x + M.r0.y * pos.y) + M.r0.z * pos.z) + M.r0.w;
-            op.y = ((M.r1.x * pos.x + M.r1.y * pos.y) + M.r1.z * pos.z) + M.r1.w;
-            op.z = ((M.r2.x * pos.x + M.r2.y * pos.y) + M.r2.z * pos.z) + M.r2.w;
+            op.x = dot3(pos.x, pos.y, pos.z, M.r0.x, M.r0.y, M.r0.z) + M.r0.w;
+            op.y = dot3(pos.x, pos.y, pos.z, M.r1.x, M.r1.y, M.r1.z) + M.r1.w;
+            op.z = dot3(pos.x, pos.y, pos.z, M.r2.x, M.r2.y, M.r2.z) + M.r2.w;
             st3(p.outPos, writeOffset, op);
             auto rot = [&](Vec3 v) -> Vec3 {
-                return {(M.r0.x * v.x + M.r0.y * v.y) + M.r0.z * v.z, (M.r1.x * v.x + M.r1.y * v.y) + M.r1.z * v.z,
-                        (M.r2.x * v.x + M.r2.y * v.y) + M.r2.z * v.z};
+                return {dot3(v.x, v.y, v.z, M.r0.x, M.r0.y, M.r0.z), dot3(v.x, v.y, v.z, M.r1.x, M.r1.y, M.r1.z),
+                        dot3(v.x, v.y, v.z, M.r2.x, M.r2.y, M.r2.z)};
             };
             st3(p.outNrm, writeOffset, rot(nrm));
             st3(p.outTan, writeOffset, rot(tan));
