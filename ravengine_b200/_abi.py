@@ -8,7 +8,10 @@ from __future__ import annotations
 import ctypes as C
 from pathlib import Path
 
-LIB_PATH = Path(__file__).resolve().parent / "librve_b200.so"
+import os
+
+# RVE_B200_LIB selects a tuning variant built with `python -m ravengine_b200.build -D... path.so` (development only)
+LIB_PATH = Path(os.environ.get("RVE_B200_LIB") or Path(__file__).resolve().parent / "librve_b200.so")
 
 u32, u64, f32, i32 = C.c_uint32, C.c_uint64, C.c_float, C.c_int32
 

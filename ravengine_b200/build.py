@@ -37,20 +37,23 @@ def needs_build() -> bool:
     return any(d.exists() and d.stat().st_mtime > t for d in deps)
 
 
-def build_native(force: bool = False, verbose: bool = False) -> Path:
-    if not force and not needs_build():
+def build_native(force: bool = False, verbose: bool = False, out: Path | None = None, defines: list[str] | None = None) -> Path:
+    """`out` / `defines` build a tuning variant (e.g. -DRVE_CULL_STAGES=2) beside the product library."""
+    if out is None and not force and not needs_build():
         return LIB
+    out = out or LIB
     srcs = [str(CSRC / s) for s in SOURCES if (CSRC / s).exists()]
-    cmd = [nvcc_path(), *NVCC_FLAGS, *(["-Xptxas", "-v"] if verbose else []), "-o", str(LIB), *srcs]
+    cmd = [nvcc_path(), *NVCC_FLAGS, *(defines or []), *(["-Xptxas", "-v"] if verbose else []), "-o", str(out), *srcs]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("nvcc failed building librve_b200.so")
     if verbose:
         print(r.stdout + r.stderr)
-    return LIB
+    return out
 
 
 if __name__ == "__main__":
-    build_native(force=True, verbose="-v" in sys.argv)
-    print(LIB)
+    defs = [a for a in sys.argv[1:] if a.startswith("-D")]
+    outs = [a for a in sys.argv[1:] if a.endswith(".so")]
+    print(build_native(force=True, verbose="-v" in sys.argv, out=Path(outs[0]).resolve() if outs else None, defines=defs))
