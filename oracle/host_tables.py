@@ -91,3 +91,84 @@ def sorted_slices(indirect: np.ndarray, culling: np.ndarray, cubos: np.ndarray, 
             start = int(cb["numObjects"]) * lod + int(cb["cullingBufferOffset"])
             out.append(np.sort(culling[start:start + cnt]))
     return out
+
+
+# ---- skinned path (src/RenderEngine_Draw.cpp:546-574, 577-630, 1067-1218) --------------------------------------
+@dataclass
+class SkinnedMeshDesc:
+    num_verts: int
+    num_indices: int
+    index_start: int
+    vertex_start: int
+    radius: float
+
+
+@dataclass
+class SkinnedCommandDesc:
+    mesh: SkinnedMeshDesc
+    num_bones: int
+    entity_ids: np.ndarray
+
+
+@dataclass
+class SkinnedTables:
+    cubos: list  # per material: CUBO_DTYPE[numCommands]
+    dispatch_groups: list  # per material: ceil(LAST command's numObjects / 64)  (:1214)
+    indirect_reset: list  # per material: (total_entities, 5) u32 staging table (:1081-1123)
+    prepare_ubos: list  # per material: list of SkinningPrepareUBO field tuples, one per command (:552-570)
+    skinning_ubos: list  # flat over all materials/commands: SkinningUBO field tuples (:597-625)
+    bindless: list
+
+
+def build_skinned_tables(materials) -> SkinnedTables:
+    """materials: list[list[SkinnedCommandDesc]]. Handle numbering: per material culling, indirect; then per
+    command its id list; one shared +inf lodDistance buffer per mesh object."""
+    bindless: list = []
+
+    def handle(arr):
+        bindless.append(arr)
+        return len(bindless) - 1
+
+    cubos_all, groups, resets, prep_all, skin_all = [], [], [], [], []
+    skeletal_vertex_offset = 0  # runs across materials (:1070)
+    bone_read, vert_write = 0, 0  # SkinningUBO offsets run across all commands (:585, 623-624)
+    lod_handles: dict[int, int] = {}
+    for cmds in materials:
+        total = sum(len(c.entity_ids) for c in cmds)
+        reset = np.zeros((total, 5), np.uint32)
+        for c in cmds:
+            mesh_id = 0  # declared inside the per-command loop (:1088): every command starts at slot 0
+            for i in range(len(c.entity_ids)):
+                slot = mesh_id * 1 + 0 + i
+                if slot < total:
+                    reset[slot] = (c.mesh.num_indices, 0, c.mesh.index_start, skeletal_vertex_offset & 0xFFFFFFFF, i)
+                skeletal_vertex_offset += c.mesh.num_verts
+        culling = np.full(max(total, 1), 0xFFFFFFFF, np.uint32)
+        h_cull, h_ind = handle(culling), handle(reset.copy())
+        cubos = np.zeros(len(cmds), dtype=CUBO_DTYPE)
+        ind_off = cull_off = 0
+        last_n = 0
+        prep = []
+        vb_off = dc_off = bi_off = 0  # SkinningPrepareUBO is fresh per material (:551)
+        for k, c in enumerate(cmds):
+            n = len(c.entity_ids)
+            key = id(c.mesh)
+            if key not in lod_handles:
+                lod_handles[key] = handle(np.array([np.inf], np.float32))
+            ids = np.ascontiguousarray(c.entity_ids, dtype=np.uint32)
+            cubos[k] = (ind_off, n, cull_off, np.float32(c.mesh.radius), 1, h_cull, handle(ids), h_ind, lod_handles[key])
+            ind_off += 1
+            cull_off += n
+            last_n = n
+            prep.append((c.mesh.index_start, vb_off, c.mesh.num_indices, c.mesh.num_verts, n, dc_off, bi_off))
+            vb_off += c.mesh.num_verts
+            dc_off += n
+            bi_off += n
+            skin_all.append((n, c.mesh.num_verts, c.num_bones, bone_read, vert_write, c.mesh.vertex_start))
+            bone_read += c.num_bones * n
+            vert_write += c.mesh.num_verts * n
+        cubos_all.append(cubos)
+        groups.append(int(np.ceil(np.float32(last_n) / np.float32(64.0))))
+        resets.append(reset)
+        prep_all.append(prep)
+    return SkinnedTables(cubos_all, groups, resets, prep_all, skin_all, bindless)
