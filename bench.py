@@ -157,37 +157,6 @@ class DeviceScene:
         return np.concatenate(out)
 
 
-class ShardExchange:
-    """per-slot visible counts of every rank -> NCCL all-gather -> exclusive scan over
-    ranks (device kernel) = each rank's output offsets in the global compacted buffers."""
-
-    def __init__(self, scene: DeviceScene, world_size: int):
-        torch = scene.torch
-        self.scene, self.ws = scene, world_size
-        dev = scene.t_model.device
-        s = scene.slots
-        with torch.cuda.stream(scene.stream):
-            self.t_local = torch.zeros(s, dtype=torch.int32, device=dev)
-            self.t_all = torch.zeros(world_size * s, dtype=torch.int32, device=dev)
-            self.t_off = torch.zeros(world_size * s, dtype=torch.int32, device=dev)
-            self.t_tot = torch.zeros(s, dtype=torch.int32, device=dev)
-        c = scene.ctx
-        self.local, self.all = c.wrap_tensor(self.t_local), c.wrap_tensor(self.t_all)
-        self.off, self.tot = c.wrap_tensor(self.t_off), c.wrap_tensor(self.t_tot)
-
-    def step(self):
-        import torch.distributed as dist
-
-        sc = self.scene
-        lods = len(C2["lod_distances"])
-        for i, mat in enumerate(sc.mats):
-            _, ind, _, _ = sc.world.material_outputs(mat)
-            sc.ctx.gather_instance_counts(ind, 0, lods, self.local, i * lods * 4)
-        with sc.torch.cuda.stream(sc.stream):
-            dist.all_gather_into_tensor(self.t_all, self.t_local)
-        sc.ctx.shard_offsets(self.all, self.ws, sc.slots, self.off, self.tot)
-
-
 def cpu_sample_run(sample: int, reps: int, cam, depth, workers: int | None = None):
     """The oracle (CPU restatement; taskflow executor when the reference's vendored taskflow was
     available at build time) on `sample` instances of the same generator / camera / pyramid.
@@ -265,7 +234,11 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = args.instances
     sc = DeviceScene(n, rank, local_rank)
-    ex = ShardExchange(sc, world_size) if world_size > 1 else None
+    ex = None
+    if world_size > 1:
+        from ravengine_b200.sharding import ShardedCull
+
+        ex = ShardedCull(sc.ctx, sc.world, sc.mats, [len(C2["lod_distances"])] * len(sc.mats), world_size, sc.stream)
 
     def barrier():
         if dist:
@@ -275,7 +248,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     def one_step():
         sc.step()
         if ex:
-            ex.step()
+            ex.exchange()
 
     for _ in range(max(args.warmup, 3)):
         one_step()

@@ -1,0 +1,155 @@
+"""Instance-range sharding of the cull across ranks (partition A). One process per GPU; torch.distributed
+is the plumbing. Every rank culls its slice of each command's entity list into rank-local compact slices; the only
+exchange step is the per-slot visible counts (all-gather, a few dozen bytes) followed by an exclusive scan over ranks,
+which gives each rank's offset inside the global per-(draw, LOD) slice and the global instanceCount. The compacted ids
+are gathered only when a single consumer needs them.
+
+Slot layout (identical to the single-GPU one, shaders/defaultcull.csh:305-312, src/RenderEngine_Draw.cpp:1334-1362):
+per material, command c with n_c entities and L_c LODs owns indirect slots [sum L_<c, +L_c) and the culling-buffer
+range starting at sum_{c'<c} L_c' * n_c', LOD l at + n_c * l.
+
+This module holds host logic only (integer plans + collectives); the scan itself is `rve_shard_offsets` on the device.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import numpy as np
+
+
+def split_range(n: int, world: int) -> list[tuple[int, int]]:
+    """Contiguous, balanced [lo, hi) ranges: rank r owns floor(r*n/world) .. floor((r+1)*n/world)."""
+    return [(r * n // world, (r + 1) * n // world) for r in range(world)]
+
+
+@dataclass(frozen=True)
+class SlotPlan:
+    """Slots of ONE material. counts[c] = entities of command c (on this rank, or globally), lods[c] = its LOD count."""
+    counts: tuple[int, ...]
+    lods: tuple[int, ...]
+
+    @property
+    def num_slots(self) -> int:
+        return sum(self.lods)
+
+    def slot_starts(self) -> list[int]:
+        """Start of every slot's slice in the material's culling buffer, in slot order."""
+        out, off = [], 0
+        for n, l in zip(self.counts, self.lods):
+            out += [off + n * k for k in range(l)]
+            off += n * l
+        return out
+
+    @property
+    def culling_slots(self) -> int:
+        return sum(self.counts) * sum(self.lods)  # numEntities * numLODs (:1288)
+
+
+def shard_plans(global_counts: list[tuple[int, ...]], lods: list[tuple[int, ...]], world: int) -> list[list[SlotPlan]]:
+    """plans[rank][material] when every command's entity list is split by split_range."""
+    plans = []
+    for r in range(world):
+        per_mat = []
+        for counts, l in zip(global_counts, lods):
+            per_mat.append(SlotPlan(tuple(split_range(n, world)[r][1] - split_range(n, world)[r][0] for n in counts), tuple(l)))
+        plans.append(per_mat)
+    return plans
+
+
+def exchange_counts(local_counts, world: int):
+    """all-gather of this rank's u32[slots] visible counts -> [world, slots] (same device / dtype)."""
+    import torch
+    import torch.distributed as dist
+
+    out = torch.empty((world, local_counts.numel()), dtype=local_counts.dtype, device=local_counts.device)
+    if world == 1:
+        out[0] = local_counts
+        return out
+    try:
+        dist.all_gather_into_tensor(out.view(-1), local_counts.contiguous())
+    except (RuntimeError, NotImplementedError):  # older gloo builds
+        parts = [torch.empty_like(local_counts) for _ in range(world)]
+        dist.all_gather(parts, local_counts.contiguous())
+        out = torch.stack(parts)
+    return out
+
+
+def gather_ids(local_ids, local_plan: list[SlotPlan], global_plan: list[SlotPlan], counts_all, offsets_all, rank: int, world: int,
+               id_base_of_rank):
+    """All-gather of the compacted id slices into the global culling-buffer layout (only when one consumer needs them).
+
+    local_ids[m]: this rank's culling buffer of material m (torch int32/uint32-as-int32 tensor);
+    counts_all / offsets_all: [world, total_slots] from exchange_counts / the exclusive scan (slots of all materials
+    concatenated in material order); id_base_of_rank(r): value added to rank r's local ids to make them global.
+    Returns one global culling buffer per material (filled with -1 where nothing was written)."""
+    import torch
+    import torch.distributed as dist
+
+    dev = local_ids[0].device
+    counts_host = counts_all.cpu().numpy().astype(np.int64)
+    offs_host = offsets_all.cpu().numpy().astype(np.int64)
+    # pack this rank's visible ids slot by slot, pad to the largest rank, all-gather
+    packed, s = [], 0
+    for m, plan in enumerate(local_plan):
+        for start in plan.slot_starts():
+            c = int(counts_host[rank, s])
+            packed.append(local_ids[m][start:start + c])
+            s += 1
+    mine = torch.cat(packed) if packed else torch.empty(0, dtype=torch.int32, device=dev)
+    per_rank = counts_host.sum(axis=1)
+    cap = int(per_rank.max()) if per_rank.size else 0
+    buf = torch.zeros(max(cap, 1), dtype=mine.dtype, device=dev)
+    buf[: mine.numel()] = mine
+    if world > 1:
+        parts = [torch.empty_like(buf) for _ in range(world)]
+        dist.all_gather(parts, buf)
+    else:
+        parts = [buf]
+    out = [torch.full((max(p.culling_slots, 1),), -1, dtype=mine.dtype, device=dev) for p in global_plan]
+    for r in range(world):
+        pos, s = 0, 0
+        base = id_base_of_rank(r)
+        for m, plan in enumerate(global_plan):
+            for gstart in plan.slot_starts():
+                c = int(counts_host[r, s])
+                if c:
+                    dst = gstart + int(offs_host[r, s])
+                    out[m][dst:dst + c] = parts[r][pos:pos + c] + base
+                pos += c
+                s += 1
+    return out
+
+
+class ShardedCull:
+    """GPU-side driver of one rank: after `world.cull_static(...)` has run on this rank's shard, `exchange()` enqueues
+    count gather -> NCCL all-gather -> device offset scan on the context's stream (no host synchronisation)."""
+
+    def __init__(self, ctx, world_obj, materials: list[int], lods_per_material: list[int], world_size: int, torch_stream):
+        import torch
+
+        self.ctx, self.world_obj, self.mats, self.lods, self.ws, self.stream = ctx, world_obj, materials, lods_per_material, world_size, torch_stream
+        self.slots = sum(lods_per_material)
+        dev = torch.device("cuda", ctx.device)
+        with torch.cuda.stream(torch_stream):
+            self.t_local = torch.zeros(self.slots, dtype=torch.int32, device=dev)
+            self.t_all = torch.zeros((world_size, self.slots), dtype=torch.int32, device=dev)
+            self.t_off = torch.zeros((world_size, self.slots), dtype=torch.int32, device=dev)
+            self.t_tot = torch.zeros(self.slots, dtype=torch.int32, device=dev)
+        self.b_local, self.b_all = ctx.wrap_tensor(self.t_local), ctx.wrap_tensor(self.t_all)
+        self.b_off, self.b_tot = ctx.wrap_tensor(self.t_off), ctx.wrap_tensor(self.t_tot)
+
+    def exchange(self) -> None:
+        import torch
+        import torch.distributed as dist
+
+        off = 0
+        for mat, lods in zip(self.mats, self.lods):
+            _, ind, _, _ = self.world_obj.material_outputs(mat)
+            self.ctx.gather_instance_counts(ind, 0, lods, self.b_local, off * 4)
+            off += lods
+        with torch.cuda.stream(self.stream):
+            if self.ws > 1:
+                dist.all_gather_into_tensor(self.t_all.view(-1), self.t_local)
+            else:
+                self.t_all[0].copy_(self.t_local)
+        self.ctx.shard_offsets(self.b_all, self.ws, self.slots, self.b_off, self.b_tot)

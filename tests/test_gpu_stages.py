@@ -147,3 +147,55 @@ def test_gen_instances_matches_oracle(ctx):
     np.testing.assert_array_equal(layers, bl.download(np.uint32))
     np.testing.assert_array_equal(flags, bf.download(np.uint16))
     np.testing.assert_array_equal(ids, bi.download(np.uint32))
+
+
+def test_shard_offsets_and_count_gather(ctx):
+    """8(e) helpers: instanceCount gather from the 20-B-stride commands and the exclusive scan over ranks."""
+    rng = np.random.default_rng(5)
+    world, slots = 8, 12
+    counts = rng.integers(0, 1_000_000, size=(world, slots)).astype(np.uint32)
+    b_counts, b_off, b_tot = ctx.buffer_from_numpy(counts), ctx.create_buffer(world * slots * 4), ctx.create_buffer(slots * 4)
+    ctx.shard_offsets(b_counts, world, slots, b_off, b_tot)
+    cmds = rng.integers(0, 2**31, size=(slots, 5)).astype(np.uint32)
+    b_cmds, b_out = ctx.buffer_from_numpy(cmds), ctx.create_buffer(64 + slots * 4)
+    ctx.gather_instance_counts(b_cmds, 3, slots - 3, b_out, 16)
+    ctx.synchronize()
+    c64 = counts.astype(np.uint64)
+    np.testing.assert_array_equal(b_off.download(np.uint32).reshape(world, slots), (np.cumsum(c64, axis=0) - c64).astype(np.uint32))
+    np.testing.assert_array_equal(b_tot.download(np.uint32), c64.sum(axis=0).astype(np.uint32))
+    np.testing.assert_array_equal(b_out.download(np.uint32)[4:4 + slots - 3], cmds[3:, 1])
+
+
+def test_sharded_cull_single_rank_exchange(ctx):
+    """ShardedCull with world_size 1: the count gather + scan path runs on the context's stream and reports the
+    indirect buffers' instance counts as totals with zero offsets."""
+    import torch
+
+    from ravengine_b200.sharding import ShardedCull
+    from ravengine_b200.world import World
+
+    rng = np.random.default_rng(21)
+    n = 20_000
+    model = scenes.random_transforms(rng, n, 200.0, 50.0)
+    w = World(ctx)
+    keep = [ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(np.full(n, 0xFFFFFFFF, np.uint32)), ctx.buffer_from_numpy(np.full(n, 0xFFFF, np.uint16))]
+    w.set_entity_buffers(*keep)
+    mats = []
+    for i in range(2):
+        ids = ctx.buffer_from_numpy(np.arange(i * n // 2, (i + 1) * n // 2, dtype=np.uint32))
+        keep.append(ids)
+        mesh = w.mesh_collection(1.5, [0.0, 40.0, 120.0], [36, 24, 12], [0, 36, 60], [0, 24, 40])
+        m = w.material()
+        w.add_command(m, mesh, ids, n // 2)
+        mats.append(m)
+    cam = scenes.default_camera(z_far=500.0)
+    w.cull_static(cam.view_proj_cm, cam.pos, ctx.create_pyramid(64))
+    stream = torch.cuda.ExternalStream(ctx.stream) if ctx.stream else torch.cuda.current_stream()
+    sh = ShardedCull(ctx, w, mats, [3, 3], 1, stream)
+    sh.exchange()
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    want = np.concatenate([w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:3, 1] for m in mats])
+    np.testing.assert_array_equal(sh.t_tot.cpu().numpy().view(np.uint32), want)
+    assert int(sh.t_off.abs().sum()) == 0 and want.sum() > 0
+    w.destroy()
