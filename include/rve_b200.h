@@ -290,6 +290,10 @@ RVE_API int rve_depth_pyramid_info(rve_ctx* ctx, rve_pyramid pyr, uint32_t* dim,
  * (mip 0, min-reduction sample of the w x h f32 depth buffer) followed by
  * depthpyramid.csh for mips 1..N-1. Whole chain in one call. */
 RVE_API int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height);
+/* The library keeps a derived copy of the chain for rve_cull (the min over each 2x2 sampler footprint, one load per
+ * sample). It follows rve_depth_pyramid_build and rve_buffer_upload/copy/fill_zero on the texel buffer automatically;
+ * call this after writing the texels any other way (own kernel through rve_buffer_device_ptr). */
+RVE_API int rve_depth_pyramid_texels_changed(rve_ctx* ctx, rve_pyramid pyr);
 
 /* ------------------------------------------------------------------ */
 /* a-2 cull + LOD + indirect compaction — shaders/defaultcull.csh      */

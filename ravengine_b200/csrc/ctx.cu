@@ -230,6 +230,7 @@ int rve_buffer_upload(rve_ctx* ctx, rve_buffer buf, size_t dst_offset, const voi
     if (dst_offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "upload out of range");
     if (!bytes) return 0;
     RVE_CUDA(cudaMemcpyAsync(static_cast<char*>(b->ptr) + dst_offset, host_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    pyramid_note_buffer_write(ctx, buf);
     return 0;
 }
 
@@ -256,6 +257,7 @@ int rve_buffer_copy(rve_ctx* ctx, rve_buffer src, size_t src_offset, rve_buffer 
     if (!bytes) return 0;
     RVE_CUDA(cudaMemcpyAsync(static_cast<char*>(d->ptr) + dst_offset, static_cast<const char*>(s->ptr) + src_offset, bytes,
                              cudaMemcpyDeviceToDevice, ctx->stream));
+    pyramid_note_buffer_write(ctx, dst);
     return 0;
 }
 
@@ -267,6 +269,7 @@ int rve_buffer_fill_zero(rve_ctx* ctx, rve_buffer buf, size_t offset, size_t byt
     if (offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "fill out of range");
     if (!bytes) return 0;
     RVE_CUDA(cudaMemsetAsync(static_cast<char*>(b->ptr) + offset, 0, bytes, ctx->stream));
+    pyramid_note_buffer_write(ctx, buf);
     return 0;
 }
 

@@ -22,6 +22,11 @@ struct PyramidRec {
     uint32_t dim = 0, levels = 0;
     rve_buffer texels = RVE_BUFFER_INVALID;
     rve_buffer counter = RVE_BUFFER_INVALID;  // u32 "blocks done" ticket for the fused build
+    // Footprint-min copy of the chain (acceleration structure of rve_cull, derived from `texels`): per level of n x n
+    // texels an (n+1)^2 image F[j][i] = min over the clamped 2x2 footprint {i-1,i} x {j-1,j}, i.e. the value of one
+    // min-reduction sample whose footprint starts at texel (i-1, j-1). One load per sample instead of four.
+    rve_buffer footmin = RVE_BUFFER_INVALID;
+    bool footmin_valid = true;  // both buffers start zeroed, which is consistent
     bool live = false;
 };
 
@@ -76,6 +81,10 @@ PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h);
 // makes sure the device pointer table reflects the host table (enqueued on the stream)
 int sync_table(rve_ctx* ctx);
 int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes);
+// (re)derives the footprint-min chain of a pyramid from its texels when they changed since the last derivation
+int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p);
+// marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)
+void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf);
 
 // RAII: brackets a kernel launch with events when ctx->profiling
 struct ProfScope {
@@ -143,5 +152,10 @@ __device__ __forceinline__ uint64_t pyr_level_offset(uint32_t dim, uint32_t leve
     return 4ull * (d0 * d0 - dl * dl) / 3ull;
 }
 #endif
+// start of level `level` in the footprint-min chain: sum over l < level of ((dim>>l)+1)^2
+__host__ __device__ inline uint64_t footmin_level_offset(uint32_t dim, uint32_t level) {
+    const uint64_t d0 = dim, dl = dim >> level;
+    return 4ull * (d0 * d0 - dl * dl) / 3ull + 4ull * (d0 - dl) + level;
+}
 
 }  // namespace rve

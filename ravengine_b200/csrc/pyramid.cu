@@ -122,6 +122,41 @@ pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, fl
     if (threadIdx.x == 0) *ticket = 0;  // re-arm for the next build on this stream
 }
 
+// footprint-min chain (see PyramidRec::footmin): one thread per output, all levels in one launch
+__global__ void pyramid_footmin_kernel(const float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels,
+                                       uint32_t total) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    uint32_t level = 0;
+    while (level + 1 < levels && i >= uint32_t(footmin_level_offset(dim, level + 1))) ++level;
+    const uint32_t n = dim >> level, n1 = n + 1;
+    const uint32_t local = i - uint32_t(footmin_level_offset(dim, level));
+    const uint32_t fx = local % n1, fy = local / n1;
+    const uint32_t x0 = fx ? fx - 1 : 0, x1 = fx < n ? fx : n - 1;
+    const uint32_t y0 = fy ? fy - 1 : 0, y1 = fy < n ? fy : n - 1;
+    const float* img = pyr + pyr_level_offset(dim, level);
+    fm[i] = gmin(gmin(img[y0 * n + x0], img[y0 * n + x1]), gmin(img[y1 * n + x0], img[y1 * n + x1]));
+}
+
+int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p) {
+    if (p->footmin_valid) return 0;
+    BufferRec* t = get_buffer(ctx, p->texels, "pyramid texels");
+    BufferRec* f = get_buffer(ctx, p->footmin, "pyramid footprint-min chain");
+    if (!t || !f) return RVE_ERR_BAD_HANDLE;
+    const uint32_t total = uint32_t(footmin_level_offset(p->dim, p->levels));
+    pyramid_footmin_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(static_cast<const float*>(t->ptr), static_cast<float*>(f->ptr),
+                                                                        p->dim, p->levels, total);
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    p->footmin_valid = true;
+    return 0;
+}
+
+void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf) {
+    for (auto& p : ctx->pyramids)
+        if (p.live && p.texels == buf) p.footmin_valid = false;
+}
+
 }  // namespace rve
 
 using namespace rve;
@@ -146,6 +181,8 @@ int rve_depth_pyramid_create(rve_ctx* ctx, uint32_t width, rve_pyramid* out) {
     if (rc) return rc;
     rc = rve_buffer_create(ctx, sizeof(uint32_t), &rec.counter);
     if (rc) return rc;
+    rc = rve_buffer_create(ctx, footmin_level_offset(dim, rec.levels) * sizeof(float), &rec.footmin);
+    if (rc) return rc;
     rec.live = true;
     std::lock_guard<std::mutex> lk(ctx->mu);
     ctx->pyramids.push_back(rec);
@@ -159,7 +196,16 @@ int rve_depth_pyramid_destroy(rve_ctx* ctx, rve_pyramid pyr) {
     if (!p) return RVE_ERR_BAD_HANDLE;
     rve_buffer_destroy(ctx, p->texels);
     rve_buffer_destroy(ctx, p->counter);
+    rve_buffer_destroy(ctx, p->footmin);
     p->live = false;
+    return 0;
+}
+
+int rve_depth_pyramid_texels_changed(rve_ctx* ctx, rve_pyramid pyr) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    PyramidRec* p = get_pyramid(ctx, pyr);
+    if (!p) return RVE_ERR_BAD_HANDLE;
+    p->footmin_valid = false;
     return 0;
 }
 
@@ -195,7 +241,9 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     }
     ctx->launches++;
     RVE_CUDA(cudaGetLastError());
-    return 0;
+    // the cull's footprint-min chain follows the texels (second, small launch: 1.4 M outputs from L2-resident texels)
+    p->footmin_valid = false;
+    return pyramid_refresh_footmin(ctx, p);
 }
 
 }  // extern "C"
