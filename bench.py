@@ -257,13 +257,16 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     if rank == 0:
         sampler.start()
     launches0 = sc.ctx.launch_count
+    ex_launches0 = ex.launch_count if ex else 0
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(sc.stream)
     for _ in range(args.steps):
         one_step()
+    if ex:
+        ex.finish()  # the side stream's count exchange + offset scan belong to the timed region
     ev1.record(sc.stream)
     barrier()
-    launches = sc.ctx.launch_count - launches0
+    launches = sc.ctx.launch_count - launches0 + (ex.launch_count - ex_launches0 if ex else 0)
     ms_total = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
     if dist:
@@ -286,6 +289,11 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     pyr_bytes = 4 * (4 * sc.pyr.dim ** 2 - 1) // 3
     algo_bytes = n * BYTES_PER_INSTANCE + visible * 4 + 36 * C2["materials"] + 20 * sc.slots + pyr_bytes
     achieved = algo_bytes / (cull_avg_ms * 1e-3) / 1e9
+    traffic, traffic_src = None, None
+    tf = ROOT / "profiles" / "cull_kernel_traffic.json"  # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` launch
+    if tf.exists() and n == C2["instances"]:
+        tj = json.loads(tf.read_text())
+        traffic, traffic_src = tj["traffic_bytes"], tj["source"]
 
     # --- e2e: host buffers through the shim, H2D + D2H inside the timed region ---
     e2e = run_e2e(sc, args, torch, barrier, dist)
@@ -311,7 +319,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                    "sharding": "instance range per rank; per-slot counts all-gathered with NCCL + device offset scan"
                    if world_size > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "kernel": "cull_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": cull_avg_ms,
                      "frac_of_8000_datasheet": achieved / 8000.0, "pyramid_kernel_ms": pyr_ms / max(pyr_n, 1)},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,

@@ -354,6 +354,12 @@ RVE_API int rve_shard_offsets(rve_ctx* ctx, rve_buffer counts_all, uint32_t worl
 RVE_API int rve_gather_instance_counts(rve_ctx* ctx, rve_buffer indirect, uint32_t first_slot, uint32_t num_slots,
                                        rve_buffer counts_out, size_t counts_offset_bytes);
 
+/* Same for several indirect buffers in ONE launch (one per material): slots of buffer i land after those of
+ * buffers < i. n_buffers <= 64 per call. */
+RVE_API int rve_gather_instance_counts_multi(rve_ctx* ctx, const rve_buffer* indirect, const uint32_t* first_slot,
+                                             const uint32_t* num_slots, uint32_t n_buffers, rve_buffer counts_out,
+                                             size_t counts_offset_bytes);
+
 /* ------------------------------------------------------------------ */
 /* synthetic scene generation on the device (bench / C5)  */
 /* ------------------------------------------------------------------ */

@@ -109,6 +109,7 @@ PROTOTYPES = {
     "rve_cluster_assign": (C.c_int, [VP, C.POINTER(GridAssignUBO), u32, u32, u32, u32]),
     "rve_shard_offsets": (C.c_int, [VP, u32, u32, u32, u32, u32]),
     "rve_gather_instance_counts": (C.c_int, [VP, u32, u32, u32, u32, C.c_size_t]),
+    "rve_gather_instance_counts_multi": (C.c_int, [VP, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), u32, u32, C.c_size_t]),
     "rve_gen_instances": (C.c_int, [VP, C.POINTER(SceneGenParams), u64, u32, u32, u32, u32, u32]),
 }
 

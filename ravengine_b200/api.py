@@ -177,3 +177,10 @@ class Context:
 
     def gather_instance_counts(self, indirect: Buffer, first_slot: int, slots: int, out: Buffer, out_off: int = 0) -> None:
         _check(self.lib, self.lib.rve_gather_instance_counts(self.h, indirect.handle, first_slot, slots, out.handle, out_off))
+
+    def gather_instance_counts_multi(self, indirect: list[Buffer], first_slots: list[int], slots: list[int], out: Buffer, out_off: int = 0) -> None:
+        n = len(indirect)
+        h = (C.c_uint32 * n)(*[b.handle for b in indirect])
+        f = (C.c_uint32 * n)(*first_slots)
+        s = (C.c_uint32 * n)(*slots)
+        _check(self.lib, self.lib.rve_gather_instance_counts_multi(self.h, h, f, s, n, out.handle, out_off))

@@ -75,6 +75,19 @@ __global__ void gather_counts_kernel(const RveIndirectIndexedCommand* __restrict
     if (s < n) out[s] = cmds[first + s].instanceCount;
 }
 
+struct GatherMulti {
+    const RveIndirectIndexedCommand* cmds[64];
+    uint32_t first[64], n[64], outStart[64];
+    uint32_t count, total;
+};
+__global__ void gather_counts_multi_kernel(const GatherMulti g, uint32_t* __restrict__ out) {
+    const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= g.total) return;
+    uint32_t b = 0;
+    while (b + 1 < g.count && s >= g.outStart[b + 1]) ++b;
+    out[s] = g.cmds[b][g.first[b] + (s - g.outStart[b])].instanceCount;
+}
+
 }  // namespace rve
 
 using namespace rve;
@@ -138,6 +151,37 @@ int rve_gather_instance_counts(rve_ctx* ctx, rve_buffer indirect, uint32_t first
     gather_counts_kernel<<<(num_slots + threads - 1) / threads, threads, 0, ctx->stream>>>(
         static_cast<const RveIndirectIndexedCommand*>(i->ptr), first_slot, num_slots,
         reinterpret_cast<uint32_t*>(static_cast<char*>(o->ptr) + counts_offset_bytes));
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int rve_gather_instance_counts_multi(rve_ctx* ctx, const rve_buffer* indirect, const uint32_t* first_slot, const uint32_t* num_slots,
+                                     uint32_t n_buffers, rve_buffer counts_out, size_t counts_offset_bytes) {
+    if (!ctx || !indirect || !first_slot || !num_slots) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    if (!n_buffers) return 0;
+    RVE_REQUIRE(n_buffers <= 64, "at most 64 indirect buffers per call");
+    BufferRec* o = get_buffer(ctx, counts_out, "counts");
+    if (!o) return RVE_ERR_BAD_HANDLE;
+    GatherMulti gm{};
+    gm.count = n_buffers;
+    uint32_t total = 0;
+    for (uint32_t i = 0; i < n_buffers; ++i) {
+        BufferRec* b = get_buffer(ctx, indirect[i], "indirect");
+        if (!b) return RVE_ERR_BAD_HANDLE;
+        RVE_REQUIRE((uint64_t(first_slot[i]) + num_slots[i]) * 20 <= b->bytes, "indirect buffer too small");
+        gm.cmds[i] = static_cast<const RveIndirectIndexedCommand*>(b->ptr);
+        gm.first[i] = first_slot[i];
+        gm.n[i] = num_slots[i];
+        gm.outStart[i] = total;
+        total += num_slots[i];
+    }
+    gm.total = total;
+    if (!total) return 0;
+    RVE_REQUIRE(counts_offset_bytes % 4 == 0 && counts_offset_bytes + uint64_t(total) * 4 <= o->bytes, "counts buffer too small");
+    gather_counts_multi_kernel<<<(total + 127) / 128, 128, 0, ctx->stream>>>(
+        gm, reinterpret_cast<uint32_t*>(static_cast<char*>(o->ptr) + counts_offset_bytes));
     ctx->launches++;
     RVE_CUDA(cudaGetLastError());
     return 0;

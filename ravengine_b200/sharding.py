@@ -121,35 +121,72 @@ def gather_ids(local_ids, local_plan: list[SlotPlan], global_plan: list[SlotPlan
 
 
 class ShardedCull:
-    """GPU-side driver of one rank: after `world.cull_static(...)` has run on this rank's shard, `exchange()` enqueues
-    count gather -> NCCL all-gather -> device offset scan on the context's stream (no host synchronisation)."""
+    """GPU-side driver of one rank. After `world.cull_static(...)` has run on this rank's shard, `exchange()` enqueues
+    ONE kernel on the cull's stream that copies the per-slot instance counts out of the indirect buffers (the next
+    frame re-initialises them), then - on a side stream, so the next frame's pyramid build and cull are not held up by
+    collective latency - the NCCL all-gather of those counts and the device exclusive scan over ranks. Buffers are
+    double-buffered; `finish()` joins the side stream (call it before reading offsets / totals, or at frame end).
+    Nothing synchronises with the host."""
 
     def __init__(self, ctx, world_obj, materials: list[int], lods_per_material: list[int], world_size: int, torch_stream):
         import torch
 
+        from .api import Context
+
         self.ctx, self.world_obj, self.mats, self.lods, self.ws, self.stream = ctx, world_obj, materials, lods_per_material, world_size, torch_stream
         self.slots = sum(lods_per_material)
         dev = torch.device("cuda", ctx.device)
+        self.side = torch.cuda.Stream(device=dev)
+        self.ctx2 = Context(ctx.device, self.side.cuda_stream)  # same device memory, enqueues on the side stream
+        self.t_local, self.t_all, self.t_off, self.t_tot = [], [], [], []
+        self.b_local, self.b_all, self.b_off, self.b_tot, self.done = [], [], [], [], [None, None]
         with torch.cuda.stream(torch_stream):
-            self.t_local = torch.zeros(self.slots, dtype=torch.int32, device=dev)
-            self.t_all = torch.zeros((world_size, self.slots), dtype=torch.int32, device=dev)
-            self.t_off = torch.zeros((world_size, self.slots), dtype=torch.int32, device=dev)
-            self.t_tot = torch.zeros(self.slots, dtype=torch.int32, device=dev)
-        self.b_local, self.b_all = ctx.wrap_tensor(self.t_local), ctx.wrap_tensor(self.t_all)
-        self.b_off, self.b_tot = ctx.wrap_tensor(self.t_off), ctx.wrap_tensor(self.t_tot)
+            for _ in range(2):
+                self.t_local.append(torch.zeros(self.slots, dtype=torch.int32, device=dev))
+                self.t_all.append(torch.zeros((world_size, self.slots), dtype=torch.int32, device=dev))
+                self.t_off.append(torch.zeros((world_size, self.slots), dtype=torch.int32, device=dev))
+                self.t_tot.append(torch.zeros(self.slots, dtype=torch.int32, device=dev))
+        torch_stream.synchronize()
+        for i in range(2):
+            self.b_local.append(ctx.wrap_tensor(self.t_local[i]))
+            self.b_all.append(self.ctx2.wrap_tensor(self.t_all[i]))
+            self.b_off.append(self.ctx2.wrap_tensor(self.t_off[i]))
+            self.b_tot.append(self.ctx2.wrap_tensor(self.t_tot[i]))
+        self.k = 0
+        self._indirect = None
 
-    def exchange(self) -> None:
+    def _indirect_buffers(self):
+        bufs = [self.world_obj.material_outputs(m)[1] for m in self.mats]
+        return bufs
+
+    def exchange(self, refresh_buffers: bool = False) -> int:
+        """Returns the index (0/1) of the buffer set this frame's counts / offsets / totals land in."""
         import torch
         import torch.distributed as dist
 
-        off = 0
-        for mat, lods in zip(self.mats, self.lods):
-            _, ind, _, _ = self.world_obj.material_outputs(mat)
-            self.ctx.gather_instance_counts(ind, 0, lods, self.b_local, off * 4)
-            off += lods
-        with torch.cuda.stream(self.stream):
+        b = self.k & 1
+        self.k += 1
+        if self._indirect is None or refresh_buffers:  # handles change only when the shim reallocates (entity counts changed)
+            self._indirect = self._indirect_buffers()
+        if self.done[b] is not None:
+            self.stream.wait_event(self.done[b])  # the exchange that last used this buffer set has finished
+        self.ctx.gather_instance_counts_multi(self._indirect, [0] * len(self.mats), self.lods, self.b_local[b])
+        ev = torch.cuda.Event()
+        ev.record(self.stream)
+        self.side.wait_event(ev)
+        with torch.cuda.stream(self.side):
             if self.ws > 1:
-                dist.all_gather_into_tensor(self.t_all.view(-1), self.t_local)
+                dist.all_gather_into_tensor(self.t_all[b].view(-1), self.t_local[b])
             else:
-                self.t_all[0].copy_(self.t_local)
-        self.ctx.shard_offsets(self.b_all, self.ws, self.slots, self.b_off, self.b_tot)
+                self.t_all[b][0].copy_(self.t_local[b])
+        self.ctx2.shard_offsets(self.b_all[b], self.ws, self.slots, self.b_off[b], self.b_tot[b])
+        self.done[b] = torch.cuda.Event()
+        self.done[b].record(self.side)
+        return b
+
+    def finish(self) -> None:
+        self.stream.wait_stream(self.side)
+
+    @property
+    def launch_count(self) -> int:
+        return self.ctx2.launch_count

@@ -192,10 +192,25 @@ def test_sharded_cull_single_rank_exchange(ctx):
     w.cull_static(cam.view_proj_cm, cam.pos, ctx.create_pyramid(64))
     stream = torch.cuda.ExternalStream(ctx.stream) if ctx.stream else torch.cuda.current_stream()
     sh = ShardedCull(ctx, w, mats, [3, 3], 1, stream)
-    sh.exchange()
+    want = None
+    for frame in range(3):  # double-buffered: frames alternate buffer sets
+        if frame:
+            w.cull_static(cam.view_proj_cm, cam.pos, ctx.create_pyramid(64))
+        b = sh.exchange()
+        assert b == frame % 2
+        sh.finish()
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        want = np.concatenate([w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:3, 1] for m in mats])
+        np.testing.assert_array_equal(sh.t_tot[b].cpu().numpy().view(np.uint32), want)
+        assert int(sh.t_off[b].abs().sum()) == 0 and want.sum() > 0
+    # the multi-buffer gather equals the per-buffer one
+    out1, out2 = ctx.create_buffer(6 * 4), ctx.create_buffer(6 * 4)
+    inds = [w.material_outputs(m)[1] for m in mats]
+    ctx.gather_instance_counts_multi(inds, [0, 0], [3, 3], out1)
+    for i, ind in enumerate(inds):
+        ctx.gather_instance_counts(ind, 0, 3, out2, i * 12)
     ctx.synchronize()
-    torch.cuda.synchronize()
-    want = np.concatenate([w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:3, 1] for m in mats])
-    np.testing.assert_array_equal(sh.t_tot.cpu().numpy().view(np.uint32), want)
-    assert int(sh.t_off.abs().sum()) == 0 and want.sum() > 0
+    np.testing.assert_array_equal(out1.download(np.uint32), out2.download(np.uint32))
+    np.testing.assert_array_equal(out1.download(np.uint32), want)
     w.destroy()
