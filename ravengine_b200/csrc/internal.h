@@ -139,6 +139,44 @@ __device__ __forceinline__ float dot3(float ax, float ay, float az, float bx, fl
     return __fmaf_rn(az, bz, __fmaf_rn(ay, by, ax * bx));
 }
 
+// Packed pairs of IEEE f32 (sm_100 FFMA2 / FMUL2 / FADD2): two independent, individually rounded operations per
+// issued instruction - same bits as two scalar operations, half the issue slots. The cull kernel is issue-bound.
+struct f2 {
+    float x, y;
+};
+__device__ __forceinline__ unsigned long long f2_pack(f2 a) {
+    unsigned long long r;
+    asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a.x), "f"(a.y));
+    return r;
+}
+__device__ __forceinline__ f2 f2_unpack(unsigned long long r) {
+    f2 d;
+    asm("mov.b64 {%0,%1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(r));
+    return d;
+}
+#ifdef RVE_F2_SCALAR  // tuning aid: the same operations as scalar instructions
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) { return f2{__fmaf_rn(a.x, b.x, c.x), __fmaf_rn(a.y, b.y, c.y)}; }
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) { return f2{a.x * b.x, a.y * b.y}; }
+__device__ __forceinline__ f2 add2(f2 a, f2 b) { return f2{a.x + b.x, a.y + b.y}; }
+#else
+__device__ __forceinline__ f2 fma2(f2 a, f2 b, f2 c) {
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)), "l"(f2_pack(c)));
+    return f2_unpack(d);
+}
+__device__ __forceinline__ f2 mul2(f2 a, f2 b) {
+    unsigned long long d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
+    return f2_unpack(d);
+}
+__device__ __forceinline__ f2 add2(f2 a, f2 b) {
+    unsigned long long d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(f2_pack(a)), "l"(f2_pack(b)));
+    return f2_unpack(d);
+}
+#endif
+__device__ __forceinline__ f2 splat2(float s) { return f2{s, s}; }
+
 // 128-bit read-only load that does not allocate in L1 (streamed once)
 __device__ __forceinline__ float4 ld_stream_f4(const float4* p) {
     float4 r;
