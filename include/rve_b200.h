@@ -342,6 +342,12 @@ RVE_API int rve_cluster_assign(rve_ctx* ctx, const RveGridAssignUBO* ubo, rve_bu
 /* ------------------------------------------------------------------ */
 /* 8(e) multi-GPU helpers (instance-range sharding)                    */
 /* ------------------------------------------------------------------ */
+/* Scatter of a packed dirty list (the device half of the dirty-range upload that replaces the reference's
+ * per-range CopyBufferToBuffer, src/BufferedVRAMVector.cpp:87-104): staging holds `count` rows of elem_bytes at
+ * rows_offset and their u32 destination row indices at indices_offset; dst[indices[i]] = rows[i]. */
+RVE_API int rve_scatter_rows(rve_ctx* ctx, rve_buffer dst, uint32_t elem_bytes, rve_buffer staging, uint64_t indices_offset,
+                             uint64_t rows_offset, uint32_t count);
+
 /* After every rank culled its shard into rank-local slices and the per-slot
  * counts were all-gathered (NCCL, done by the host plumbing), compute on the
  * device: offsets[r][s] = sum_{q<r} counts[q][s] and total[s] = sum_q counts[q][s].

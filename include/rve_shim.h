@@ -97,6 +97,45 @@ RVE_API int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float v
                            uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count,
                            rve_buffer* out_cluster_buffer);
 
+/* ---- dirty-range upload: BufferedVRAMVector / EncodeSync (include/RavEngine/BufferedVRAMVector.hpp:33-209,
+ * src/BufferedVRAMVector.cpp:27-144) - the step before the render-prep path ---- */
+typedef struct rvs_vector rvs_vector;
+typedef struct rvs_sync_stats {
+    uint32_t ranges;         /* ranges the reference's scan produces (maxGapSize 5) */
+    uint32_t rows_in_ranges; /* elements they cover */
+    uint32_t direct_copies;  /* ranges sent as one host->device copy each */
+    uint32_t packed_rows;    /* modified rows of short ranges, sent through the packed staging block + scatter kernel */
+    uint64_t direct_bytes;
+    uint64_t packed_bytes;   /* staging block size (rows + u32 indices) */
+} rvs_sync_stats;
+#define RVS_SYNC_RANGES 0u /* the reference's behaviour: one copy per range */
+#define RVS_SYNC_PACKED 1u /* ranges shorter than direct_min_rows: ONE staging upload + ONE scatter kernel */
+#define RVS_SYNC_PULL 2u   /* no host scan at all: one kernel reads the flags and the flagged rows from the pinned host
+                              arrays over PCIe, writes the rows to the private buffer and clears the flags. The flag
+                              block is double-buffered: rvs_vector_tracking() changes at every such sync. Like the
+                              reference's shared-buffer copies, rows must not be rewritten before the stream got there. */
+
+RVE_API int rvs_vector_create(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, rvs_vector** out);
+RVE_API int rvs_vector_destroy(rvs_vector* v);
+/* Resize: new elements are zero and start out modified (BufferedVRAMVector.hpp:64-69) */
+RVE_API int rvs_vector_resize(rvs_vector* v, uint32_t count);
+RVE_API uint32_t rvs_vector_size(rvs_vector* v);
+/* GetHostBuffer(): pinned host memory, count * elem_bytes; valid until the next growth */
+RVE_API void* rvs_vector_host(rvs_vector* v);
+/* syncTrackingBuffer: one byte per element, non-zero = modified since the last sync */
+RVE_API uint8_t* rvs_vector_tracking(rvs_vector* v);
+/* SetValueAt / GetValueAtForWriting (hpp:113-121) */
+RVE_API int rvs_vector_set(rvs_vector* v, uint32_t index, const void* value);
+RVE_API int rvs_vector_mark(rvs_vector* v, uint32_t begin, uint32_t end);
+/* EncodeSync: enqueues the copies on the context's stream; afterwards the private buffer equals the host buffer */
+RVE_API int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_rows, rvs_sync_stats* stats);
+/* GetPrivateBuffer(): may change at every rvs_vector_encode_sync after a growth, like the reference's */
+RVE_API rve_buffer rvs_vector_private_buffer(rvs_vector* v);
+/* rows copied by RVS_SYNC_PULL syncs since creation (reads a device counter: synchronises the stream) */
+RVE_API uint64_t rvs_vector_pulled_rows(rvs_vector* v);
+/* (begin, end) pairs of the last sync, for inspection; returns their number */
+RVE_API uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max_pairs);
+
 #ifdef __cplusplus
 }
 #endif

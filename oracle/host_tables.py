@@ -172,3 +172,29 @@ def build_skinned_tables(materials) -> SkinnedTables:
         resets.append(reset)
         prep_all.append(prep)
     return SkinnedTables(cubos_all, groups, resets, prep_all, skin_all, bindless)
+
+
+def sync_ranges(tracking: np.ndarray, max_gap: int = 5) -> np.ndarray:
+    """Copy ranges of BufferedVRAMStructureBase::EncodeSync (src/BufferedVRAMVector.cpp:106-139), restated loop for
+    loop: dirty elements open / extend a range, `max_gap` consecutive clean ones close it at the index of the last
+    of them. Returns (begin, end) pairs; clears the flags like the reference does."""
+    out = []
+    gap, begin = 0, 0
+    n = len(tracking)
+    for i in range(n):
+        modified = bool(tracking[i])
+        if modified and gap == 0:
+            gap = max_gap
+            begin = i
+        elif modified:
+            gap = max_gap
+        if not modified:
+            prev = gap
+            gap = max(0, gap - 1)
+            if gap == 0 and prev != 0:
+                out.append((begin, i))
+        if modified:
+            tracking[i] = 0
+    if gap != 0:
+        out.append((begin, n))
+    return np.array(out, np.uint32).reshape(-1, 2)

@@ -110,6 +110,7 @@ PROTOTYPES = {
     "rve_shard_offsets": (C.c_int, [VP, u32, u32, u32, u32, u32]),
     "rve_gather_instance_counts": (C.c_int, [VP, u32, u32, u32, u32, C.c_size_t]),
     "rve_gather_instance_counts_multi": (C.c_int, [VP, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), u32, u32, C.c_size_t]),
+    "rve_scatter_rows": (C.c_int, [VP, u32, u32, u32, u64, u64, u32]),
     "rve_gen_instances": (C.c_int, [VP, C.POINTER(SceneGenParams), u64, u32, u32, u32, u32, u32]),
 }
 
@@ -138,6 +139,29 @@ PROTOTYPES.update({
     "rvs_skinned_outputs": (C.c_int, [VP, UP, UP]),
     "rvs_skinned_material_outputs": (C.c_int, [VP, u32, UP, UP, UP]),
     "rvs_bin_lights": (C.c_int, [VP, FP, FP, UP, UP, f32, f32, u32, u32, u32, u32, UP]),
+})
+
+
+
+class SyncStats(C.Structure):
+    _fields_ = [("ranges", u32), ("rows_in_ranges", u32), ("direct_copies", u32), ("packed_rows", u32),
+                ("direct_bytes", u64), ("packed_bytes", u64)]
+
+
+SYNC_RANGES, SYNC_PACKED, SYNC_PULL = 0, 1, 2
+PROTOTYPES.update({
+    "rvs_vector_create": (C.c_int, [VP, u32, u32, C.POINTER(VP)]),
+    "rvs_vector_destroy": (C.c_int, [VP]),
+    "rvs_vector_resize": (C.c_int, [VP, u32]),
+    "rvs_vector_size": (u32, [VP]),
+    "rvs_vector_host": (VP, [VP]),
+    "rvs_vector_tracking": (VP, [VP]),
+    "rvs_vector_set": (C.c_int, [VP, u32, VP]),
+    "rvs_vector_mark": (C.c_int, [VP, u32, u32]),
+    "rvs_vector_encode_sync": (C.c_int, [VP, u32, u32, C.POINTER(SyncStats)]),
+    "rvs_vector_private_buffer": (u32, [VP]),
+    "rvs_vector_pulled_rows": (u64, [VP]),
+    "rvs_vector_last_ranges": (u32, [VP, UP, u32]),
 })
 
 _lib = None

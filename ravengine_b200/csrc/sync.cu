@@ -1,0 +1,481 @@
+// sync.cu — dirty-range upload of host-shared per-entity arrays: the step BEFORE the render-prep
+// path. Mirrors BufferedVRAMVector / BufferedVRAMStructureBase::EncodeSync
+// (include/RavEngine/BufferedVRAMVector.hpp:33-209, src/BufferedVRAMVector.cpp:27-144).
+//
+// The reference walks one byte flag per element, merges dirty elements whose gaps are <= maxGapSize (5) into
+// ranges and records one CopyBufferToBuffer per range. That is reproduced exactly by RVS_SYNC_RANGES (the range
+// list is the same, each range is one async copy). With many small ranges (scattered moving objects) the copy
+// count explodes, so RVS_SYNC_PACKED - the B200-first path - sends long ranges as direct copies and packs all
+// short ranges' modified rows (not the clean gap rows a range drags along) into ONE pinned staging block
+// [rows][u32 row indices], uploads it with one copy and scatters it with one kernel (16-B lanes, fully coalesced
+// on the staging side). The flag scan skips clean spans eight
+// flags at a time. Both modes leave the private buffer byte-identical to the host buffer.
+#include <cstring>
+
+#include "frame_internal.h"
+#include "internal.h"
+
+namespace rve {
+
+// one thread per 16-B chunk of a row (rows are multiples of 4 B; the 16-B path needs 16-B aligned rows)
+__global__ void scatter_rows16_kernel(uint4* __restrict__ dst, const uint32_t* __restrict__ idx, const uint4* __restrict__ rows,
+                                      uint32_t count, uint32_t chunksPerRow) {
+    const uint64_t t = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint64_t total = uint64_t(count) * chunksPerRow;
+    for (uint64_t i = t; i < total; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint32_t r = uint32_t(i / chunksPerRow), c = uint32_t(i % chunksPerRow);
+        dst[uint64_t(__ldg(idx + r)) * chunksPerRow + c] = __ldg(rows + i);
+    }
+}
+__global__ void scatter_rows4_kernel(uint32_t* __restrict__ dst, const uint32_t* __restrict__ idx, const uint32_t* __restrict__ rows,
+                                     uint32_t count, uint32_t wordsPerRow) {
+    const uint64_t t = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    const uint64_t total = uint64_t(count) * wordsPerRow;
+    for (uint64_t i = t; i < total; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint32_t r = uint32_t(i / wordsPerRow), c = uint32_t(i % wordsPerRow);
+        dst[uint64_t(__ldg(idx + r)) * wordsPerRow + c] = __ldg(rows + i);
+    }
+}
+// 2-byte rows (perObjectAttributes): one thread per row
+__global__ void scatter_rows2_kernel(uint16_t* __restrict__ dst, const uint32_t* __restrict__ idx, const uint16_t* __restrict__ rows,
+                                     uint32_t count) {
+    const uint64_t t = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    for (uint64_t i = t; i < count; i += uint64_t(gridDim.x) * blockDim.x) dst[__ldg(idx + i)] = rows[i];
+}
+
+// RVS_SYNC_PULL: the GPU walks the modification flags itself (pinned host memory, read over PCIe), copies every
+// flagged row straight from the pinned host array into the private buffer and clears the flag - no host scan, no
+// host packing, one launch. A warp owns 32 consecutive rows; flagged rows are copied by groups of lanes.
+template <typename Chunk>
+__global__ void pull_rows_kernel(uint8_t* __restrict__ flags, const Chunk* __restrict__ src, Chunk* __restrict__ dst, uint32_t n,
+                                 uint32_t chunksPerRow, uint32_t lanesPerRow, uint32_t* __restrict__ rowsCopied) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
+    const uint32_t groups = (n + 31) / 32;
+    const uint32_t rowsPerIter = 32 / lanesPerRow;
+    uint32_t copied = 0;
+    for (uint32_t grp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); grp < groups; grp += warpsTotal) {
+        const uint32_t row0 = grp * 32;
+        uint8_t f = 0;
+        if (row0 + lane < n) f = flags[row0 + lane];
+        const uint32_t mask = __ballot_sync(0xffffffffu, f != 0);
+        if (mask == 0) continue;
+        if (f) flags[row0 + lane] = 0;
+        const uint32_t cnt = __popc(mask);
+        copied += cnt;
+        for (uint32_t i = 0; i < cnt; i += rowsPerIter) {
+            const uint32_t j = i + lane / lanesPerRow;
+            if (j < cnt) {
+                const uint64_t row = row0 + (__fns(mask, 0, int(j) + 1));
+                for (uint32_t c = lane % lanesPerRow; c < chunksPerRow; c += lanesPerRow) dst[row * chunksPerRow + c] = src[row * chunksPerRow + c];
+            }
+        }
+    }
+    if (lane == 0 && copied) atomicAdd(rowsCopied, copied);
+}
+
+static uint32_t pow2_at_most_32(uint32_t v) {
+    uint32_t p = 1;
+    while (p * 2 <= v && p < 32) p *= 2;
+    return p;
+}
+
+int launch_pull(rve_ctx* ctx, uint8_t* flags, const unsigned char* host, unsigned char* dev, uint32_t n, uint32_t elemBytes,
+                uint32_t* rowsCopied) {
+    const int threads = 256;
+    const uint32_t groups = (n + 31) / 32;
+    uint32_t blocks = (groups + 7) / 8;
+    const uint32_t maxBlocks = uint32_t(ctx->sm_count) * 8u;
+    if (blocks > maxBlocks) blocks = maxBlocks;
+    const bool a16 = elemBytes % 16 == 0 && ((reinterpret_cast<uintptr_t>(host) | reinterpret_cast<uintptr_t>(dev)) & 15) == 0;
+    if (a16) {
+        const uint32_t cpr = elemBytes / 16;
+        pull_rows_kernel<uint4><<<blocks, threads, 0, ctx->stream>>>(flags, reinterpret_cast<const uint4*>(host), reinterpret_cast<uint4*>(dev), n,
+                                                                    cpr, pow2_at_most_32(cpr), rowsCopied);
+    } else if (elemBytes % 4 == 0) {
+        const uint32_t cpr = elemBytes / 4;
+        pull_rows_kernel<uint32_t><<<blocks, threads, 0, ctx->stream>>>(flags, reinterpret_cast<const uint32_t*>(host),
+                                                                       reinterpret_cast<uint32_t*>(dev), n, cpr, pow2_at_most_32(cpr), rowsCopied);
+    } else {
+        const uint32_t cpr = elemBytes / 2;
+        pull_rows_kernel<uint16_t><<<blocks, threads, 0, ctx->stream>>>(flags, reinterpret_cast<const uint16_t*>(host),
+                                                                       reinterpret_cast<uint16_t*>(dev), n, cpr, pow2_at_most_32(cpr), rowsCopied);
+    }
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace rve
+
+using namespace rve;
+
+extern "C" int rve_scatter_rows(rve_ctx* ctx, rve_buffer dst, uint32_t elem_bytes, rve_buffer staging, uint64_t indices_offset,
+                                uint64_t rows_offset, uint32_t count) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "null context");
+    if (count == 0) return 0;
+    DeviceGuard g(ctx->device);
+    BufferRec* bd = get_buffer(ctx, dst, "scatter destination");
+    BufferRec* bs = get_buffer(ctx, staging, "scatter staging");
+    if (!bd || !bs) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE(elem_bytes == 2 || (elem_bytes % 4) == 0, "row size must be 2 or a multiple of 4 bytes");
+    RVE_REQUIRE(indices_offset % 4 == 0 && indices_offset + uint64_t(count) * 4 <= bs->bytes, "index list outside the staging buffer");
+    RVE_REQUIRE(rows_offset + uint64_t(count) * elem_bytes <= bs->bytes, "row payload outside the staging buffer");
+    const auto* base = static_cast<const unsigned char*>(bs->ptr);
+    const auto* idx = reinterpret_cast<const uint32_t*>(base + indices_offset);
+    const unsigned char* rows = base + rows_offset;
+    const int threads = 256;
+    const uint32_t maxBlocks = uint32_t(ctx->sm_count) * 8u;
+    if (elem_bytes == 2) {
+        RVE_REQUIRE(rows_offset % 2 == 0, "row payload must be 2-byte aligned");
+        const uint32_t blocks = std::min<uint64_t>((uint64_t(count) + threads - 1) / threads, maxBlocks);
+        scatter_rows2_kernel<<<blocks, threads, 0, ctx->stream>>>(static_cast<uint16_t*>(bd->ptr), idx,
+                                                                 reinterpret_cast<const uint16_t*>(rows), count);
+    } else if (elem_bytes % 16 == 0 && rows_offset % 16 == 0 && (reinterpret_cast<uintptr_t>(bd->ptr) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(bs->ptr) & 15) == 0) {
+        const uint32_t cpr = elem_bytes / 16;
+        const uint32_t blocks = std::min<uint64_t>((uint64_t(count) * cpr + threads - 1) / threads, maxBlocks);
+        scatter_rows16_kernel<<<blocks, threads, 0, ctx->stream>>>(static_cast<uint4*>(bd->ptr), idx, reinterpret_cast<const uint4*>(rows),
+                                                                  count, cpr);
+    } else {
+        RVE_REQUIRE(rows_offset % 4 == 0, "row payload must be 4-byte aligned");
+        const uint32_t wpr = elem_bytes / 4;
+        const uint32_t blocks = std::min<uint64_t>((uint64_t(count) * wpr + threads - 1) / threads, maxBlocks);
+        scatter_rows4_kernel<<<blocks, threads, 0, ctx->stream>>>(static_cast<uint32_t*>(bd->ptr), idx,
+                                                                 reinterpret_cast<const uint32_t*>(rows), count, wpr);
+    }
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// BufferedVRAMVector stand-in (host-shared buffer + modification flags + device-private buffer)
+// ---------------------------------------------------------------------------------------------------------
+struct rvs_vector {
+    rve_ctx* ctx = nullptr;
+    uint32_t elemBytes = 0;
+    uint32_t count = 0, capacity = 0;
+    unsigned char* host = nullptr;  // pinned: VRAMVector's host-mapped Shared buffer
+    // syncTrackingBuffer: pinned, capacity rounded up to 32 flags, double-buffered so that RVS_SYNC_PULL can hand
+    // the flags of this frame to the GPU while the host already records the next frame's modifications
+    uint8_t* trackBuf[2] = {nullptr, nullptr};
+    uint8_t* track = nullptr;  // == trackBuf[cur]
+    int cur = 0;
+    cudaEvent_t pullDone[2] = {nullptr, nullptr};  // the pull kernel that read (and cleared) trackBuf[i] has finished
+    bool pullBusy[2] = {false, false};
+    uint32_t* pullRows = nullptr;  // device counter: rows copied by pull kernels since creation
+    rve_buffer priv = RVE_BUFFER_INVALID;
+    size_t privBytes = 0;
+    unsigned char* stageHost = nullptr;  // packed mode: pinned staging block [rows][indices]
+    size_t stageHostBytes = 0;
+    rve_buffer stageDev = RVE_BUFFER_INVALID;
+    size_t stageDevBytes = 0;
+    cudaEvent_t stageFree = nullptr;  // upload of the previous staging block has completed
+    bool stageBusy = false;
+    std::vector<uint32_t> ranges;  // (begin, end) pairs of the last sync
+};
+
+namespace {
+
+constexpr int kMaxGapSize = 5;  // src/BufferedVRAMVector.cpp:106
+
+uint32_t next_pow2(uint32_t v) {
+    uint32_t p = 1;
+    while (p < v) p <<= 1;
+    return p;
+}
+
+int vec_reserve(rvs_vector* v, uint32_t newCap) {
+    if (newCap <= v->capacity) return 0;
+    DeviceGuard g(v->ctx->device);
+    unsigned char* nh = nullptr;
+    RVE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&nh), size_t(newCap) * v->elemBytes, cudaHostAllocDefault));
+    if (v->host) {
+        // copies enqueued from the old block must have been consumed before it is released
+        RVE_CUDA(cudaStreamSynchronize(v->ctx->stream));
+        std::memcpy(nh, v->host, size_t(v->count) * v->elemBytes);
+        cudaFreeHost(v->host);
+    }
+    v->host = nh;
+    for (int i = 0; i < 2; ++i) {
+        uint8_t* nt = nullptr;
+        RVE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&nt), size_t(newCap) + 32, cudaHostAllocDefault));
+        std::memset(nt, 0, size_t(newCap) + 32);
+        if (v->trackBuf[i]) {
+            if (v->pullBusy[i]) cudaEventSynchronize(v->pullDone[i]);
+            v->pullBusy[i] = false;
+            std::memcpy(nt, v->trackBuf[i], v->count);
+            cudaFreeHost(v->trackBuf[i]);
+        }
+        v->trackBuf[i] = nt;
+    }
+    v->track = v->trackBuf[v->cur];
+    v->capacity = newCap;
+    return 0;
+}
+
+// The reference's range computation (src/BufferedVRAMVector.cpp:108-139); clean spans are skipped eight flags at a
+// time while no range is open (same result: they neither open nor close a range). The flags are cleared by the
+// caller, range by range (the reference clears them inside this loop; every set flag lies inside some range).
+void compute_ranges(const uint8_t* track, uint32_t n, std::vector<uint32_t>& out) {
+    out.clear();
+    int gap = 0;
+    uint32_t begin = 0, i = 0;
+    while (i < n) {
+        if (gap == 0 && (i & 7u) == 0) {
+            while (i + 8 <= n) {
+                uint64_t w;
+                std::memcpy(&w, track + i, 8);
+                if (w) break;
+                i += 8;
+            }
+            if (i >= n) break;
+        }
+        if (track[i]) {
+            if (gap == 0) begin = i;
+            gap = kMaxGapSize;
+        } else {
+            const int prev = gap;
+            gap = gap > 0 ? gap - 1 : 0;
+            if (gap == 0 && prev != 0) {
+                out.push_back(begin);
+                out.push_back(i);
+            }
+        }
+        ++i;
+    }
+    if (gap != 0) {
+        out.push_back(begin);
+        out.push_back(n);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int rvs_vector_create(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, rvs_vector** out) {
+    if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(elem_bytes == 2 || (elem_bytes % 4 == 0 && elem_bytes > 0), "element size must be 2 or a multiple of 4 bytes");
+    auto* v = new rvs_vector();
+    v->ctx = ctx;
+    v->elemBytes = elem_bytes;
+    {
+        DeviceGuard g(ctx->device);
+        if (cudaEventCreateWithFlags(&v->stageFree, cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&v->pullDone[0], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&v->pullDone[1], cudaEventDisableTiming) != cudaSuccess ||
+            cudaMalloc(reinterpret_cast<void**>(&v->pullRows), sizeof(uint32_t)) != cudaSuccess ||
+            cudaMemsetAsync(v->pullRows, 0, sizeof(uint32_t), ctx->stream) != cudaSuccess) {
+            delete v;
+            return set_error(RVE_ERR_CUDA, "rvs_vector_create: CUDA resource creation failed");
+        }
+    }
+    *out = v;
+    return count ? rvs_vector_resize(v, count) : 0;
+}
+
+int rvs_vector_destroy(rvs_vector* v) {
+    if (!v) return 0;
+    DeviceGuard g(v->ctx->device);
+    cudaStreamSynchronize(v->ctx->stream);
+    if (v->priv != RVE_BUFFER_INVALID) rve_buffer_destroy(v->ctx, v->priv);
+    if (v->stageDev != RVE_BUFFER_INVALID) rve_buffer_destroy(v->ctx, v->stageDev);
+    if (v->host) cudaFreeHost(v->host);
+    if (v->stageHost) cudaFreeHost(v->stageHost);
+    if (v->stageFree) cudaEventDestroy(v->stageFree);
+    for (int i = 0; i < 2; ++i) {
+        if (v->trackBuf[i]) cudaFreeHost(v->trackBuf[i]);
+        if (v->pullDone[i]) cudaEventDestroy(v->pullDone[i]);
+    }
+    if (v->pullRows) cudaFree(v->pullRows);
+    delete v;
+    return 0;
+}
+
+// BufferedVRAMVector::Resize (BufferedVRAMVector.hpp:64-69): new elements start out modified
+int rvs_vector_resize(rvs_vector* v, uint32_t count) {
+    if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
+    if (count == v->count) return 0;
+    if (count > v->capacity) {
+        const int rc = vec_reserve(v, next_pow2(count));
+        if (rc) return rc;
+    }
+    const uint32_t old = v->count;
+    if (count > old) {
+        std::memset(v->host + size_t(old) * v->elemBytes, 0, size_t(count - old) * v->elemBytes);
+        std::memset(v->track + old, 1, count - old);
+    } else {
+        std::memset(v->track + count, 0, old - count);
+    }
+    v->count = count;
+    return 0;
+}
+
+uint32_t rvs_vector_size(rvs_vector* v) { return v ? v->count : 0; }
+void* rvs_vector_host(rvs_vector* v) { return v ? v->host : nullptr; }
+uint8_t* rvs_vector_tracking(rvs_vector* v) { return v ? v->track : nullptr; }
+rve_buffer rvs_vector_private_buffer(rvs_vector* v) { return v ? v->priv : RVE_BUFFER_INVALID; }
+
+// SetValueAt (BufferedVRAMVector.hpp:113-116)
+int rvs_vector_set(rvs_vector* v, uint32_t index, const void* value) {
+    if (!v || !value) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(index < v->count, "index out of range");
+    std::memcpy(v->host + size_t(index) * v->elemBytes, value, v->elemBytes);
+    v->track[index] = 1;
+    return 0;
+}
+
+// GetValueAtForWriting over [begin, end): the caller writes through rvs_vector_host()
+int rvs_vector_mark(rvs_vector* v, uint32_t begin, uint32_t end) {
+    if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
+    RVE_REQUIRE(begin <= end && end <= v->count, "range out of bounds");
+    std::memset(v->track + begin, 1, end - begin);
+    return 0;
+}
+
+// rows copied by RVS_SYNC_PULL syncs since creation (reads a device counter: synchronises the stream)
+uint64_t rvs_vector_pulled_rows(rvs_vector* v) {
+    if (!v || !v->pullRows) return 0;
+    DeviceGuard g(v->ctx->device);
+    uint32_t r = 0;
+    if (cudaMemcpyAsync(&r, v->pullRows, sizeof(r), cudaMemcpyDeviceToHost, v->ctx->stream) != cudaSuccess) return 0;
+    cudaStreamSynchronize(v->ctx->stream);
+    return r;
+}
+
+uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max_pairs) {
+    if (!v) return 0;
+    const uint32_t n = uint32_t(v->ranges.size() / 2);
+    for (uint32_t i = 0; i < n && i < max_pairs; ++i) {
+        out_pairs[2 * i] = v->ranges[2 * i];
+        out_pairs[2 * i + 1] = v->ranges[2 * i + 1];
+    }
+    return n;
+}
+
+// BufferedVRAMStructureBase::EncodeSync (src/BufferedVRAMVector.cpp:27-144)
+int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_rows, rvs_sync_stats* stats) {
+    if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
+    RVE_REQUIRE(mode == RVS_SYNC_RANGES || mode == RVS_SYNC_PACKED || mode == RVS_SYNC_PULL, "unknown sync mode");
+    rve_ctx* ctx = v->ctx;
+    DeviceGuard g(ctx->device);
+    rvs_sync_stats st{};
+    const size_t eb = v->elemBytes;
+
+    // private buffer follows the host buffer's size; old contents are carried over (:31-81)
+    const size_t wantBytes = size_t(v->capacity) * eb;
+    if (wantBytes && (v->priv == RVE_BUFFER_INVALID || v->privBytes != wantBytes)) {
+        rve_buffer nb;
+        int rc = rve_buffer_create(ctx, wantBytes, &nb);
+        if (rc) return rc;
+        if (v->priv != RVE_BUFFER_INVALID) {
+            rc = rve_buffer_copy(ctx, v->priv, 0, nb, 0, v->privBytes < wantBytes ? v->privBytes : wantBytes);
+            if (rc) return rc;
+            rc = rve_buffer_destroy(ctx, v->priv);  // deferred to stream order, like gcBuffers
+            if (rc) return rc;
+        }
+        v->priv = nb;
+        v->privBytes = wantBytes;
+    }
+
+    if (mode == RVS_SYNC_PULL) {
+        v->ranges.clear();
+        if (v->count == 0) {
+            if (stats) *stats = st;
+            return 0;
+        }
+        auto* devp = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
+        if (!devp) return RVE_ERR_BAD_HANDLE;
+        const int rc = launch_pull(ctx, v->track, v->host, devp, v->count, v->elemBytes, v->pullRows);
+        if (rc) return rc;
+        RVE_CUDA(cudaEventRecord(v->pullDone[v->cur], ctx->stream));
+        v->pullBusy[v->cur] = true;
+        // the host records the next frame's modifications in the other flag block; the kernel that last read it
+        // (two syncs ago) must have finished clearing it
+        v->cur ^= 1;
+        if (v->pullBusy[v->cur]) RVE_CUDA(cudaEventSynchronize(v->pullDone[v->cur]));
+        v->pullBusy[v->cur] = false;
+        v->track = v->trackBuf[v->cur];
+        st.packed_bytes = uint64_t(v->count);  // flag bytes the kernel reads; row bytes depend on the flags (rvs_vector_pulled_rows)
+        if (stats) *stats = st;
+        return 0;
+    }
+
+    compute_ranges(v->track, v->count, v->ranges);
+    const uint32_t nRanges = uint32_t(v->ranges.size() / 2);
+    st.ranges = nRanges;
+    if (nRanges == 0) {
+        if (stats) *stats = st;
+        return 0;
+    }
+    auto* dev = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
+    if (!dev) return RVE_ERR_BAD_HANDLE;
+
+    uint64_t packedRows = 0;
+    for (uint32_t r = 0; r < nRanges; ++r) {
+        const uint32_t len = v->ranges[2 * r + 1] - v->ranges[2 * r];
+        st.rows_in_ranges += len;
+        if (mode == RVS_SYNC_PACKED && len < direct_min_rows)
+            for (uint32_t k = v->ranges[2 * r]; k < v->ranges[2 * r + 1]; ++k) packedRows += v->track[k] ? 1u : 0u;
+    }
+    unsigned char* rowsDst = nullptr;
+    uint32_t* idxDst = nullptr;
+    size_t idxOffset = 0;
+    if (packedRows) {
+        RVE_REQUIRE(packedRows <= 0xFFFFFFFFull, "too many packed rows");
+        idxOffset = (size_t(packedRows) * eb + 15) & ~size_t(15);
+        const size_t need = idxOffset + size_t(packedRows) * 4;
+        if (need > v->stageHostBytes) {
+            if (v->stageBusy) RVE_CUDA(cudaEventSynchronize(v->stageFree));
+            v->stageBusy = false;
+            if (v->stageHost) cudaFreeHost(v->stageHost);
+            const size_t cap = need + need / 2;
+            RVE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&v->stageHost), cap, cudaHostAllocDefault));
+            v->stageHostBytes = cap;
+        }
+        if (need > v->stageDevBytes) {
+            if (v->stageDev != RVE_BUFFER_INVALID) rve_buffer_destroy(ctx, v->stageDev);
+            const size_t cap = need + need / 2;
+            const int rc = rve_buffer_create(ctx, cap, &v->stageDev);
+            if (rc) return rc;
+            v->stageDevBytes = cap;
+        }
+        if (v->stageBusy) RVE_CUDA(cudaEventSynchronize(v->stageFree));  // previous upload consumed the block
+        v->stageBusy = false;
+        rowsDst = v->stageHost;
+        idxDst = reinterpret_cast<uint32_t*>(v->stageHost + idxOffset);
+    }
+    uint64_t pr = 0;
+    for (uint32_t r = 0; r < nRanges; ++r) {
+        const uint32_t b = v->ranges[2 * r], e = v->ranges[2 * r + 1], len = e - b;
+        if (mode == RVS_SYNC_PACKED && len < direct_min_rows) {
+            for (uint32_t k = b; k < e; ++k)
+                if (v->track[k]) {
+                    std::memcpy(rowsDst + pr * eb, v->host + size_t(k) * eb, eb);
+                    idxDst[pr++] = k;
+                }
+        } else {
+            RVE_CUDA(cudaMemcpyAsync(dev + size_t(b) * eb, v->host + size_t(b) * eb, size_t(len) * eb, cudaMemcpyHostToDevice, ctx->stream));
+            st.direct_copies++;
+            st.direct_bytes += uint64_t(len) * eb;
+        }
+        std::memset(v->track + b, 0, len);
+    }
+    if (packedRows) {
+        auto* sdev = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->stageDev));
+        const size_t bytes = idxOffset + size_t(packedRows) * 4;
+        RVE_CUDA(cudaMemcpyAsync(sdev, v->stageHost, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        RVE_CUDA(cudaEventRecord(v->stageFree, ctx->stream));
+        v->stageBusy = true;
+        const int rc = rve_scatter_rows(ctx, v->priv, v->elemBytes, v->stageDev, idxOffset, 0, uint32_t(packedRows));
+        if (rc) return rc;
+        st.packed_rows = uint32_t(packedRows);
+        st.packed_bytes = bytes;
+    }
+    if (stats) *stats = st;
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,77 @@
+"""BufferedVRAMVector mirror (include/RavEngine/BufferedVRAMVector.hpp:33-209): a host-shared array with
+per-element modification flags and a device-private copy, synchronised by EncodeSync
+(src/BufferedVRAMVector.cpp:27-144). Marshalling only: the scan, the copies and the scatter kernel
+live in librve_b200.so (csrc/sync.cu)."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _abi
+from .api import Buffer, Context, _check
+
+SYNC_RANGES, SYNC_PACKED, SYNC_PULL = _abi.SYNC_RANGES, _abi.SYNC_PACKED, _abi.SYNC_PULL
+
+
+class BufferedVRAMVector:
+    def __init__(self, ctx: Context, elem_bytes: int, count: int = 0):
+        self.ctx, self.elem_bytes = ctx, elem_bytes
+        h = C.c_void_p()
+        _check(ctx.lib, ctx.lib.rvs_vector_create(ctx.h, elem_bytes, count, C.byref(h)))
+        self.h = h
+
+    def __len__(self) -> int:
+        return self.ctx.lib.rvs_vector_size(self.h)
+
+    def resize(self, count: int) -> None:
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_resize(self.h, count))
+
+    def host(self, dtype=np.uint8) -> np.ndarray:
+        """GetHostBuffer(): a view of the pinned host block (invalid after the next growth)."""
+        n = len(self) * self.elem_bytes
+        if n == 0:
+            return np.empty(0, dtype)
+        raw = (C.c_uint8 * n).from_address(self.ctx.lib.rvs_vector_host(self.h))
+        return np.frombuffer(raw, dtype=dtype)
+
+    def tracking(self) -> np.ndarray:
+        n = len(self)
+        if n == 0:
+            return np.empty(0, np.uint8)
+        raw = (C.c_uint8 * n).from_address(self.ctx.lib.rvs_vector_tracking(self.h))
+        return np.frombuffer(raw, dtype=np.uint8)
+
+    def set_value_at(self, i: int, value: np.ndarray) -> None:
+        value = np.ascontiguousarray(value)
+        assert value.nbytes == self.elem_bytes
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_set(self.h, i, value.ctypes.data))
+
+    def mark(self, begin: int, end: int) -> None:
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_mark(self.h, begin, end))
+
+    def encode_sync(self, mode: int = SYNC_PACKED, direct_min_rows: int = 256) -> _abi.SyncStats:
+        st = _abi.SyncStats()
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_encode_sync(self.h, mode, direct_min_rows, C.byref(st)))
+        return st
+
+    def pulled_rows(self) -> int:
+        return int(self.ctx.lib.rvs_vector_pulled_rows(self.h))
+
+    def last_ranges(self) -> np.ndarray:
+        n = self.ctx.lib.rvs_vector_last_ranges(self.h, None, 0)
+        out = np.zeros((n, 2), np.uint32)
+        if n:
+            self.ctx.lib.rvs_vector_last_ranges(self.h, out.ctypes.data_as(C.POINTER(C.c_uint32)), n)
+        return out
+
+    @property
+    def private_buffer(self) -> Buffer:
+        """GetPrivateBuffer(): ask again after every encode_sync (growth replaces it, like the reference)."""
+        h = self.ctx.lib.rvs_vector_private_buffer(self.h)
+        return Buffer(self.ctx, h, self.ctx.lib.rve_buffer_size(self.ctx.h, h))
+
+    def destroy(self) -> None:
+        if self.h:
+            self.ctx.lib.rvs_vector_destroy(self.h)
+            self.h = None

@@ -1,0 +1,116 @@
+"""Dirty-range upload: the range scan against the restated reference loop
+(src/BufferedVRAMVector.cpp:106-139), and - on the GPU - both sync modes leaving the private buffer
+byte-identical to the host buffer."""
+import numpy as np
+import pytest
+
+from oracle import host_tables
+
+
+def ranges_of(flags):
+    return host_tables.sync_ranges(np.array(flags, np.uint8)).tolist()
+
+
+def test_range_scan_known_answers():
+    # a single dirty element drags maxGapSize-1 clean ones along: closed at the index of the 5th clean flag
+    assert ranges_of([1, 0, 0, 0, 0, 0, 0, 0]) == [[0, 5]]
+    # a second dirty element inside the gap window extends the range ...
+    assert ranges_of([1, 0, 0, 0, 0, 1]) == [[0, 6]]
+    # ... one flag later it opens a new one
+    assert ranges_of([1, 0, 0, 0, 0, 0, 1]) == [[0, 5], [6, 7]]
+    assert ranges_of([0, 0, 0]) == []
+    assert ranges_of([]) == []
+    assert ranges_of([0, 0, 1]) == [[2, 3]]
+    assert ranges_of([1] * 9) == [[0, 9]]
+    # range still open at the end of the array
+    assert ranges_of([0, 1, 0, 0]) == [[1, 4]]
+
+
+def test_range_scan_clears_flags():
+    t = np.array([0, 1, 1, 0, 0, 0, 0, 0, 0, 1], np.uint8)
+    r = host_tables.sync_ranges(t)
+    assert r.tolist() == [[1, 7], [9, 10]]
+    assert not t.any()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("elem_bytes,dtype", [(64, np.float32), (4, np.uint32), (2, np.uint16), (12, np.float32)])
+@pytest.mark.parametrize("density", [0.0, 0.001, 0.05, 0.6, 1.0])
+def test_sync_modes_match_host(ctx, elem_bytes, dtype, density):
+    from ravengine_b200.vram_vector import SYNC_PACKED, SYNC_PULL, SYNC_RANGES, BufferedVRAMVector
+
+    rng = np.random.default_rng(int(density * 1000) + elem_bytes)
+    n = 50_003
+    per = elem_bytes // np.dtype(dtype).itemsize
+    for mode in (SYNC_RANGES, SYNC_PACKED, SYNC_PULL):
+        v = BufferedVRAMVector(ctx, elem_bytes, n)
+        h = v.host(dtype).reshape(n, per)
+        h[:] = rng.integers(0, 60000, size=(n, per)).astype(dtype)
+        st = v.encode_sync(mode, 64)  # Resize marked everything: one range
+        assert mode == SYNC_PULL or (st.ranges == 1 and st.rows_in_ranges == n)
+        pulled = n
+        assert np.array_equal(v.private_buffer.download(dtype).reshape(-1, per)[:n], h)
+        for frame in range(3):
+            dirty = rng.random(n) < density
+            if frame == 1:
+                dirty[1000:3000] = True  # one long run: goes by direct copy in packed mode
+            idx = np.nonzero(dirty)[0]
+            h[idx] = rng.integers(0, 60000, size=(len(idx), per)).astype(dtype)
+            v.tracking()[idx] = 1
+            expect = host_tables.sync_ranges(dirty.astype(np.uint8))
+            st = v.encode_sync(mode, 64)
+            if mode == SYNC_PULL:  # no host scan: the kernel consumed (and cleared) the flags it was handed
+                pulled += len(idx)
+                assert np.array_equal(v.private_buffer.download(dtype).reshape(-1, per)[:n], h)
+                assert v.pulled_rows() == pulled
+                assert not v.tracking().any()
+                continue
+            assert np.array_equal(v.last_ranges(), expect)
+            assert st.ranges == len(expect)
+            assert not v.tracking().any()
+            if mode == SYNC_RANGES:
+                assert st.packed_rows == 0 and st.direct_copies == len(expect)
+            else:
+                lens = expect[:, 1] - expect[:, 0] if len(expect) else np.zeros(0, np.uint32)
+                assert st.direct_copies == int((lens >= 64).sum())
+                short = expect[lens < 64]
+                assert st.packed_rows == sum(int(dirty[b:e].sum()) for b, e in short)
+            assert np.array_equal(v.private_buffer.download(dtype).reshape(-1, per)[:n], h)
+        v.destroy()
+
+
+@pytest.mark.gpu
+def test_growth_keeps_contents_and_marks_new_rows(ctx):
+    from ravengine_b200.vram_vector import SYNC_PACKED, BufferedVRAMVector
+
+    v = BufferedVRAMVector(ctx, 64, 1000)
+    a = v.host(np.float32).reshape(-1, 16)
+    a[:] = np.arange(16000, dtype=np.float32).reshape(-1, 16)
+    v.encode_sync(SYNC_PACKED)
+    before = a.copy()  # the view dies with the old pinned block at the next growth
+    v.set_value_at(7, np.full(16, -1.0, np.float32))
+    before[7] = -1.0
+    v.resize(5000)  # capacity 1024 -> 8192: new pinned block, new private buffer, old rows carried over
+    b = v.host(np.float32).reshape(-1, 16)
+    assert np.array_equal(b[:1000], before)
+    b[1000:] = 3.5
+    st = v.encode_sync(SYNC_PACKED)
+    assert st.ranges == 2  # row 7 (+ gap tail) and the 4000 new rows
+    got = v.private_buffer.download(np.float32).reshape(-1, 16)[:5000]
+    assert np.array_equal(got, b)
+    assert got[7, 0] == -1.0 and got[4999, 15] == 3.5
+    # the same through the GPU-pull mode, across another growth
+    from ravengine_b200.vram_vector import SYNC_PULL
+
+    keep = b.copy()
+    v.resize(20000)
+    c = v.host(np.float32).reshape(-1, 16)
+    c[5000:] = -7.25
+    c[11] = 42.0
+    v.tracking()[11] = 1
+    v.encode_sync(SYNC_PULL)
+    got = v.private_buffer.download(np.float32).reshape(-1, 16)[:20000]
+    keep[11] = 42.0
+    assert np.array_equal(got[:5000], keep) and np.all(got[5000:] == -7.25)
+    assert v.pulled_rows() == 15001
+    v.destroy()
