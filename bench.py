@@ -235,10 +235,11 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     n = args.instances
     sc = DeviceScene(n, rank, local_rank)
     ex = None
-    if world_size > 1:
+    if world_size > 1 or args.force_exchange:
         from ravengine_b200.sharding import ShardedCull
 
-        ex = ShardedCull(sc.ctx, sc.world, sc.mats, [len(C2["lod_distances"])] * len(sc.mats), world_size, sc.stream)
+        ex = ShardedCull(sc.ctx, sc.world, sc.mats, [len(C2["lod_distances"])] * len(sc.mats), world_size, sc.stream, rank=rank,
+                         exchange=args.exchange)
 
     def barrier():
         if dist:
@@ -252,27 +253,32 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
 
     for _ in range(max(args.warmup, 3)):
         one_step()
-    barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
-        sampler.start()
+        sampler.start()  # before the barrier: spawning nvidia-smi takes milliseconds and would skew rank 0's start
+    barrier()
     launches0 = sc.ctx.launch_count
     ex_launches0 = ex.launch_count if ex else 0
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(sc.stream)
+    t_host0 = time.perf_counter()
     for _ in range(args.steps):
         one_step()
     if ex:
         ex.finish()  # the side stream's count exchange + offset scan belong to the timed region
     ev1.record(sc.stream)
+    host_enqueue_ms = (time.perf_counter() - t_host0) * 1e3 / args.steps  # CPU time to enqueue one step (no sync inside)
     barrier()
     launches = sc.ctx.launch_count - launches0 + (ex.launch_count - ex_launches0 if ex else 0)
     ms_total = ev0.elapsed_time(ev1)
     clocks = sampler.stop() if rank == 0 else None
+    by_rank = [ms_total / args.steps]
     if dist:
         t = torch.tensor([ms_total], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
+        allt = torch.zeros(world_size, device="cuda")
+        dist.all_gather_into_tensor(allt, t)
+        by_rank = [float(x) / args.steps for x in allt.tolist()]
+        ms_total = float(allt.max().item())  # MAX over ranks
     ms_step = ms_total / args.steps
     counts = sc.visible_counts()
     visible = int(counts.sum())
@@ -285,6 +291,11 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     pyr_ms, pyr_n = sc.ctx.profile_read(1)
     sc.ctx.set_profiling(False)
     cull_avg_ms = cull_ms / max(cull_n, 1)
+    cull_by_rank = [cull_avg_ms]
+    if dist:
+        allk = torch.zeros(world_size, device="cuda")
+        dist.all_gather_into_tensor(allk, torch.tensor([cull_avg_ms], device="cuda"))
+        cull_by_rank = [float(x) for x in allk.tolist()]
     peak, peak_src = peaks()
     pyr_bytes = 4 * (4 * sc.pyr.dim ** 2 - 1) // 3
     algo_bytes = n * BYTES_PER_INSTANCE + visible * 4 + 36 * C2["materials"] + 20 * sc.slots + pyr_bytes
@@ -320,13 +331,15 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                                "1024^2 pyramid, rebuilt every step) + LOD + indirect compaction",
                    "instances_per_gpu": n, "ids": "identity order", "visible": visible,
                    "l2": "inputs (74 B x 10M = 740 MB) exceed the 126 MB L2; no explicit flush",
-                   "sharding": "instance range per rank; per-slot counts all-gathered with NCCL + device offset scan"
-                   if world_size > 1 else "single GPU"},
+                   "sharding": ("instance range per rank; per-slot counts exchanged by "
+                                + ("one kernel over NVLink peer memory (peer stores + flags + scan)" if ex and ex.mode == "p2p"
+                                   else "NCCL all-gather + device offset scan")) if world_size > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "kernel": "cull_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": cull_avg_ms,
                      "frac_of_8000_datasheet": achieved / 8000.0, "pyramid_kernel_ms": pyr_ms / max(pyr_n, 1)},
-        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks,
+        "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
+        "ms_per_step_by_rank": by_rank, "cull_kernel_ms_by_rank": cull_by_rank,
         "visible_per_slot": counts.tolist(),
     }
     if cpu:
@@ -447,6 +460,8 @@ def main():
     ap.add_argument("--instances", type=int, default=C2["instances"], help="instances per GPU")
     ap.add_argument("--cpu-sample", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--force-exchange", action="store_true", help="N=1: run the count exchange machinery anyway (diagnostics)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: per-slot count exchange")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))

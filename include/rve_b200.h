@@ -366,6 +366,22 @@ RVE_API int rve_gather_instance_counts_multi(rve_ctx* ctx, const rve_buffer* ind
                                              const uint32_t* num_slots, uint32_t n_buffers, rve_buffer counts_out,
                                              size_t counts_offset_bytes);
 
+/* The exchange step as ONE kernel over NVLink peer memory (no NCCL call): every rank owns a mailbox buffer of
+ * rve_count_mailbox_bytes(world, slots) bytes, zero-filled once, created with rve_buffer_create and made visible
+ * to its peers with rve_ipc_export / rve_ipc_import (CUDA IPC; one process per GPU). The kernel takes this rank's
+ * counts (from `n_buffers` indirect buffers like rve_gather_instance_counts_multi, or - n_buffers == 0 - from the
+ * dense u32[dense_slots] array `dense_counts`), stores them into every rank's mailbox, signals, waits for every
+ * peer's signal of the same `epoch` (1, 2, 3, ... - one per exchange, the same on all ranks) and writes
+ * offsets_out[world][slots] (exclusive scan over ranks) and totals_out[slots]. mailboxes[q] is rank q's mailbox
+ * (mailboxes[rank] = the local one). status (u32) is set to 1 if a peer did not arrive within ~2 s. world <= 8. */
+RVE_API size_t rve_count_mailbox_bytes(uint32_t world, uint32_t total_slots);
+RVE_API int rve_ipc_export(rve_ctx* ctx, rve_buffer buf, unsigned char out_handle[64]);
+RVE_API int rve_ipc_import(rve_ctx* ctx, const unsigned char handle[64], size_t bytes, rve_buffer* out);
+RVE_API int rve_exchange_counts_p2p(rve_ctx* ctx, const rve_buffer* indirect, const uint32_t* first_slot,
+                                    const uint32_t* num_slots, uint32_t n_buffers, rve_buffer dense_counts,
+                                    uint32_t dense_slots, const rve_buffer* mailboxes, uint32_t rank, uint32_t world,
+                                    uint32_t epoch, rve_buffer offsets_out, rve_buffer totals_out, rve_buffer status);
+
 /* ------------------------------------------------------------------ */
 /* synthetic scene generation on the device (bench / C5)  */
 /* ------------------------------------------------------------------ */

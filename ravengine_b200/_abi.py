@@ -110,6 +110,11 @@ PROTOTYPES = {
     "rve_shard_offsets": (C.c_int, [VP, u32, u32, u32, u32, u32]),
     "rve_gather_instance_counts": (C.c_int, [VP, u32, u32, u32, u32, C.c_size_t]),
     "rve_gather_instance_counts_multi": (C.c_int, [VP, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), u32, u32, C.c_size_t]),
+    "rve_count_mailbox_bytes": (C.c_size_t, [u32, u32]),
+    "rve_ipc_export": (C.c_int, [VP, u32, VP]),
+    "rve_ipc_import": (C.c_int, [VP, VP, C.c_size_t, C.POINTER(u32)]),
+    "rve_exchange_counts_p2p": (C.c_int, [VP, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), u32, u32, u32, C.POINTER(u32), u32, u32, u32,
+                                          u32, u32, u32]),
     "rve_scatter_rows": (C.c_int, [VP, u32, u32, u32, u64, u64, u32]),
     "rve_gen_instances": (C.c_int, [VP, C.POINTER(SceneGenParams), u64, u32, u32, u32, u32, u32]),
 }

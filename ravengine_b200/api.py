@@ -175,6 +175,27 @@ class Context:
     def shard_offsets(self, counts_all: Buffer, world: int, slots: int, offsets: Buffer, totals: Buffer) -> None:
         _check(self.lib, self.lib.rve_shard_offsets(self.h, counts_all.handle, world, slots, offsets.handle, totals.handle))
 
+    # ---- peer-memory count exchange (csrc/p2p.cu) ----
+    def ipc_export(self, buf: Buffer) -> bytes:
+        h = (C.c_uint8 * 64)()
+        _check(self.lib, self.lib.rve_ipc_export(self.h, buf.handle, h))
+        return bytes(h)
+
+    def ipc_import(self, handle: bytes, nbytes: int) -> Buffer:
+        raw = (C.c_uint8 * 64).from_buffer_copy(handle)
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rve_ipc_import(self.h, raw, nbytes, C.byref(out)))
+        return Buffer(self, out.value, nbytes)
+
+    def mailbox_bytes(self, world: int, slots: int) -> int:
+        return int(self.lib.rve_count_mailbox_bytes(world, slots))
+
+    def exchange_counts_p2p(self, dense_counts: Buffer, slots: int, mailboxes: list[Buffer], rank: int, world: int, epoch: int,
+                            offsets: Buffer, totals: Buffer, status: Buffer) -> None:
+        m = (C.c_uint32 * world)(*[b.handle for b in mailboxes])
+        _check(self.lib, self.lib.rve_exchange_counts_p2p(self.h, None, None, None, 0, dense_counts.handle, slots, m, rank, world, epoch,
+                                                          offsets.handle, totals.handle, status.handle))
+
     def gather_instance_counts(self, indirect: Buffer, first_slot: int, slots: int, out: Buffer, out_off: int = 0) -> None:
         _check(self.lib, self.lib.rve_gather_instance_counts(self.h, indirect.handle, first_slot, slots, out.handle, out_off))
 

@@ -128,7 +128,10 @@ class ShardedCull:
     double-buffered; `finish()` joins the side stream (call it before reading offsets / totals, or at frame end).
     Nothing synchronises with the host."""
 
-    def __init__(self, ctx, world_obj, materials: list[int], lods_per_material: list[int], world_size: int, torch_stream):
+    def __init__(self, ctx, world_obj, materials: list[int], lods_per_material: list[int], world_size: int, torch_stream,
+                 rank: int = 0, exchange: str = "auto"):
+        """exchange: "p2p" = one kernel over NVLink peer memory (csrc/p2p.cu: peer stores + flags + scan, no NCCL call),
+        "nccl" = all-gather + scan kernel, "auto" = p2p when every rank could map its peers' mailboxes."""
         import torch
 
         from .api import Context
@@ -136,7 +139,10 @@ class ShardedCull:
         self.ctx, self.world_obj, self.mats, self.lods, self.ws, self.stream = ctx, world_obj, materials, lods_per_material, world_size, torch_stream
         self.slots = sum(lods_per_material)
         dev = torch.device("cuda", ctx.device)
-        self.side = torch.cuda.Stream(device=dev)
+        import os
+
+        self.inline = os.environ.get("RVE_EXCHANGE_INLINE") == "1"  # diagnostics: exchange on the cull's own stream
+        self.side = torch_stream if self.inline else torch.cuda.Stream(device=dev)
         self.ctx2 = Context(ctx.device, self.side.cuda_stream)  # same device memory, enqueues on the side stream
         self.t_local, self.t_all, self.t_off, self.t_tot = [], [], [], []
         self.b_local, self.b_all, self.b_off, self.b_tot, self.done = [], [], [], [], [None, None]
@@ -154,6 +160,43 @@ class ShardedCull:
             self.b_tot.append(self.ctx2.wrap_tensor(self.t_tot[i]))
         self.k = 0
         self._indirect = None
+        self.rank, self.mode = rank, "nccl"
+        if world_size > 1 and exchange in ("auto", "p2p"):
+            self._setup_p2p(strict=exchange == "p2p")
+
+    def _setup_p2p(self, strict: bool) -> None:
+        """Mailboxes: one cudaMalloc block per rank, zero-filled, exchanged as CUDA IPC handles through the process group."""
+        import torch
+        import torch.distributed as dist
+
+        nbytes = self.ctx2.mailbox_bytes(self.ws, self.slots)
+        ok, err = 1, ""
+        try:
+            self.mailbox = self.ctx2.create_buffer(nbytes)
+            self.mailbox.zero()
+            self.status = self.ctx2.create_buffer(16)
+            self.status.zero()
+            self.ctx2.synchronize()
+            handle = self.ctx2.ipc_export(self.mailbox)
+        except Exception as e:  # noqa: BLE001 - reported below, every rank must take the same branch
+            ok, err, handle = 0, str(e), b""
+        handles = [None] * self.ws
+        dist.all_gather_object(handles, (ok, handle))
+        peers = []
+        if all(h[0] for h in handles):
+            try:
+                for q, (_, h) in enumerate(handles):
+                    peers.append(self.mailbox if q == self.rank else self.ctx2.ipc_import(h, nbytes))
+            except Exception as e:  # noqa: BLE001
+                ok, err = 0, str(e)
+        else:
+            ok = 0
+        flag = torch.tensor([ok], dtype=torch.int32, device=torch.device("cuda", self.ctx.device))
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
+            self.peers, self.mode = peers, "p2p"
+        elif strict:
+            raise RuntimeError(f"peer-memory count exchange unavailable: {err}")
 
     def _indirect_buffers(self):
         bufs = [self.world_obj.material_outputs(m)[1] for m in self.mats]
@@ -174,18 +217,32 @@ class ShardedCull:
         ev = torch.cuda.Event()
         ev.record(self.stream)
         self.side.wait_event(ev)
-        with torch.cuda.stream(self.side):
-            if self.ws > 1:
-                dist.all_gather_into_tensor(self.t_all[b].view(-1), self.t_local[b])
-            else:
-                self.t_all[b][0].copy_(self.t_local[b])
-        self.ctx2.shard_offsets(self.b_all[b], self.ws, self.slots, self.b_off[b], self.b_tot[b])
+        if self.mode == "p2p":
+            if not hasattr(self, "b_local2"):
+                self.b_local2 = [self.ctx2.wrap_tensor(t) for t in self.t_local]
+            self.ctx2.exchange_counts_p2p(self.b_local2[b], self.slots, self.peers, self.rank, self.ws, self.k, self.b_off[b],
+                                          self.b_tot[b], self.status)
+        else:
+            with torch.cuda.stream(self.side):
+                if self.ws > 1:
+                    dist.all_gather_into_tensor(self.t_all[b].view(-1), self.t_local[b])
+                else:
+                    self.t_all[b][0].copy_(self.t_local[b])
+            self.ctx2.shard_offsets(self.b_all[b], self.ws, self.slots, self.b_off[b], self.b_tot[b])
         self.done[b] = torch.cuda.Event()
         self.done[b].record(self.side)
         return b
 
     def finish(self) -> None:
         self.stream.wait_stream(self.side)
+
+    def timed_out(self) -> bool:
+        """True when a peer failed to arrive within the exchange kernel's timeout (p2p mode; synchronises)."""
+        if self.mode != "p2p":
+            return False
+        import numpy as np
+
+        return bool(self.status.download(np.uint32)[0])
 
     @property
     def launch_count(self) -> int:

@@ -214,3 +214,49 @@ def test_sharded_cull_single_rank_exchange(ctx):
     np.testing.assert_array_equal(out1.download(np.uint32), out2.download(np.uint32))
     np.testing.assert_array_equal(out1.download(np.uint32), want)
     w.destroy()
+
+
+@pytest.mark.gpu
+def test_p2p_count_exchange_two_ranks_on_one_device(ctx):
+    """csrc/p2p.cu: two 'ranks' (two streams of one device, mailboxes in the same memory) exchange per-slot counts in
+    one kernel each - peer stores, flags, exclusive scan - over several epochs; against numpy."""
+    import torch
+
+    from ravengine_b200 import Context
+
+    world, slots = 2, 7
+    s2 = torch.cuda.Stream()
+    ctxs = [ctx, Context(ctx.device, s2.cuda_stream)]
+    nbytes = ctx.mailbox_bytes(world, slots)
+    boxes = [ctx.create_buffer(nbytes) for _ in range(world)]
+    for b in boxes:
+        b.zero()
+    ctx.synchronize()
+    rng = np.random.default_rng(5)
+    # the other context sees the same device memory through wrapped pointers
+    def view(c, b):
+        import ctypes as C
+        out = C.c_uint32()
+        assert c.lib.rve_buffer_wrap(c.h, C.c_void_p(b.ptr), b.nbytes, C.byref(out)) == 0
+        from ravengine_b200.api import Buffer
+        return Buffer(c, out.value, b.nbytes)
+
+    per_rank = []
+    for r, c in enumerate(ctxs):
+        mb = boxes if r == 0 else [view(c, b) for b in boxes]
+        per_rank.append(dict(c=c, mb=mb, dense=c.create_buffer(slots * 4), off=c.create_buffer(world * slots * 4),
+                             tot=c.create_buffer(slots * 4), status=c.create_buffer(16)))
+        per_rank[-1]["status"].zero()
+    for epoch in range(1, 6):
+        counts = rng.integers(0, 1000, size=(world, slots)).astype(np.uint32)
+        for r, pr in enumerate(per_rank):
+            pr["dense"].upload(counts[r])
+        for r, pr in enumerate(per_rank):
+            pr["c"].exchange_counts_p2p(pr["dense"], slots, pr["mb"], r, world, epoch, pr["off"], pr["tot"], pr["status"])
+        expect_off = np.cumsum(counts, axis=0, dtype=np.uint32) - counts
+        for pr in per_rank:
+            pr["c"].synchronize()
+            assert pr["status"].download(np.uint32)[0] == 0
+            assert np.array_equal(pr["off"].download(np.uint32).reshape(world, slots), expect_off)
+            assert np.array_equal(pr["tot"].download(np.uint32), counts.sum(axis=0, dtype=np.uint32))
+    ctxs[1].close()
