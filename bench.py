@@ -307,11 +307,14 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         traffic, traffic_src = tj["traffic_bytes"], tj["source"]
 
     # --- e2e: host buffers through the shim, H2D + D2H inside the timed region ---
-    e2e = run_e2e(sc, args, torch, barrier, dist)
-    e2e["dirty_fraction"] = 1.0
-    e2e["by_dirty_fraction"] = run_e2e_dirty(sc, args, torch, barrier, dist)
-    e2e["by_dirty_fraction_note"] = ("same step with worldTransforms in a BufferedVRAMVector: only rows flagged since the last frame "
-                                     "are uploaded (the reference's EncodeSync policy, GPU-pull variant); keys = fraction of rows flagged per step")
+    if args.no_e2e:
+        e2e = None
+    else:
+        e2e = run_e2e(sc, args, torch, barrier, dist)
+        e2e["dirty_fraction"] = 1.0
+        e2e["by_dirty_fraction"] = run_e2e_dirty(sc, args, torch, barrier, dist)
+        e2e["by_dirty_fraction_note"] = ("same step with worldTransforms in a BufferedVRAMVector: only rows flagged since the last frame "
+                                         "are uploaded (the reference's EncodeSync policy, GPU-pull variant); keys = fraction of rows flagged per step")
 
     if rank != 0:
         if dist:
@@ -327,10 +330,11 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         "metric": "culled instances/s", "value": total_instances / (ms_step * 1e-3), "unit": "instances/s",
         "n_gpus": world_size, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2: 10M instances/GPU, 4 materials x 3 LODs {0,40,120}, frustum + Hi-Z (3840x2160 depth -> "
+        "config": {"workload": ("C2" if n == C2["instances"] else "C5 shard" if n >= 100_000_000 else "C2 distribution")
+                               + f": {n / 1e6:g}M instances/GPU, 4 materials x 3 LODs {{0,40,120}}, frustum + Hi-Z (3840x2160 depth -> "
                                "1024^2 pyramid, rebuilt every step) + LOD + indirect compaction",
                    "instances_per_gpu": n, "ids": "identity order", "visible": visible,
-                   "l2": "inputs (74 B x 10M = 740 MB) exceed the 126 MB L2; no explicit flush",
+                   "l2": f"inputs (74 B x {n / 1e6:g}M = {n * 74 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
                    "sharding": ("instance range per rank; per-slot counts exchanged by "
                                 + ("one kernel over NVLink peer memory (peer stores + flags + scan)" if ex and ex.mode == "p2p"
                                    else "NCCL all-gather + device offset scan")) if world_size > 1 else "single GPU"},
@@ -460,6 +464,7 @@ def main():
     ap.add_argument("--instances", type=int, default=C2["instances"], help="instances per GPU")
     ap.add_argument("--cpu-sample", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer e2e legs (C5-sized shards: 9 GB of pinned host memory per rank)")
     ap.add_argument("--force-exchange", action="store_true", help="N=1: run the count exchange machinery anyway (diagnostics)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: per-slot count exchange")
     args = ap.parse_args()
