@@ -149,3 +149,52 @@ def test_pyramid_sizes(ctx, size):
         ctx.build_pyramid(pyr, d, w, h)
     ctx.synchronize()
     np.testing.assert_array_equal(ref, pyr.texels.download(np.float32))
+
+
+def test_broken_id_runs_mix_all_staging_paths(ctx):
+    """Entity-id lists made of dense runs of 1..300 ids at arbitrary (unaligned) starts, in shuffled run order, over a
+    sparse entity space: one dispatch mixes 64-row TMA rounds, single dense halves, gathers, CUBO boundaries inside
+    rounds and a partial last round (csrc/cull.cu issue_round / load_round_ids)."""
+    rng = np.random.default_rng(11)
+    n_entities = 120_000
+    model = scenes.random_transforms(rng, n_entities, 300.0, 300.0)
+    layers = np.full(n_entities, 0xFFFFFFFF, np.uint32)
+    flags = np.full(n_entities, 0xFFFF, np.uint16)
+    layers[rng.random(n_entities) < 0.05] = 0
+    flags[rng.random(n_entities) < 0.1] &= 0xFFFC
+    runs, pos = [], 3  # entity 0..2 unused: the first run starts unaligned
+    while pos < n_entities - 400:
+        ln = int(rng.integers(1, 301))
+        runs.append(np.arange(pos, pos + ln, dtype=np.uint32))
+        pos += ln + int(rng.integers(0, 5))  # holes in the entity space
+    order = rng.permutation(len(runs))
+    cut = [0, len(runs) // 3, len(runs) // 3 + 1, 2 * len(runs) // 3, len(runs)]
+    mats = []
+    for i in range(4):
+        ids = np.concatenate([runs[j] for j in order[cut[i]:cut[i + 1]]])
+        mesh = scenes.simple_mesh(scenes.CUBE_RADIUS, (0.0, 60.0, 150.0) if i % 2 == 0 else (math.inf,), base=i * 1000)
+        mats.append(scenes.MaterialDraws([scenes.DrawCommand(mesh, ids)]))
+    cam = scenes.default_camera(z_far=1000.0)
+    depth = scenes.synth_depth(640, 360, cam, n_occluders=30)
+    _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=360)
+
+
+def test_c2_full_size_10m_matches_oracle(ctx):
+    """BASELINE config C2 at its full size: 10 M instances, 4 materials x 3 LODs, Hi-Z against the 3840x2160 pyramid,
+    scene generated by the shared (seed, index) generator; counts and sorted id slices against the oracle."""
+    from ravengine_b200 import SceneGenParams
+
+    n = 10_000_000
+    params = SceneGenParams(20240, 500.0, 50.0, 0.5, 2.0, 0.05, 0.05, 0)
+    model = np.zeros((n, 16), np.float32)
+    layers, flags, ids = np.zeros(n, np.uint32), np.zeros(n, np.uint16), np.zeros(n, np.uint32)
+    oracle.gen_instances(params, 0, n, model, layers, flags, ids)
+    mats = []
+    for i in range(4):
+        mesh = scenes.simple_mesh(1.7320508 if i % 2 == 0 else 1.74, (0.0, 40.0, 120.0))
+        mats.append(scenes.MaterialDraws([scenes.DrawCommand(mesh, ids[n * i // 4: n * (i + 1) // 4])]))
+    cam = scenes.default_camera(z_near=0.1, z_far=1000.0)
+    depth = scenes.synth_depth(3840, 2160, cam)
+    t, ref = _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=2160, nthreads=oracle.default_workers())
+    counts = np.concatenate([b.reshape(-1, 5)[:, 1] for b in ref if b is not None and b.dtype == np.uint32 and b.ndim == 2])
+    assert int(counts.sum()) == 2405721  # the bench's visible count for this seed
