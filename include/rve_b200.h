@@ -267,6 +267,15 @@ RVE_API int rve_buffer_wrap(rve_ctx* ctx, void* device_ptr, size_t bytes, rve_bu
 RVE_API int rve_buffer_destroy(rve_ctx* ctx, rve_buffer buf);
 /* IBuffer::SetBufferData / UpdateBufferData + staging CopyBufferToBuffer. */
 RVE_API int rve_buffer_upload(rve_ctx* ctx, rve_buffer buf, size_t dst_offset, const void* host_src, size_t bytes);
+/* Several small uploads in one stream operation (the reference records one CopyBufferToBuffer per table,
+ * src/RenderEngine_Draw.cpp:1321-1329, 1367-1375). Data is consumed before the call returns. */
+typedef struct rve_upload_segment {
+    rve_buffer dst;
+    size_t dst_offset;
+    const void* src;
+    size_t bytes;
+} rve_upload_segment;
+RVE_API int rve_buffer_upload_batch(rve_ctx* ctx, const rve_upload_segment* segs, uint32_t n);
 RVE_API int rve_buffer_download(rve_ctx* ctx, rve_buffer buf, size_t src_offset, void* host_dst, size_t bytes);
 /* ICommandBuffer::CopyBufferToBuffer — deps/RGL/include/RGL/CommandBuffer.hpp */
 RVE_API int rve_buffer_copy(rve_ctx* ctx, rve_buffer src, size_t src_offset, rve_buffer dst, size_t dst_offset, size_t bytes);

@@ -91,6 +91,7 @@ PROTOTYPES = {
     "rve_buffer_wrap": (C.c_int, [VP, VP, C.c_size_t, C.POINTER(u32)]),
     "rve_buffer_destroy": (C.c_int, [VP, u32]),
     "rve_buffer_upload": (C.c_int, [VP, u32, C.c_size_t, VP, C.c_size_t]),
+    "rve_buffer_upload_batch": (C.c_int, [VP, VP, u32]),
     "rve_buffer_download": (C.c_int, [VP, u32, C.c_size_t, VP, C.c_size_t]),
     "rve_buffer_copy": (C.c_int, [VP, u32, C.c_size_t, u32, C.c_size_t, C.c_size_t]),
     "rve_buffer_fill_zero": (C.c_int, [VP, u32, C.c_size_t, C.c_size_t]),

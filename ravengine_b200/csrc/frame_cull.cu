@@ -43,7 +43,9 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
     std::memset(cuboStaging.data(), 0, cuboStaging.size() * sizeof(RveCullingUBOinstance));
 
     uint32_t cuboIdx = 0;
-    std::vector<RveIndirectIndexedCommand> indirectStaging;
+    // every table of the pass goes out in one stream operation (rve_buffer_upload_batch) at the end
+    std::vector<std::vector<RveIndirectIndexedCommand>> indirectTables;
+    std::vector<rve_upload_segment> uploads;
     for (auto& m : w->materials) {
         if (!(m.kind & pass_mask)) continue;
         // :1265-1286 prepass
@@ -64,7 +66,8 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
         if (numLODs == 0) continue;
 
         // :1295-1320 initial populate of the drawcall buffer: one command per mesh per LOD
-        indirectStaging.assign(numLODs, RveIndirectIndexedCommand{0, 0, 0, 0, 0});
+        indirectTables.emplace_back(numLODs, RveIndirectIndexedCommand{0, 0, 0, 0, 0});
+        std::vector<RveIndirectIndexedCommand>& indirectStaging = indirectTables.back();
         {
             uint32_t meshID = 0, baseInstance = 0, lodBase = 0;
             for (auto& c : m.commands) {
@@ -82,8 +85,7 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
             }
         }
         // :1321-1329 CopyBufferToBuffer(indirectStagingBuffer -> indirectBuffer)
-        rc = rve_buffer_upload(ctx, m.indirectBuffer, 0, indirectStaging.data(), numLODs * sizeof(RveIndirectIndexedCommand));
-        if (rc) return rc;
+        uploads.push_back({m.indirectBuffer, 0, indirectStaging.data(), numLODs * sizeof(RveIndirectIndexedCommand)});
 
         // :1334-1362 one CUBO per command; offsets restart per material
         RveCullingUBOinstance cubo{};
@@ -104,7 +106,8 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
         }
     }
     // :1367-1375 copy to the cubo buffer
-    rc = rve_buffer_upload(ctx, w->cuboBuffer, 0, cuboStaging.data(), cuboStaging.size() * sizeof(RveCullingUBOinstance));
+    uploads.push_back({w->cuboBuffer, 0, cuboStaging.data(), cuboStaging.size() * sizeof(RveCullingUBOinstance)});
+    rc = rve_buffer_upload_batch(ctx, uploads.data(), uint32_t(uploads.size()));
     if (rc) return rc;
     // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
     const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));

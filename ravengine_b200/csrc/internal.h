@@ -82,7 +82,7 @@ PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h);
 int sync_table(rve_ctx* ctx);
 int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes);
 // (re)derives the footprint-min chain of a pyramid from its texels when they changed since the last derivation
-int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p);
+int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel = 0);
 // marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)
 void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf);
 

@@ -42,9 +42,8 @@ __device__ __forceinline__ float sample_min_src(const float* __restrict__ img, u
 }
 
 // reduce `lv` (n x n, shared) into `out` (n/2 x n/2, shared) and global level
-__device__ __forceinline__ void reduce_level(const float* lv, float* out, uint32_t n_out, float* __restrict__ gdst,
+__device__ __forceinline__ void reduce_level(const float* lv, uint32_t n_in, float* out, uint32_t n_out, float* __restrict__ gdst,
                                              uint32_t g_dim_out, uint32_t gx0, uint32_t gy0) {
-    const uint32_t n_in = n_out * 2;
     for (uint32_t i = threadIdx.x; i < n_out * n_out; i += blockDim.x) {
         const uint32_t x = i % n_out, y = i / n_out;
         const float a = lv[(2 * y) * n_in + 2 * x];
@@ -58,38 +57,57 @@ __device__ __forceinline__ void reduce_level(const float* lv, float* out, uint32
 }
 
 __global__ void __launch_bounds__(kPyrThreads)
-pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, float* __restrict__ pyr, uint32_t dim,
-                     uint32_t levels, uint32_t tile, uint32_t* __restrict__ ticket) {
-    // all in-tile levels back to back: tile^2 + (tile/2)^2 + ... + 1 <= 1365 floats
-    __shared__ float s_lv[(4 * kPyrTile * kPyrTile) / 3 + 2];
+pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
+                     uint32_t dim, uint32_t levels, uint32_t tile, uint32_t* __restrict__ ticket) {
+    // mip 0 of the tile plus one halo column / row ((tile+1)^2, stride tile+1), then the in-tile levels 1.. back to back
+    __shared__ float s_lv[(kPyrTile + 1) * (kPyrTile + 1) + (kPyrTile * kPyrTile) / 3 + 2];
     __shared__ bool s_last;
 
     const uint32_t tiles_per_row = dim / tile;
     const uint32_t tx0 = (blockIdx.x % tiles_per_row) * tile;
     const uint32_t ty0 = (blockIdx.x / tiles_per_row) * tile;
 
-    // mip 0 — depthpyramidcopy.fsh: texcoord = gl_FragCoord.xy / targetDim (pixel centres)
-    for (uint32_t i = threadIdx.x; i < tile * tile; i += blockDim.x) {
-        const uint32_t lx = i % tile, ly = i / tile;
-        const uint32_t x = tx0 + lx, y = ty0 + ly;
+    // mip 0 — depthpyramidcopy.fsh: texcoord = gl_FragCoord.xy / targetDim (pixel centres). The tile is sampled with
+    // one extra column and row (clamped at the image edge) so that level 0 of the footprint-min chain - 3/4 of it -
+    // is produced here, from shared memory, instead of by a second pass over the texels.
+    const uint32_t S = tile + 1;
+    for (uint32_t i = threadIdx.x; i < S * S; i += blockDim.x) {
+        const uint32_t lx = i % S, ly = i / S;
+        uint32_t x = tx0 + lx, y = ty0 + ly;
+        x = x < dim ? x : dim - 1;
+        y = y < dim ? y : dim - 1;
         const float u = (float(x) + 0.5f) / float(dim);
         const float v = (float(y) + 0.5f) / float(dim);
         const float m = sample_min_src(depth, w, h, u, v);
         s_lv[i] = m;
-        pyr[uint64_t(y) * dim + x] = m;
+        if (lx < tile && ly < tile) pyr[uint64_t(y) * dim + x] = m;
     }
     __syncthreads();
+    {   // footprint-min level 0: F[fy][fx] = min of texels {fx-1,fx} x {fy-1,fy} (clamped), (dim+1)^2 entries
+        const uint32_t n1 = dim + 1;
+        for (uint32_t i = threadIdx.x; i < tile * tile; i += blockDim.x) {
+            const uint32_t lx = i % tile + 1, ly = i / tile + 1;
+            fm[uint64_t(ty0 + ly) * n1 + (tx0 + lx)] =
+                gmin(gmin(s_lv[(ly - 1) * S + lx - 1], s_lv[(ly - 1) * S + lx]), gmin(s_lv[ly * S + lx - 1], s_lv[ly * S + lx]));
+        }
+        if (tx0 == 0)
+            for (uint32_t ly = threadIdx.x + 1; ly <= tile; ly += blockDim.x) fm[uint64_t(ty0 + ly) * n1] = gmin(s_lv[(ly - 1) * S], s_lv[ly * S]);
+        if (ty0 == 0)
+            for (uint32_t lx = threadIdx.x + 1; lx <= tile; lx += blockDim.x) fm[tx0 + lx] = gmin(s_lv[lx - 1], s_lv[lx]);
+        if (tx0 == 0 && ty0 == 0 && threadIdx.x == 0) fm[0] = s_lv[0];
+    }
 
     // mips 1..log2(tile) from shared memory — depthpyramid.csh
-    uint32_t in_off = 0, n = tile, level = 1;
+    uint32_t in_off = 0, n = tile, n_stride = S, level = 1;
     while (n > 1 && level < levels) {
         const uint32_t n_out = n / 2;
-        const uint32_t out_off = in_off + n * n;
-        reduce_level(s_lv + in_off, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level,
+        const uint32_t out_off = in_off + (level == 1 ? S * S : n * n);
+        reduce_level(s_lv + in_off, n_stride, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level,
                      tx0 >> level, ty0 >> level);
         __syncthreads();
         in_off = out_off;
         n = n_out;
+        n_stride = n_out;
         ++level;
     }
     if (level >= levels) return;  // dim <= tile: the single CTA did the whole chain
@@ -113,7 +131,7 @@ pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, fl
     while (n > 1 && level < levels) {
         const uint32_t n_out = n / 2;
         const uint32_t out_off = in_off + n * n;
-        reduce_level(s_lv + in_off, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level, 0, 0);
+        reduce_level(s_lv + in_off, n, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level, 0, 0);
         __syncthreads();
         in_off = out_off;
         n = n_out;
@@ -122,12 +140,12 @@ pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, fl
     if (threadIdx.x == 0) *ticket = 0;  // re-arm for the next build on this stream
 }
 
-// footprint-min chain (see PyramidRec::footmin): one thread per output, all levels in one launch
+// footprint-min chain (see PyramidRec::footmin): one thread per output, levels firstLevel.. in one launch
 __global__ void pyramid_footmin_kernel(const float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels,
-                                       uint32_t total) {
-    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+                                       uint32_t firstLevel, uint32_t total) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x + uint32_t(footmin_level_offset(dim, firstLevel));
     if (i >= total) return;
-    uint32_t level = 0;
+    uint32_t level = firstLevel;
     while (level + 1 < levels && i >= uint32_t(footmin_level_offset(dim, level + 1))) ++level;
     const uint32_t n = dim >> level, n1 = n + 1;
     const uint32_t local = i - uint32_t(footmin_level_offset(dim, level));
@@ -138,16 +156,19 @@ __global__ void pyramid_footmin_kernel(const float* __restrict__ pyr, float* __r
     fm[i] = gmin(gmin(img[y0 * n + x0], img[y0 * n + x1]), gmin(img[y1 * n + x0], img[y1 * n + x1]));
 }
 
-int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p) {
+int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel) {
     if (p->footmin_valid) return 0;
     BufferRec* t = get_buffer(ctx, p->texels, "pyramid texels");
     BufferRec* f = get_buffer(ctx, p->footmin, "pyramid footprint-min chain");
     if (!t || !f) return RVE_ERR_BAD_HANDLE;
     const uint32_t total = uint32_t(footmin_level_offset(p->dim, p->levels));
-    pyramid_footmin_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(static_cast<const float*>(t->ptr), static_cast<float*>(f->ptr),
-                                                                        p->dim, p->levels, total);
-    ctx->launches++;
-    RVE_CUDA(cudaGetLastError());
+    const uint32_t todo = firstLevel < p->levels ? total - uint32_t(footmin_level_offset(p->dim, firstLevel)) : 0u;
+    if (todo) {
+        pyramid_footmin_kernel<<<(todo + 255) / 256, 256, 0, ctx->stream>>>(static_cast<const float*>(t->ptr), static_cast<float*>(f->ptr),
+                                                                           p->dim, p->levels, firstLevel, total);
+        ctx->launches++;
+        RVE_CUDA(cudaGetLastError());
+    }
     p->footmin_valid = true;
     return 0;
 }
@@ -230,20 +251,23 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     RVE_REQUIRE(size_t(width) * height * sizeof(float) <= d->bytes, "depth buffer smaller than width*height floats");
     BufferRec* t = get_buffer(ctx, p->texels, "pyramid texels");
     BufferRec* c = get_buffer(ctx, p->counter, "pyramid ticket");
-    if (!t || !c) return RVE_ERR_BAD_HANDLE;
+    BufferRec* f = get_buffer(ctx, p->footmin, "pyramid footprint-min chain");
+    if (!t || !c || !f) return RVE_ERR_BAD_HANDLE;
     const uint32_t tile = p->dim < uint32_t(kPyrTile) ? p->dim : uint32_t(kPyrTile);
     const uint32_t blocks = (p->dim / tile) * (p->dim / tile);
     {
         ProfScope prof(ctx, RVE_PROF_PYRAMID);
         pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height,
-                                                                      static_cast<float*>(t->ptr), p->dim, p->levels, tile,
+                                                                      static_cast<float*>(t->ptr), static_cast<float*>(f->ptr), p->dim,
+                                                                      p->levels, tile,
                                                                       static_cast<uint32_t*>(c->ptr));
     }
     ctx->launches++;
     RVE_CUDA(cudaGetLastError());
-    // the cull's footprint-min chain follows the texels (second, small launch: 1.4 M outputs from L2-resident texels)
+    // level 0 of the cull's footprint-min chain came out of the build kernel; the upper levels (1/4 of the chain) follow
+    // the texels in a second, small launch
     p->footmin_valid = false;
-    return pyramid_refresh_footmin(ctx, p);
+    return pyramid_refresh_footmin(ctx, p, 1);
 }
 
 }  // extern "C"
