@@ -320,9 +320,26 @@ RVE_API int rve_cull(rve_ctx* ctx, const RveCullingUBO* ubo, rve_buffer cubos,
                      rve_buffer per_object_flags, rve_pyramid pyramid,
                      uint32_t num_groups_x);
 
+/* View-batched cull (SURVEY 8e partition B, 8f-2): the reference runs cullTheRenderData once per view of a frame
+ * (main camera, every shadow cascade / spot / point face: src/RenderEngine_Draw.cpp:1769-1866, 1875-1987), each
+ * pass re-reading every transform. Here one launch reads each instance ONCE and tests it against all `num_views`
+ * views (<= 128): ubos[v] / pyramids[v] are what the v-th rve_cull call would take (same numCubos everywhere, no
+ * single-instance mode). View v appends into the same buffers the CUBOs name, displaced by v * strides[c]:
+ * indirect slot + v * indirect_stride commands, culling-buffer index + v * culling_stride slots, per CUBO c (host
+ * array of numCubos entries; normally the material's numLODs and numEntities * numLODs). The caller sizes and
+ * initialises the buffers for num_views views. Results are bit-identical to num_views separate rve_cull calls. */
+typedef struct RveViewStride {
+    uint32_t indirect_stride; /* IndirectIndexedCommands between consecutive views */
+    uint32_t culling_stride;  /* u32 id slots between consecutive views */
+} RveViewStride;
+RVE_API int rve_cull_views(rve_ctx* ctx, const RveCullingUBO* ubos, uint32_t num_views, const rve_pyramid* pyramids,
+                           const RveViewStride* strides, rve_buffer cubos, rve_buffer model_matrices,
+                           rve_buffer render_layers, rve_buffer per_object_flags, uint32_t num_groups_x);
+
 /* ------------------------------------------------------------------ */
 /* a-3 skinning — shaders/skinning_cs.csh                              */
 /* ------------------------------------------------------------------ */
+
 /* Replaces src/RenderEngine_Draw.cpp:577-630: out bindings 0-4
  * (pos,normal,tangent,bitangent vec3; uv vec2), in bindings 10-14, pose 20,
  * weights 21; DispatchCompute(ceil(nObj/8), ceil(nVerts/32),1, 8,32,1). */

@@ -205,3 +205,15 @@ class Context:
         f = (C.c_uint32 * n)(*first_slots)
         s = (C.c_uint32 * n)(*slots)
         _check(self.lib, self.lib.rve_gather_instance_counts_multi(self.h, h, f, s, n, out.handle, out_off))
+
+
+def cull_views(ctx: "Context", ubos: list, pyramids: list, strides, cubos: Buffer, model: Buffer, layers: Buffer, flags: Buffer,
+               num_groups_x: int) -> None:
+    """rve_cull_views: one launch, every instance read once and tested against all views. `strides` = (numCubos, 2)
+    uint32 array of (indirect, culling) strides between consecutive views."""
+    n = len(ubos)
+    arr = (CullingUBO * n)(*ubos)
+    ph = (C.c_uint32 * n)(*[p.handle for p in pyramids])
+    st = np.ascontiguousarray(strides, dtype=np.uint32)
+    _check(ctx.lib, ctx.lib.rve_cull_views(ctx.h, arr, n, ph, st.ctypes.data, cubos.handle, model.handle, layers.handle, flags.handle,
+                                           num_groups_x))
