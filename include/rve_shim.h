@@ -59,6 +59,19 @@ RVE_API int rvs_material_set_command_entities(rvs_world* w, uint32_t material, u
 /* cullTheRenderData(staticMeshRenderData) — src/RenderEngine_Draw.cpp:1221-1407. */
 RVE_API int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
                             uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid);
+/* All views of a frame in one pass: the reference calls cullTheRenderData once per view - main camera,
+ * shadow cascades, spot / point shadow faces (src/RenderEngine_Draw.cpp:1769-1866, 1875-1987) - re-walking the scene
+ * each time and reusing the material buffers between culls. Here the tables are built once and rve_cull_views tests
+ * every instance against all views in one launch; each material's cullingBuffer / indirectBuffer then hold num_views
+ * consecutive copies of the single-view layout (view v at v * numEntities*numLODs ids / v * numLODs commands). */
+typedef struct rvs_view {
+    float view_proj[16];
+    float cam_pos[3];
+    uint32_t camera_layers;
+    uint32_t shadow_pass;
+} rvs_view;
+RVE_API int rvs_cull_static_views(rvs_world* w, uint32_t num_views, const rvs_view* views, const rve_pyramid* pyramids,
+                                  uint32_t pass_mask);
 /* drawcommand.cullingBuffer / indirectBuffer of a material after rvs_cull_static */
 RVE_API int rvs_material_outputs(rvs_world* w, uint32_t material, rve_buffer* culling_buffer, rve_buffer* indirect_buffer,
                                  uint32_t* num_lods_total, uint32_t* num_entities_total);

@@ -133,6 +133,7 @@ PROTOTYPES.update({
     "rvs_material_add_command": (C.c_int, [VP, u32, u32, u32, u32]),
     "rvs_material_set_command_entities": (C.c_int, [VP, u32, u32, u32, u32]),
     "rvs_cull_static": (C.c_int, [VP, FP, FP, u32, u32, u32, u32]),
+    "rvs_cull_static_views": (C.c_int, [VP, u32, VP, UP, u32]),
     "rvs_material_outputs": (C.c_int, [VP, u32, UP, UP, UP, UP]),
     "rvs_last_cull_info": (C.c_int, [VP, UP, UP, UP]),
     "rvs_skinned_mesh_create": (C.c_int, [VP, u32, u32, u32, u32, f32, u32, UP]),
@@ -148,6 +149,10 @@ PROTOTYPES.update({
     "rvs_bin_lights": (C.c_int, [VP, FP, FP, UP, UP, f32, f32, u32, u32, u32, u32, UP]),
 })
 
+
+
+class ShimView(C.Structure):
+    _fields_ = [("view_proj", f32 * 16), ("cam_pos", f32 * 3), ("camera_layers", u32), ("shadow_pass", u32)]
 
 
 class SyncStats(C.Structure):

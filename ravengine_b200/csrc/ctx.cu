@@ -163,6 +163,7 @@ int rve_ctx_destroy(rve_ctx* ctx) {
     if (ctx->d_cubo_res) cudaFree(ctx->d_cubo_res);
     if (ctx->d_cubo_lod) cudaFree(ctx->d_cubo_lod);
     if (ctx->d_view_stride) cudaFree(ctx->d_view_stride);
+    if (ctx->d_views) cudaFree(ctx->d_views);
     if (ctx->d_lights) cudaFree(ctx->d_lights);
     if (ctx->d_slices) cudaFree(ctx->d_slices);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);

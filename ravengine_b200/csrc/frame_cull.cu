@@ -11,17 +11,21 @@ using namespace rvs;
 
 extern "C" {
 
-int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
-                    uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid) {
-    if (!w || !view_proj || !cam_pos) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+}  // extern "C"
+
+// cullTheRenderData for `nviews` views at once (nviews == 0: the reference's single pass through rve_cull). With
+// views, every per-material output buffer holds nviews consecutive copies of the single-view layout.
+static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views, const float view_proj[16], const float cam_pos[3],
+                            uint32_t camera_layers, uint32_t shadow_pass, uint32_t pass_mask, const rve_pyramid* pyramids) {
     rve_ctx* ctx = w->ctx;
+    const uint32_t copies = nviews ? nviews : 1;
     // :1223-1229
     RveCullingUBO globalCubo{};
-    std::memcpy(globalCubo.viewProj, view_proj, 64);
-    std::memcpy(globalCubo.camPos, cam_pos, 12);
+    std::memcpy(globalCubo.viewProj, nviews ? views[0].view_proj : view_proj, 64);
+    std::memcpy(globalCubo.camPos, nviews ? views[0].cam_pos : cam_pos, 12);
     globalCubo.numCubos = 0;
-    globalCubo.cameraRenderLayers = camera_layers;
-    globalCubo.singleInstanceModeAndShadowMode = shadow_pass ? RVE_CULL_SHADOW_MODE : 0u;
+    globalCubo.cameraRenderLayers = nviews ? views[0].camera_layers : camera_layers;
+    globalCubo.singleInstanceModeAndShadowMode = (nviews ? views[0].shadow_pass : shadow_pass) ? RVE_CULL_SHADOW_MODE : 0u;
 
     // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch
     uint32_t totalEntities = 0;
@@ -46,6 +50,7 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
     // every table of the pass goes out in one stream operation (rve_buffer_upload_batch) at the end
     std::vector<std::vector<RveIndirectIndexedCommand>> indirectTables;
     std::vector<rve_upload_segment> uploads;
+    std::vector<RveViewStride> strides(globalCubo.numCubos);
     for (auto& m : w->materials) {
         if (!(m.kind & pass_mask)) continue;
         // :1265-1286 prepass
@@ -58,10 +63,10 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
         m.numEntities = numEntities;
         // :1288-1291
         const size_t cullingbufferTotalSlots = size_t(numEntities) * numLODs;
-        RVE_REQUIRE(cullingbufferTotalSlots <= 0xFFFFFFFFull, "culling buffer exceeds 2^32 slots (u32 indices in the CUBO layout)");
-        rc = realloc_buffer(w, &m.cullingBuffer, &m.cullingBytes, cullingbufferTotalSlots, sizeof(uint32_t));
+        RVE_REQUIRE(cullingbufferTotalSlots * copies <= 0xFFFFFFFFull, "culling buffer exceeds 2^32 slots (u32 indices in the CUBO layout)");
+        rc = realloc_buffer(w, &m.cullingBuffer, &m.cullingBytes, cullingbufferTotalSlots * copies, sizeof(uint32_t));
         if (rc) return rc;
-        rc = realloc_buffer(w, &m.indirectBuffer, &m.indirectBytes, numLODs, sizeof(RveIndirectIndexedCommand));
+        rc = realloc_buffer(w, &m.indirectBuffer, &m.indirectBytes, size_t(numLODs) * copies, sizeof(RveIndirectIndexedCommand));
         if (rc) return rc;
         if (numLODs == 0) continue;
 
@@ -85,7 +90,9 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
             }
         }
         // :1321-1329 CopyBufferToBuffer(indirectStagingBuffer -> indirectBuffer)
-        uploads.push_back({m.indirectBuffer, 0, indirectStaging.data(), numLODs * sizeof(RveIndirectIndexedCommand)});
+        for (uint32_t v = 1; v < copies; ++v)  // the same initial commands for every view
+            for (uint32_t k = 0; k < numLODs; ++k) indirectStaging.push_back(indirectStaging[k]);
+        uploads.push_back({m.indirectBuffer, 0, indirectStaging.data(), indirectStaging.size() * sizeof(RveIndirectIndexedCommand)});
 
         // :1334-1362 one CUBO per command; offsets restart per material
         RveCullingUBOinstance cubo{};
@@ -100,6 +107,7 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
             cubo.indirectOutputBufferBindlessHandle = rve_buffer_bindless_index(ctx, m.indirectBuffer);
             cubo.lodDistanceBufferBindlessHandle = rve_buffer_bindless_index(ctx, mesh.lodDistances);
             cubo.entityIDInputBufferBindlessHandle = rve_buffer_bindless_index(ctx, c.entityIds);
+            strides[cuboIdx] = RveViewStride{numLODs, uint32_t(cullingbufferTotalSlots)};
             cuboStaging[cuboIdx++] = cubo;
             cubo.indirectBufferOffset += lodsForThisMesh;
             cubo.cullingBufferOffset += lodsForThisMesh * c.count;
@@ -111,7 +119,29 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
     if (rc) return rc;
     // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
     const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));
-    return rve_cull(ctx, &globalCubo, w->cuboBuffer, w->model, w->layers, w->flagsBuf, pyramid, groups);
+    if (!nviews) return rve_cull(ctx, &globalCubo, w->cuboBuffer, w->model, w->layers, w->flagsBuf, pyramids[0], groups);
+    std::vector<RveCullingUBO> ubos(nviews, globalCubo);
+    for (uint32_t v = 0; v < nviews; ++v) {
+        std::memcpy(ubos[v].viewProj, views[v].view_proj, 64);
+        std::memcpy(ubos[v].camPos, views[v].cam_pos, 12);
+        ubos[v].cameraRenderLayers = views[v].camera_layers;
+        ubos[v].singleInstanceModeAndShadowMode = views[v].shadow_pass ? RVE_CULL_SHADOW_MODE : 0u;
+    }
+    return rve_cull_views(ctx, ubos.data(), nviews, pyramids, strides.data(), w->cuboBuffer, w->model, w->layers, w->flagsBuf, groups);
+}
+
+extern "C" {
+
+int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
+                    uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid) {
+    if (!w || !view_proj || !cam_pos) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    return cull_static_impl(w, 0, nullptr, view_proj, cam_pos, camera_layers, shadow_pass, pass_mask, &pyramid);
+}
+
+int rvs_cull_static_views(rvs_world* w, uint32_t num_views, const rvs_view* views, const rve_pyramid* pyramids, uint32_t pass_mask) {
+    if (!w || !views || !pyramids) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(num_views >= 1 && num_views <= 128, "1..128 views per batch");
+    return cull_static_impl(w, num_views, views, nullptr, nullptr, 0, 0, pass_mask, pyramids);
 }
 
 int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[16], const uint32_t grid_size[3],

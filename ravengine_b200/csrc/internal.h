@@ -62,6 +62,8 @@ struct rve_ctx {
     size_t d_cubo_res_cap = 0;
     void* d_cubo_lod = nullptr;  // per-CUBO squared LOD thresholds
     size_t d_cubo_lod_cap = 0;
+    void* d_views = nullptr;  // view table of a view-batched cull
+    size_t d_views_cap = 0;
     void* d_view_stride = nullptr;  // per-CUBO output strides of a view-batched cull
     size_t d_view_stride_cap = 0;
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once

@@ -69,6 +69,21 @@ class World:
         k2, cp = _fp(cam_pos)
         _check(self.lib, self.lib.rvs_cull_static(self.h, vp, cp, layers, 1 if shadow else 0, mask, pyramid.handle))
 
+    def cull_static_views(self, views, pyramids, mask=MAT_ALL):
+        """views: list of (view_proj_cm[16], cam_pos[3], camera_layers, shadow) - all of them in ONE launch
+        (rvs_cull_static_views); outputs hold len(views) consecutive copies of the single-view layout."""
+        from ._abi import ShimView
+
+        n = len(views)
+        arr = (ShimView * n)()
+        for a, (vp, cp, layers, shadow) in zip(arr, views):
+            a.view_proj[:] = [float(x) for x in vp]
+            a.cam_pos[:] = [float(x) for x in cp]
+            a.camera_layers = layers
+            a.shadow_pass = 1 if shadow else 0
+        ph = (C.c_uint32 * n)(*[p.handle for p in pyramids])
+        _check(self.lib, self.lib.rvs_cull_static_views(self.h, n, arr, ph, mask))
+
     def material_outputs(self, material: int):
         c, i, l, e = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
         _check(self.lib, self.lib.rvs_material_outputs(self.h, material, C.byref(c), C.byref(i), C.byref(l), C.byref(e)))

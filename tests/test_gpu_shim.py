@@ -245,3 +245,48 @@ def test_bin_lights_matches_oracle(ctx):
     ctx.synchronize()
     np.testing.assert_array_equal(out.download(np.uint32).reshape(n, 40), ref)
     w.destroy()
+
+
+def test_cull_static_views_matches_per_view_culls(ctx):
+    """rvs_cull_static_views: all views of a frame (main camera + shadow passes) in one launch == the reference's
+    one cullTheRenderData per view; view v occupies the v-th copy of every material's output layout."""
+    model, layers, flags, mats = _static_scene(seed=9)
+    t = host_tables.build_static_tables(mats)
+    cams = [scenes.default_camera(z_far=500.0), scenes.default_camera(z_far=500.0, eye=(80, 20, 60), target=(0, 0, 0)),
+            scenes.default_camera(z_far=800.0, fovy=90.0, eye=(-50, 100, 0), target=(0, 0, -10)),
+            scenes.default_camera(z_far=300.0, eye=(0, 0, -100), target=(0, 0, 0))]
+    shadows = [False, True, True, False]
+    refs, pyrs, views = [], [], []
+    for cam, sh in zip(cams, shadows):
+        depth = scenes.synth_depth(512, 288, cam, n_occluders=20)
+        pyr_h, dim, levels = oracle.pyramid_build(depth, 288)
+        ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos, shadow=sh)
+        refs.append(oracle_cull(t, ubo, model, layers, flags, pyr_h, dim, levels, nthreads=4))
+        p = ctx.create_pyramid(288)
+        ctx.build_pyramid(p, ctx.buffer_from_numpy(depth), 512, 288)
+        pyrs.append(p)
+        views.append((cam.view_proj_cm, cam.pos, 0xFFFFFFFF, sh))
+    w, mat_ids, keep = _world_from(ctx, model, layers, flags, mats)
+    for _ in range(2):
+        w.cull_static_views(views, pyrs)
+    ctx.synchronize()
+    ci = 0
+    for mat, m in zip(mat_ids, mats):
+        cull_b, ind_b, lods, ents = w.material_outputs(mat)
+        cb = t.cubos[ci]
+        all_ind = ind_b.download(np.uint32).reshape(-1, 5)
+        all_ids = cull_b.download(np.uint32)
+        rng_c = range(ci, ci + len(m.commands))
+        for v, ref in enumerate(refs):
+            r_ind, r_ids = ref[int(cb["indirectOutputBufferBindlessHandle"])], ref[int(cb["idOutputBufferBindlessHandle"])]
+            g_ind = all_ind[v * lods:(v + 1) * lods]
+            g_ids = all_ids[v * lods * ents:(v + 1) * lods * ents]
+            np.testing.assert_array_equal(g_ind, r_ind)
+            for x, y in zip(host_tables.sorted_slices(r_ind, r_ids, t.cubos, rng_c), host_tables.sorted_slices(g_ind, g_ids, t.cubos, rng_c)):
+                np.testing.assert_array_equal(x, y)
+        ci += len(m.commands)
+    # back to a single-view pass on the same world
+    w.cull_static(cams[0].view_proj_cm, cams[0].pos, pyrs[0])
+    ctx.synchronize()
+    _compare_static(ctx, w, mat_ids, mats, t, refs[0])
+    w.destroy()
