@@ -366,6 +366,39 @@ RVE_API int rve_cluster_assign(rve_ctx* ctx, const RveGridAssignUBO* ubo, rve_bu
                                rve_buffer point_lights, rve_buffer spot_lights, uint32_t num_clusters);
 
 /* ------------------------------------------------------------------ */
+/* f-3 cascaded-shadow-map matrices                                    */
+/* ------------------------------------------------------------------ */
+/* One camera of the frame as the cascade fit sees it (src/RenderEngine_Draw.cpp:161-176): viewOnly is the
+ * column-major view matrix, tanHalfFovy = tan(deg_to_rad(FOV * 1.5) / 2) computed by the caller (:219 widens the
+ * fov by 1.5), aspect = float(targetWidth / targetHeight), the reference's INTEGER ratio (:219). */
+typedef struct RveCsmCamera {
+    float viewOnly[16];
+    float zNear, zFar;
+    float tanHalfFovy, aspect;
+} RveCsmCamera;
+/* One directional light (World::DirLightUploadData + its shadow settings, src/RenderEngine_Draw.cpp:178-180,
+ * 205-216): shadowCascades are the split fractions in [0,1], numCascades <= 4. */
+typedef struct RveCsmLight {
+    float direction[3];
+    uint32_t castsShadows;
+    uint32_t numCascades;
+    float shadowCascades[4];
+    float maxShadowDistanceFactor;
+} RveCsmLight;
+/* Host helper (no device work): tanHalfFovy and aspect exactly as src/RenderEngine_Draw.cpp:220 and glm's
+ * perspectiveRH_ZO derive them (libm tanf). A zero target height yields aspect 0 instead of the reference's
+ * division fault. */
+RVE_API void rve_csm_camera_params(float fov_degrees, uint32_t target_width, uint32_t target_height, float* tan_half_fovy,
+                                   float* aspect);
+/* Replaces the CPU loop of src/RenderEngine_Draw.cpp:149-293: for every camera c, shadow-casting light l and
+ * cascade k < numCascades writes the light view-projection (and optionally the view and the projection) as 16
+ * column-major floats at matrix index (c + l) * 4 + k — the reference's passIndex + i slot, collisions included —
+ * and the cascade far distances at out_distances[l * 4 + k] (last camera wins, as light.cascadeDistances does).
+ * out_view / out_proj / out_distances may be RVE_BUFFER_INVALID. f32, glm's operation order, no contraction. */
+RVE_API int rve_csm_cascades(rve_ctx* ctx, rve_buffer cameras, uint32_t num_cameras, rve_buffer lights, uint32_t num_lights,
+                             rve_buffer out_view_proj, rve_buffer out_view, rve_buffer out_proj, rve_buffer out_distances);
+
+/* ------------------------------------------------------------------ */
 /* 8(e) multi-GPU helpers (instance-range sharding)                    */
 /* ------------------------------------------------------------------ */
 /* Scatter of a packed dirty list (the device half of the dirty-range upload that replaces the reference's

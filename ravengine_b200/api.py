@@ -217,3 +217,26 @@ def cull_views(ctx: "Context", ubos: list, pyramids: list, strides, cubos: Buffe
     st = np.ascontiguousarray(strides, dtype=np.uint32)
     _check(ctx.lib, ctx.lib.rve_cull_views(ctx.h, arr, n, ph, st.ctypes.data, cubos.handle, model.handle, layers.handle, flags.handle,
                                            num_groups_x))
+
+
+# rve_b200.h RveCsmCamera / RveCsmLight as numpy record types (host staging of rve_csm_cascades)
+CSM_CAMERA = np.dtype([("viewOnly", "<f4", 16), ("zNear", "<f4"), ("zFar", "<f4"), ("tanHalfFovy", "<f4"), ("aspect", "<f4")])
+CSM_LIGHT = np.dtype([("direction", "<f4", 3), ("castsShadows", "<u4"), ("numCascades", "<u4"), ("shadowCascades", "<f4", 4),
+                      ("maxShadowDistanceFactor", "<f4")])
+
+
+def csm_camera_params(fov_degrees: float, width: int, height: int) -> tuple[float, float]:
+    """rve_csm_camera_params: (tanHalfFovy, aspect) as src/RenderEngine_Draw.cpp:220 derives them (host, libm tanf)."""
+    from ._abi import load_library
+    t, a = C.c_float(), C.c_float()
+    load_library().rve_csm_camera_params(C.c_float(fov_degrees), width, height, C.byref(t), C.byref(a))
+    return t.value, a.value
+
+
+def csm_cascades(ctx: "Context", cameras: Buffer, n_cameras: int, lights: Buffer, n_lights: int, view_proj: Buffer,
+                 view: Buffer | None = None, proj: Buffer | None = None, distances: Buffer | None = None) -> None:
+    """rve_csm_cascades: the cascade fit of src/RenderEngine_Draw.cpp:149-293 on the device."""
+    inv = 0xFFFFFFFF
+    _check(ctx.lib, ctx.lib.rve_csm_cascades(ctx.h, cameras.handle, n_cameras, lights.handle, n_lights, view_proj.handle,
+                                             view.handle if view is not None else inv, proj.handle if proj is not None else inv,
+                                             distances.handle if distances is not None else inv))
