@@ -1,9 +1,13 @@
 // pyramid.cu — Hi-Z depth pyramid.
 // Replaces generatePyramid (src/RenderEngine_Draw.cpp:2475-2514): one raster pass of
 // depthpyramidcopy.fsh (mip 0) + one depthpyramid.csh dispatch per further mip (10 launches
-// with barriers for 1024^2) by ONE launch: every CTA produces a 32x32 tile of mip 0 from
-// the depth buffer, reduces it through shared memory down to a single texel (mips 0..5),
-// and the last CTA to finish (ticket counter) reduces the remaining 32x32 image (mips 6..10).
+// with barriers for 1024^2) by TWO launches: in the first every CTA produces a 32x32 tile of mip 0
+// from the depth buffer and reduces it through shared memory down to a single texel (mips 0..5,
+// plus level 0 of the cull's footprint-min chain); the second (programmatic dependent launch: its
+// blocks are resident before the first one drains) derives footprint-min levels 1..5 with one thread
+// per entry while one extra block reduces the remaining 32x32 image (mips 6..10) and their
+// footprint-min levels out of shared memory. No ticket counter, no grid-wide fence, no serial tail
+// inside the big kernel (the r01l ncu capture had 45 % of its samples there).
 //
 // Sampler model = oracle.cpp sample_min(): min over the clamped 2x2 bilinear footprint
 // floor(u*W-0.5)+{0,1} (src/RenderEngine.cpp:323-331, reduction mode Minimum).
@@ -58,11 +62,12 @@ __device__ __forceinline__ void reduce_level(const float* lv, uint32_t n_in, flo
 
 __global__ void __launch_bounds__(kPyrThreads)
 pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
-                     uint32_t dim, uint32_t levels, uint32_t tile, uint32_t* __restrict__ ticket) {
+                     uint32_t dim, uint32_t levels, uint32_t tile) {
     // mip 0 of the tile plus one halo column / row ((tile+1)^2, stride tile+1), then the in-tile levels 1.. back to back
     __shared__ float s_lv[(kPyrTile + 1) * (kPyrTile + 1) + (kPyrTile * kPyrTile) / 3 + 2];
-    __shared__ bool s_last;
 
+    // let pyramid_upper_kernel's blocks become resident as this grid's CTAs retire (they wait in griddepcontrol.wait)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     const uint32_t tiles_per_row = dim / tile;
     const uint32_t tx0 = (blockIdx.x % tiles_per_row) * tile;
     const uint32_t ty0 = (blockIdx.x / tiles_per_row) * tile;
@@ -110,34 +115,56 @@ pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, fl
         n_stride = n_out;
         ++level;
     }
-    if (level >= levels) return;  // dim <= tile: the single CTA did the whole chain
+    // levels above log2(tile) and the footprint-min levels >= 1: pyramid_upper_kernel
+}
 
-    // remaining levels: the last CTA to arrive reduces the (dim/tile)^2 image of level log2(tile)
-    __threadfence();
-    if (threadIdx.x == 0) {
-        const uint32_t t = atomicAdd(ticket, 1u);
-        s_last = (t == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
+__device__ __forceinline__ float footmin_entry(const float* img, uint32_t n, uint32_t fx, uint32_t fy) {
+    const uint32_t x0 = fx ? fx - 1 : 0, x1 = fx < n ? fx : n - 1;
+    const uint32_t y0 = fy ? fy - 1 : 0, y1 = fy < n ? fy : n - 1;
+    return gmin(gmin(img[y0 * n + x0], img[y0 * n + x1]), gmin(img[y1 * n + x0], img[y1 * n + x1]));
+}
 
-    const uint32_t r = dim / tile;  // <= 32
-    const float* src = pyr + pyr_level_offset(dim, level - 1);
-    for (uint32_t i = threadIdx.x; i < r * r; i += blockDim.x) s_lv[i] = __ldcg(src + i);
-    __syncthreads();
-    in_off = 0;
-    n = r;
-    while (n > 1 && level < levels) {
-        const uint32_t n_out = n / 2;
-        const uint32_t out_off = in_off + n * n;
-        reduce_level(s_lv + in_off, n, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level, 0, 0);
+// Second launch of a build. Block 0: texel levels topLevel.. (the (dim >> (topLevel-1))^2 <= 32x32 image left by the
+// tiles, reduced in shared memory) and their footprint-min levels. Blocks 1..: footprint-min levels 1..topLevel-1,
+// one thread per entry. Launched with programmatic stream serialization: everything before griddepcontrol.wait
+// overlaps the tail of pyramid_build_kernel.
+__global__ void __launch_bounds__(kPyrThreads)
+pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels, uint32_t topLevel) {
+    __shared__ float s_lv[kPyrTile * kPyrTile + (kPyrTile * kPyrTile) / 3 + 2];
+    if (blockIdx.x == 0) {
+        if (topLevel >= levels) return;
+        const uint32_t r = dim >> (topLevel - 1);  // <= 32
+        const float* src = pyr + pyr_level_offset(dim, topLevel - 1);
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        for (uint32_t i = threadIdx.x; i < r * r; i += blockDim.x) s_lv[i] = __ldcg(src + i);
         __syncthreads();
-        in_off = out_off;
-        n = n_out;
-        ++level;
+        uint32_t in_off = 0, n = r, level = topLevel;
+        while (n > 1 && level < levels) {
+            const uint32_t n_out = n / 2;
+            const uint32_t out_off = in_off + n * n;
+            reduce_level(s_lv + in_off, n, s_lv + out_off, n_out, pyr + pyr_level_offset(dim, level), dim >> level, 0, 0);
+            __syncthreads();
+            // footprint-min of the level just produced, from shared memory
+            float* f = fm + footmin_level_offset(dim, level);
+            for (uint32_t i = threadIdx.x; i < (n_out + 1) * (n_out + 1); i += blockDim.x)
+                f[i] = footmin_entry(s_lv + out_off, n_out, i % (n_out + 1), i / (n_out + 1));
+            in_off = out_off;
+            n = n_out;
+            ++level;
+        }
+        return;
     }
-    if (threadIdx.x == 0) *ticket = 0;  // re-arm for the next build on this stream
+    const uint32_t first = uint32_t(footmin_level_offset(dim, 1));
+    const uint32_t end = uint32_t(footmin_level_offset(dim, topLevel < levels ? topLevel : levels));
+    const uint32_t i = (blockIdx.x - 1) * blockDim.x + threadIdx.x + first;
+    uint32_t level = 1;
+    while (level + 1 < levels && i >= uint32_t(footmin_level_offset(dim, level + 1))) ++level;
+    const uint32_t n = dim >> level, n1 = n + 1;
+    const uint32_t local = i - uint32_t(footmin_level_offset(dim, level));
+    const float* img = pyr + pyr_level_offset(dim, level);
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (i >= end) return;
+    fm[i] = footmin_entry(img, n, local % n1, local / n1);
 }
 
 // footprint-min chain (see PyramidRec::footmin): one thread per output, levels firstLevel.. in one launch
@@ -250,24 +277,38 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     RVE_REQUIRE(width >= 1 && height >= 1, "depth buffer must be at least 1x1");
     RVE_REQUIRE(size_t(width) * height * sizeof(float) <= d->bytes, "depth buffer smaller than width*height floats");
     BufferRec* t = get_buffer(ctx, p->texels, "pyramid texels");
-    BufferRec* c = get_buffer(ctx, p->counter, "pyramid ticket");
     BufferRec* f = get_buffer(ctx, p->footmin, "pyramid footprint-min chain");
-    if (!t || !c || !f) return RVE_ERR_BAD_HANDLE;
+    if (!t || !f) return RVE_ERR_BAD_HANDLE;
     const uint32_t tile = p->dim < uint32_t(kPyrTile) ? p->dim : uint32_t(kPyrTile);
     const uint32_t blocks = (p->dim / tile) * (p->dim / tile);
+    uint32_t topLevel = 1;  // first level the tiles do not produce
+    while ((1u << topLevel) <= tile) ++topLevel;
+    float* pyrPtr = static_cast<float*>(t->ptr);
+    float* fmPtr = static_cast<float*>(f->ptr);
     {
         ProfScope prof(ctx, RVE_PROF_PYRAMID);
-        pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height,
-                                                                      static_cast<float*>(t->ptr), static_cast<float*>(f->ptr), p->dim,
-                                                                      p->levels, tile,
-                                                                      static_cast<uint32_t*>(c->ptr));
+        pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height, pyrPtr, fmPtr, p->dim,
+                                                                      p->levels, tile);
+        ctx->launches++;
+        RVE_CUDA(cudaGetLastError());
+        if (p->levels > 1) {
+            const uint32_t lastFm = topLevel < p->levels ? topLevel : p->levels;
+            const uint32_t entries = uint32_t(footmin_level_offset(p->dim, lastFm) - footmin_level_offset(p->dim, 1));
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(1 + (entries + kPyrThreads - 1) / kPyrThreads);
+            cfg.blockDim = dim3(kPyrThreads);
+            cfg.stream = ctx->stream;
+            cudaLaunchAttribute attr{};
+            attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            attr.val.programmaticStreamSerializationAllowed = 1;
+            cfg.attrs = &attr;
+            cfg.numAttrs = 1;
+            RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel));
+            ctx->launches++;
+        }
     }
-    ctx->launches++;
-    RVE_CUDA(cudaGetLastError());
-    // level 0 of the cull's footprint-min chain came out of the build kernel; the upper levels (1/4 of the chain) follow
-    // the texels in a second, small launch
-    p->footmin_valid = false;
-    return pyramid_refresh_footmin(ctx, p, 1);
+    p->footmin_valid = true;
+    return 0;
 }
 
 }  // extern "C"
