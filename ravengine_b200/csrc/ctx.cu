@@ -148,6 +148,7 @@ int rve_ctx_create(int device_ordinal, void* cuda_stream, rve_ctx** out_ctx) {
         return rc;
     }
     ctx->sm_count = prop.multiProcessorCount;
+    ctx->l2_bytes = size_t(prop.l2CacheSize);
     *out_ctx = ctx;
     return 0;
 }

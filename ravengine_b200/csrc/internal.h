@@ -37,6 +37,7 @@ struct rve_ctx {
     cudaStream_t stream = nullptr;
     bool owns_stream = false;
     int sm_count = 0;
+    size_t l2_bytes = 0;
     uint64_t launches = 0;
 
     bool profiling = false;
