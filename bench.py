@@ -144,9 +144,11 @@ class DeviceScene:
         self.slots = m * len(C2["lod_distances"])
         c.synchronize()
 
-    def step(self):
+    def step(self, before_cull=None):
         """one pass of the hot path for one view"""
         self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
+        if before_cull:
+            before_cull()
         self.world.cull_static(self.vp, self.cam_pos, self.pyr)
 
     def visible_counts(self) -> np.ndarray:
@@ -247,7 +249,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         torch.cuda.synchronize()
 
     def one_step():
-        sc.step()
+        sc.step(ex.begin_cull if ex else None)
         if ex:
             ex.exchange()
 

@@ -196,6 +196,23 @@ class Context:
         _check(self.lib, self.lib.rve_exchange_counts_p2p(self.h, None, None, None, 0, dense_counts.handle, slots, m, rank, world, epoch,
                                                           offsets.handle, totals.handle, status.handle))
 
+    def exchange_counts_p2p_indirect(self, indirect: list[Buffer], first_slots: list[int], slots: list[int], mailboxes: list[Buffer],
+                                     rank: int, world: int, epoch: int, offsets: Buffer, totals: Buffer, status: Buffer) -> None:
+        """Same exchange, the kernel reading the instanceCount fields straight out of the indirect buffers."""
+        n = len(indirect)
+        h = (C.c_uint32 * n)(*[b.handle for b in indirect])
+        f = (C.c_uint32 * n)(*first_slots)
+        c = (C.c_uint32 * n)(*slots)
+        m = (C.c_uint32 * world)(*[b.handle for b in mailboxes])
+        _check(self.lib, self.lib.rve_exchange_counts_p2p(self.h, h, f, c, n, 0xFFFFFFFF, 0, m, rank, world, epoch, offsets.handle,
+                                                          totals.handle, status.handle))
+
+    def wrap_pointer(self, ptr: int, nbytes: int, keepalive=None) -> Buffer:
+        """Register device memory owned elsewhere (another context of the same device) as a buffer of this context."""
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rve_buffer_wrap(self.h, C.c_void_p(ptr), nbytes, C.byref(out)))
+        return Buffer(self, out.value, nbytes, keepalive=keepalive)
+
     def gather_instance_counts(self, indirect: Buffer, first_slot: int, slots: int, out: Buffer, out_off: int = 0) -> None:
         _check(self.lib, self.lib.rve_gather_instance_counts(self.h, indirect.handle, first_slot, slots, out.handle, out_off))
 

@@ -160,6 +160,11 @@ class ShardedCull:
             self.b_tot.append(self.ctx2.wrap_tensor(self.t_tot[i]))
         self.k = 0
         self._indirect = None
+        self._indirect2 = None
+        self.pending = None
+        # fused: the exchange kernel gathers the counts itself (one launch less on the cull's stream); RVE_EXCHANGE_FUSED=0
+        # restores the separate gather launch
+        self.fused = os.environ.get("RVE_EXCHANGE_FUSED", "1") == "1" and not self.inline
         self.rank, self.mode = rank, "nccl"
         if world_size > 1 and exchange in ("auto", "p2p"):
             self._setup_p2p(strict=exchange == "p2p")
@@ -211,6 +216,21 @@ class ShardedCull:
         self.k += 1
         if self._indirect is None or refresh_buffers:  # handles change only when the shim reallocates (entity counts changed)
             self._indirect = self._indirect_buffers()
+            self._indirect2 = None
+        if self.mode == "p2p" and self.fused:
+            # no launch on the cull's stream at all: the exchange kernel (side stream) reads the counts out of the
+            # indirect buffers itself; begin_cull() keeps the next frame's re-initialisation behind it
+            if self._indirect2 is None:
+                self._indirect2 = [self.ctx2.wrap_pointer(x.ptr, x.nbytes, keepalive=x) for x in self._indirect]
+            ev = torch.cuda.Event()
+            ev.record(self.stream)
+            self.side.wait_event(ev)
+            self.ctx2.exchange_counts_p2p_indirect(self._indirect2, [0] * len(self.mats), self.lods, self.peers, self.rank, self.ws,
+                                                   self.k, self.b_off[b], self.b_tot[b], self.status)
+            self.done[b] = torch.cuda.Event()
+            self.done[b].record(self.side)
+            self.pending = self.done[b]
+            return b
         if self.done[b] is not None:
             self.stream.wait_event(self.done[b])  # the exchange that last used this buffer set has finished
         self.ctx.gather_instance_counts_multi(self._indirect, [0] * len(self.mats), self.lods, self.b_local[b])
@@ -232,6 +252,13 @@ class ShardedCull:
         self.done[b] = torch.cuda.Event()
         self.done[b].record(self.side)
         return b
+
+    def begin_cull(self) -> None:
+        """Call between the pyramid build and the cull of the next frame: the cull re-initialises the indirect commands,
+        which the (fused-gather) exchange of the previous frame may still be reading on the side stream."""
+        if self.pending is not None:
+            self.stream.wait_event(self.pending)
+            self.pending = None
 
     def finish(self) -> None:
         self.stream.wait_stream(self.side)

@@ -259,4 +259,24 @@ def test_p2p_count_exchange_two_ranks_on_one_device(ctx):
             assert pr["status"].download(np.uint32)[0] == 0
             assert np.array_equal(pr["off"].download(np.uint32).reshape(world, slots), expect_off)
             assert np.array_equal(pr["tot"].download(np.uint32), counts.sum(axis=0, dtype=np.uint32))
+    # the same exchange with the kernel gathering the counts out of indirect command buffers (two "materials")
+    split = [3, 4]
+    ind = [[pr["c"].create_buffer((first + n) * 20) for first, n in zip((2, 0), split)] for pr in per_rank]
+    for epoch in range(6, 9):
+        counts = rng.integers(0, 1000, size=(world, slots)).astype(np.uint32)
+        for r, pr in enumerate(per_rank):
+            k = 0
+            for j, (first, n) in enumerate(zip((2, 0), split)):
+                cmds = rng.integers(0, 2 ** 31, size=(first + n, 5)).astype(np.uint32)
+                cmds[first:, 1] = counts[r, k:k + n]
+                ind[r][j].upload(cmds)
+                k += n
+        for r, pr in enumerate(per_rank):
+            pr["c"].exchange_counts_p2p_indirect(ind[r], [2, 0], split, pr["mb"], r, world, epoch, pr["off"], pr["tot"], pr["status"])
+        expect_off = np.cumsum(counts, axis=0, dtype=np.uint32) - counts
+        for pr in per_rank:
+            pr["c"].synchronize()
+            assert pr["status"].download(np.uint32)[0] == 0
+            assert np.array_equal(pr["off"].download(np.uint32).reshape(world, slots), expect_off)
+            assert np.array_equal(pr["tot"].download(np.uint32), counts.sum(axis=0, dtype=np.uint32))
     ctxs[1].close()
