@@ -149,6 +149,61 @@ RVE_API uint64_t rvs_vector_pulled_rows(rvs_vector* v);
 /* (begin, end) pairs of the last sync, for inspection; returns their number */
 RVE_API uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max_pairs);
 
+/* ---- shared vertex arena + .rvem container: the data formats on the input side of skinning ---- */
+/* RenderEngine's shared mesh buffers (src/RenderEngine_Allocate.cpp:168-177): positions, normals, tangents, bitangents
+ * (12 B), uv0, lightmapUV (8 B), u32 indices; offsets and sizes are ELEMENTS (include/RavEngine/MeshAllocation.hpp:27-52). */
+typedef struct rvs_arena rvs_arena;
+/* MeshPartView (include/RavEngine/Mesh.hpp:35-60): host pointers, any vertex stream may be NULL (absent attribute) */
+typedef struct rvs_mesh_view {
+    const float *positions, *normals, *tangents, *bitangents, *uv0, *lightmap_uvs;
+    const uint32_t* indices;
+    uint32_t num_vertices, num_indices;
+} rvs_mesh_view;
+/* initial sizes 0 = the reference's (1024 vertices, 1536 indices; include/RavEngine/RenderEngine.hpp:87) */
+RVE_API int rvs_arena_create(rve_ctx* ctx, uint32_t initial_verts, uint32_t initial_indices, rvs_arena** out);
+RVE_API int rvs_arena_destroy(rvs_arena* a);
+/* RenderEngine::AllocateMesh (src/RenderEngine_Allocate.cpp:12-100): placement, growth and upload; out_range is the
+ * MeshRange (it follows re-packs; query it with rvs_arena_range after any later allocation) */
+RVE_API int rvs_arena_allocate_mesh(rvs_arena* a, const rvs_mesh_view* mesh, uint32_t* out_range);
+/* RenderEngine::DeallocateMesh (src/RenderEngine_Allocate.cpp:101-145) */
+RVE_API int rvs_arena_deallocate_mesh(rvs_arena* a, uint32_t range);
+/* MeshRange::getVertexRangeStart / getIndexRangeStart (+ counts) */
+RVE_API int rvs_arena_range(rvs_arena* a, uint32_t range, uint32_t* vertex_start, uint32_t* vertex_count, uint32_t* index_start,
+                            uint32_t* index_count);
+/* sharedPositionBuffer .. sharedLightmapUVBuffer, sharedIndexBuffer and currentVertexSize / currentIndexSize; the
+ * handles change when the arena grows (the reference re-creates its buffers too) */
+RVE_API int rvs_arena_buffers(rvs_arena* a, rve_buffer out_streams[7], uint32_t* vertex_capacity, uint32_t* index_capacity);
+#define RVS_ARENA_VERTEX_FREE 0u
+#define RVS_ARENA_INDEX_FREE 1u
+#define RVS_ARENA_VERTEX_ALLOCATED 2u
+#define RVS_ARENA_INDEX_ALLOCATED 3u
+/* (start, count) pairs of vertexFreeList / indexFreeList / vertexAllocatedList / indexAllocatedList in list order, for
+ * inspection; returns the list length */
+RVE_API uint32_t rvs_arena_list(rvs_arena* a, uint32_t which, uint32_t* out_pairs, uint32_t max_pairs);
+
+/* SerializedMeshDataHeader attribute bits (include/RavEngine/Mesh.hpp:18-26) */
+#define RVS_RVEM_SKINNED 0x01u
+#define RVS_RVEM_HAS_POSITIONS 0x02u
+#define RVS_RVEM_HAS_NORMALS 0x04u
+#define RVS_RVEM_HAS_TANGENTS 0x08u
+#define RVS_RVEM_HAS_BITANGENTS 0x10u
+#define RVS_RVEM_HAS_UV0 0x20u
+#define RVS_RVEM_HAS_LIGHTMAP_UV 0x40u
+/* Where each stream of a .rvem image lies (byte offsets into the image; ~0 = absent) */
+typedef struct rvs_rvem_info {
+    uint32_t num_vertices, num_indices, attributes, reserved;
+    uint64_t off_positions, off_normals, off_tangents, off_bitangents, off_uv0, off_lightmap_uv, off_indices;
+    uint64_t mesh_bytes;    /* end of the index stream = MeshAsset::DeserializeMeshFromMemory's second result */
+    uint64_t off_weights;   /* VertexWeights table of a skinned mesh (32 B per vertex), ~0 when fewer than 4 bytes follow */
+    uint64_t weights_bytes; /* whole entries only */
+} rvs_rvem_info;
+/* MeshAsset::DeserializeMeshFromMemory (src/MeshAsset.cpp:23-79), host only, zero-copy: validates the header and sizes */
+RVE_API int rvs_rvem_parse(const void* data, uint64_t size, rvs_rvem_info* out);
+/* MeshAsset(name) / MeshAssetSkinned(path) (src/MeshAsset.cpp:81-87, src/MeshAssetSkinned.cpp:25-70): parse, AllocateMesh,
+ * and for skinned != 0 the weights buffer (VertexWeights[num_vertices], binding 21 of skinning_cs.csh) */
+RVE_API int rvs_arena_load_rvem(rvs_arena* a, const void* data, uint64_t size, uint32_t skinned, uint32_t* out_range,
+                                rve_buffer* out_weights);
+
 #ifdef __cplusplus
 }
 #endif

@@ -148,6 +148,15 @@ PROTOTYPES.update({
     "rvs_cull_skeletal": (C.c_int, [VP, FP, FP, u32, u32, u32, u32]),
     "rvs_skinned_outputs": (C.c_int, [VP, UP, UP]),
     "rvs_skinned_material_outputs": (C.c_int, [VP, u32, UP, UP, UP]),
+    "rvs_arena_create": (C.c_int, [VP, u32, u32, C.POINTER(VP)]),
+    "rvs_arena_destroy": (C.c_int, [VP]),
+    "rvs_arena_allocate_mesh": (C.c_int, [VP, VP, UP]),
+    "rvs_arena_deallocate_mesh": (C.c_int, [VP, u32]),
+    "rvs_arena_range": (C.c_int, [VP, u32, UP, UP, UP, UP]),
+    "rvs_arena_buffers": (C.c_int, [VP, UP, UP, UP]),
+    "rvs_arena_list": (u32, [VP, u32, UP, u32]),
+    "rvs_rvem_parse": (C.c_int, [VP, u64, VP]),
+    "rvs_arena_load_rvem": (C.c_int, [VP, VP, u64, u32, UP, UP]),
     "rvs_bin_lights": (C.c_int, [VP, FP, FP, UP, UP, f32, f32, u32, u32, u32, u32, UP]),
 })
 
