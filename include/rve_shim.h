@@ -110,6 +110,40 @@ RVE_API int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float v
                            uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count,
                            rve_buffer* out_cluster_buffer);
 
+/* ---- one frame in one submission: the pass schedule of RenderEngine::Draw without its redundancy ---- */
+/* One camera of the frame (RenderTargetCollection.hpp:45-54 camData + its target's depth pyramid) */
+typedef struct rvs_frame_camera {
+    float view_proj[16], view[16], inv_proj[16];
+    float cam_pos[3];
+    float z_near, z_far;
+    uint32_t layers;
+    rve_pyramid pyramid;  /* target.depthPyramid */
+    rve_buffer depth;     /* last frame's depth, rebuilt into the pyramid first; RVE_BUFFER_INVALID keeps the pyramid */
+    uint32_t depth_width, depth_height;
+    uint32_t screen_dim[2];
+} rvs_frame_camera;
+typedef struct rvs_frame_desc {
+    const rvs_frame_camera* cameras;
+    uint32_t num_cameras;
+    const rvs_view* shadow_views;       /* cascades (rve_csm_cascades), spot lights, point-light faces */
+    const rve_pyramid* shadow_pyramids; /* one per shadow view */
+    uint32_t num_shadow_views;
+    rve_buffer point_lights;
+    uint32_t point_light_count;
+    rve_buffer spot_lights;
+    uint32_t spot_light_count;
+    uint32_t grid_size[3];              /* cluster grid */
+    uint32_t pass_mask;                 /* RVS_MAT_* classes to cull; 0 = all */
+} rvs_frame_desc;
+/* Replaces, for one frame, the per-pass culls and light binning of src/RenderEngine_Draw.cpp:1769-1866 (shadow views),
+ * :2177-2209 and :2567-2655 (six renderFromPerspective passes per camera, each with a cullTheRenderData over its
+ * material class; three of them re-bin the lights): pyramids built once, view-independent skinned work once, ALL
+ * views culled in one rve_cull_views launch (view v of every material's buffers: cameras first, then the shadow
+ * views, laid out as rvs_cull_static_views describes), lights binned once per camera. */
+RVE_API int rvs_frame_encode(rvs_world* w, const rvs_frame_desc* frame);
+/* the cluster buffer rvs_frame_encode filled for camera `camera` */
+RVE_API int rvs_frame_cluster_buffer(rvs_world* w, uint32_t camera, rve_buffer* out);
+
 /* ---- dirty-range upload: BufferedVRAMVector / EncodeSync (include/RavEngine/BufferedVRAMVector.hpp:33-209,
  * src/BufferedVRAMVector.cpp:27-144) - the step before the render-prep path ---- */
 typedef struct rvs_vector rvs_vector;

@@ -148,6 +148,8 @@ PROTOTYPES.update({
     "rvs_cull_skeletal": (C.c_int, [VP, FP, FP, u32, u32, u32, u32]),
     "rvs_skinned_outputs": (C.c_int, [VP, UP, UP]),
     "rvs_skinned_material_outputs": (C.c_int, [VP, u32, UP, UP, UP]),
+    "rvs_frame_encode": (C.c_int, [VP, VP]),
+    "rvs_frame_cluster_buffer": (C.c_int, [VP, u32, UP]),
     "rvs_arena_create": (C.c_int, [VP, u32, u32, C.POINTER(VP)]),
     "rvs_arena_destroy": (C.c_int, [VP]),
     "rvs_arena_allocate_mesh": (C.c_int, [VP, VP, UP]),
@@ -164,6 +166,17 @@ PROTOTYPES.update({
 
 class ShimView(C.Structure):
     _fields_ = [("view_proj", f32 * 16), ("cam_pos", f32 * 3), ("camera_layers", u32), ("shadow_pass", u32)]
+
+
+class FrameCamera(C.Structure):  # rvs_frame_camera
+    _fields_ = [("view_proj", f32 * 16), ("view", f32 * 16), ("inv_proj", f32 * 16), ("cam_pos", f32 * 3), ("z_near", f32), ("z_far", f32),
+                ("layers", u32), ("pyramid", u32), ("depth", u32), ("depth_width", u32), ("depth_height", u32), ("screen_dim", u32 * 2)]
+
+
+class FrameDesc(C.Structure):  # rvs_frame_desc
+    _fields_ = [("cameras", C.POINTER(FrameCamera)), ("num_cameras", u32), ("shadow_views", C.POINTER(ShimView)),
+                ("shadow_pyramids", C.POINTER(u32)), ("num_shadow_views", u32), ("point_lights", u32), ("point_light_count", u32),
+                ("spot_lights", u32), ("spot_light_count", u32), ("grid_size", u32 * 3), ("pass_mask", u32)]
 
 
 class SyncStats(C.Structure):

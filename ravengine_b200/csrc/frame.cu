@@ -58,6 +58,7 @@ int rvs_world_destroy(rvs_world* w) {
     }
     kill(w->cuboBuffer);
     kill(w->clusterBuffer);
+    for (auto& c : w->frameClusters) kill(c.first);
     kill(w->poseBuffer);
     for (auto b : w->skinnedOut) kill(b);
     delete w;

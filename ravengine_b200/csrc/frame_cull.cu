@@ -144,19 +144,18 @@ int rvs_cull_static_views(rvs_world* w, uint32_t num_views, const rvs_view* view
     return cull_static_impl(w, num_views, views, nullptr, nullptr, 0, 0, pass_mask, pyramids);
 }
 
-int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[16], const uint32_t grid_size[3],
-                   const uint32_t screen_dim[2], float z_near, float z_far, rve_buffer point_lights,
-                   uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count,
-                   rve_buffer* out_cluster_buffer) {
-    if (!w || !inv_proj || !view_mat || !grid_size || !screen_dim) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+// the clustered-light prologue into a given cluster buffer (the world's single lightClusterBuffer, or one per camera
+// of a frame)
+static int bin_lights_into(rvs_world* w, rve_buffer* buf, size_t* bytes, const float inv_proj[16], const float view_mat[16],
+                           const uint32_t grid_size[3], const uint32_t screen_dim[2], float z_near, float z_far, rve_buffer point_lights,
+                           uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count) {
     const uint64_t n = uint64_t(grid_size[0]) * grid_size[1] * grid_size[2];
     RVE_REQUIRE(n > 0 && n < 0x7FFFFFFFull, "bad cluster grid");
     // lightClusterBuffer: numClusters * sizeof(Cluster) (src/RenderEngine.cpp:839-845)
-    if (w->clusterBytes != n * sizeof(RveCluster)) {
-        int rc = realloc_buffer(w, &w->clusterBuffer, &w->clusterBytes, n, sizeof(RveCluster));
+    if (*bytes != n * sizeof(RveCluster)) {
+        int rc = realloc_buffer(w, buf, bytes, n, sizeof(RveCluster));
         if (rc) return rc;
     }
-    if (out_cluster_buffer) *out_cluster_buffer = w->clusterBuffer;
     // :930 — only when there is at least one point or spot light
     if (point_light_count == 0 && spot_light_count == 0) return 0;
     // :935-950 build the grid
@@ -167,7 +166,7 @@ int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[
     g.screenDim[0] = screen_dim[0];
     g.screenDim[1] = screen_dim[1];
     g.zFar = z_far;
-    int rc = rve_cluster_build(w->ctx, &g, w->clusterBuffer);
+    int rc = rve_cluster_build(w->ctx, &g, *buf);
     if (rc) return rc;
     // :953-970 assign lights; the reference dispatches numClusters/128 groups of 128
     RveGridAssignUBO a{};
@@ -175,7 +174,85 @@ int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[
     a.pointLightCount = point_light_count;
     a.spotLightCount = spot_light_count;
     const uint32_t invocations = uint32_t(n / 128) * 128;
-    return rve_cluster_assign(w->ctx, &a, w->clusterBuffer, point_lights, spot_lights, invocations);
+    return rve_cluster_assign(w->ctx, &a, *buf, point_lights, spot_lights, invocations);
+}
+
+int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[16], const uint32_t grid_size[3],
+                   const uint32_t screen_dim[2], float z_near, float z_far, rve_buffer point_lights,
+                   uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count,
+                   rve_buffer* out_cluster_buffer) {
+    if (!w || !inv_proj || !view_mat || !grid_size || !screen_dim) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    const int rc = bin_lights_into(w, &w->clusterBuffer, &w->clusterBytes, inv_proj, view_mat, grid_size, screen_dim, z_near, z_far,
+                                   point_lights, point_light_count, spot_lights, spot_light_count);
+    if (out_cluster_buffer) *out_cluster_buffer = w->clusterBuffer;
+    return rc;
+}
+
+// One frame's render-prep in one submission. The reference's Draw walks, per camera, six
+// renderFromPerspective passes (lit depth prepass + lit opaque, unlit depth prepass + unlit opaque, lit and unlit
+// transparent: src/RenderEngine_Draw.cpp:2177-2209, 2567-2655), each with its own cullTheRenderData over the
+// materials of the pass, re-bins the lights in every lit pass (:928-974, three times per camera) and runs one more
+// cull per shadow view (:1769-1866). The prepass and the colour pass of a material class see the same view, the same
+// pyramid and the same materials, and a material belongs to exactly one class, so: every pyramid is built once, ALL
+// views (cameras, then shadow views) are culled in ONE rve_cull_views launch over all requested materials, and the
+// lights are binned once per camera into that camera's own cluster buffer.
+int rvs_frame_encode(rvs_world* w, const rvs_frame_desc* f) {
+    if (!w || !f) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(f->num_cameras == 0 || f->cameras, "cameras is null");
+    RVE_REQUIRE(f->num_shadow_views == 0 || (f->shadow_views && f->shadow_pyramids), "shadow views / pyramids are null");
+    const uint32_t nviews = f->num_cameras + f->num_shadow_views;
+    RVE_REQUIRE(nviews >= 1 && nviews <= 128, "a frame holds 1..128 views");
+    int rc;
+    // generatePyramid for every camera that brought a depth buffer (last frame's depth: :2475-2514)
+    for (uint32_t c = 0; c < f->num_cameras; ++c) {
+        const rvs_frame_camera& cam = f->cameras[c];
+        if (cam.depth == RVE_BUFFER_INVALID) continue;
+        rc = rve_depth_pyramid_build(w->ctx, cam.pyramid, cam.depth, cam.depth_width, cam.depth_height);
+        if (rc) return rc;
+    }
+    // view-independent skinned work, once per frame (:530-668)
+    if (!w->skinnedMaterials.empty() && w->arena[0] != RVE_BUFFER_INVALID) {
+        uint32_t exist = 0;
+        rc = rvs_prepare_skeletal_mesh_buffers(w, &exist);
+        if (rc) return rc;
+        if (exist) {
+            rc = rvs_pose_skeletal_meshes(w);
+            if (rc) return rc;
+        }
+    }
+    std::vector<rvs_view> views(nviews);
+    std::vector<rve_pyramid> pyramids(nviews);
+    for (uint32_t c = 0; c < f->num_cameras; ++c) {
+        const rvs_frame_camera& cam = f->cameras[c];
+        std::memcpy(views[c].view_proj, cam.view_proj, 64);
+        std::memcpy(views[c].cam_pos, cam.cam_pos, 12);
+        views[c].camera_layers = cam.layers;
+        views[c].shadow_pass = 0;
+        pyramids[c] = cam.pyramid;
+    }
+    for (uint32_t s = 0; s < f->num_shadow_views; ++s) {
+        views[f->num_cameras + s] = f->shadow_views[s];
+        pyramids[f->num_cameras + s] = f->shadow_pyramids[s];
+    }
+    rc = cull_static_impl(w, nviews, views.data(), nullptr, nullptr, 0, 0, f->pass_mask ? f->pass_mask : RVS_MAT_ALL, pyramids.data());
+    if (rc) return rc;
+    // lights: once per camera
+    if (w->frameClusters.size() < f->num_cameras) w->frameClusters.resize(f->num_cameras, std::make_pair(rve_buffer(RVE_BUFFER_INVALID), size_t(0)));
+    for (uint32_t c = 0; c < f->num_cameras; ++c) {
+        const rvs_frame_camera& cam = f->cameras[c];
+        rc = bin_lights_into(w, &w->frameClusters[c].first, &w->frameClusters[c].second, cam.inv_proj, cam.view, f->grid_size, cam.screen_dim,
+                             cam.z_near, cam.z_far, f->point_lights, f->point_light_count, f->spot_lights, f->spot_light_count);
+        if (rc) return rc;
+    }
+    w->frameViews = nviews;
+    return 0;
+}
+
+int rvs_frame_cluster_buffer(rvs_world* w, uint32_t camera, rve_buffer* out) {
+    if (!w || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(camera < w->frameClusters.size(), "no such camera in the last frame");
+    *out = w->frameClusters[camera].first;
+    return 0;
 }
 
 }  // extern "C"

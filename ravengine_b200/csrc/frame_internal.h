@@ -1,6 +1,7 @@
 // frame_internal.h — World::RenderData stand-in used by the shim (frame.cu, frame_cull.cu, frame_skinned.cu)
 #pragma once
 #include <cstdint>
+#include <utility>
 #include <vector>
 
 #include "../../include/rve_shim.h"
@@ -72,6 +73,9 @@ struct rvs_world {
     // lightClusterBuffer (src/RenderEngine.cpp:839-845)
     rve_buffer clusterBuffer = RVE_BUFFER_INVALID;
     size_t clusterBytes = 0;
+    // rvs_frame_encode: one cluster buffer per camera of the frame (buffer, bytes)
+    std::vector<std::pair<rve_buffer, size_t>> frameClusters;
+    uint32_t frameViews = 0;
     // skinned path
     std::vector<rvs::SkinnedMesh> skinnedMeshes;
     std::vector<rvs::SkinnedMaterial> skinnedMaterials;

@@ -84,6 +84,40 @@ class World:
         ph = (C.c_uint32 * n)(*[p.handle for p in pyramids])
         _check(self.lib, self.lib.rvs_cull_static_views(self.h, n, arr, ph, mask))
 
+    def frame_encode(self, cameras, shadow_views=(), shadow_pyramids=(), points: Buffer | None = None, n_points: int = 0,
+                     spots: Buffer | None = None, n_spots: int = 0, grid=(12, 12, 24), mask=MAT_ALL):
+        """rvs_frame_encode. cameras: dicts(view_proj, view, inv_proj, cam_pos, z_near, z_far, layers, pyramid, depth (Buffer | None),
+        depth_wh, screen); shadow_views: (view_proj_cm, cam_pos, layers, shadow) tuples as in cull_static_views."""
+        from ._abi import FrameCamera, FrameDesc, ShimView
+
+        inv = 0xFFFFFFFF
+        cams = (FrameCamera * max(len(cameras), 1))()
+        for c, d in zip(cams, cameras):
+            c.view_proj[:] = [float(x) for x in d["view_proj"]]
+            c.view[:] = [float(x) for x in d["view"]]
+            c.inv_proj[:] = [float(x) for x in d["inv_proj"]]
+            c.cam_pos[:] = [float(x) for x in d["cam_pos"]]
+            c.z_near, c.z_far, c.layers = d["z_near"], d["z_far"], d.get("layers", 0xFFFFFFFF)
+            c.pyramid = d["pyramid"].handle
+            c.depth = d["depth"].handle if d.get("depth") is not None else inv
+            c.depth_width, c.depth_height = d.get("depth_wh", (0, 0))
+            c.screen_dim[:] = d["screen"]
+        n = len(shadow_views)
+        sv = (ShimView * max(n, 1))()
+        for s, (vp, cp, layers, shadow) in zip(sv, shadow_views):
+            s.view_proj[:] = [float(x) for x in vp]
+            s.cam_pos[:] = [float(x) for x in cp]
+            s.camera_layers, s.shadow_pass = layers, 1 if shadow else 0
+        sp = (C.c_uint32 * max(n, 1))(*[p.handle for p in shadow_pyramids])
+        f = FrameDesc(cams, len(cameras), sv, sp, n, points.handle if points else inv, n_points, spots.handle if spots else inv, n_spots,
+                      (C.c_uint32 * 3)(*grid), mask)
+        _check(self.lib, self.lib.rvs_frame_encode(self.h, C.byref(f)))
+
+    def frame_cluster_buffer(self, camera: int) -> Buffer:
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rvs_frame_cluster_buffer(self.h, camera, C.byref(out)))
+        return self._buf(out.value)
+
     def material_outputs(self, material: int):
         c, i, l, e = C.c_uint32(), C.c_uint32(), C.c_uint32(), C.c_uint32()
         _check(self.lib, self.lib.rvs_material_outputs(self.h, material, C.byref(c), C.byref(i), C.byref(l), C.byref(e)))

@@ -290,3 +290,77 @@ def test_cull_static_views_matches_per_view_culls(ctx):
     ctx.synchronize()
     _compare_static(ctx, w, mat_ids, mats, t, refs[0])
     w.destroy()
+
+
+def test_frame_encode_equals_the_reference_pass_schedule(ctx):
+    """rvs_frame_encode (one submission: pyramids, one view-batched cull over all material classes, lights binned once
+    per camera) against the reference's schedule run pass by pass through the same shim: per camera one
+    cullTheRenderData per material class + light binning, per shadow view one shadow cull."""
+    model, layers, flags, mats = _static_scene(seed=21)
+    kinds = [MAT_LIT_OPAQUE, MAT_UNLIT_OPAQUE]
+    cams = [scenes.default_camera(z_far=500.0), scenes.default_camera(z_far=400.0, fovy=75.0, eye=(90, 30, 40), target=(0, 0, 0))]
+    shadow_cams = [scenes.default_camera(z_far=600.0, eye=(0, 200, 1), target=(0, 0, 0)), scenes.default_camera(z_far=300.0, eye=(-120, 40, 0), target=(0, 0, 0)),
+                   scenes.default_camera(z_far=300.0, eye=(0, 10, 150), target=(0, 0, 0))]
+    rng = np.random.default_rng(5)
+    z = -rng.uniform(0.2, 100.0, size=300)
+    pos = np.stack([rng.uniform(-1, 1, size=300) * (-z), rng.uniform(-1, 1, size=300) * (-z) * 0.6, z], 1).astype(np.float32)
+    inten = np.exp(rng.uniform(np.log(0.05), np.log(5.0), size=300)).astype(np.float32)
+    points, spots = ctx.buffer_from_numpy(scenes.point_lights_bytes(pos[:200], inten[:200])), ctx.buffer_from_numpy(scenes.spot_lights_bytes(pos[200:], inten[200:]))
+    grid, screen = (16, 9, 24), (1280, 720)
+    depths = [ctx.buffer_from_numpy(scenes.synth_depth(640, 360, c, n_occluders=15, seed=3 + i)) for i, c in enumerate(cams)]
+    empty = ctx.create_pyramid(64)  # shadow passes: zeroed pyramid = nothing occluded
+
+    # ---- the reference's schedule, pass by pass ----
+    w1, mat1, keep1 = _world_from(ctx, model, layers, flags, mats, kinds=kinds)
+    want = {}  # (view, material) -> (indirect, ids)
+    want_clusters = []
+    views_all = [(c, False) for c in cams] + [(c, True) for c in shadow_cams]
+    for v, (cam, shadow) in enumerate(views_all):
+        pyr = empty
+        if not shadow:
+            pyr = ctx.create_pyramid(360)
+            ctx.build_pyramid(pyr, depths[v], 640, 360)
+        for mat, kind in zip(mat1, kinds):
+            w1.cull_static(cam.view_proj_cm, cam.pos, pyr, shadow=shadow, mask=kind)
+            ctx.synchronize()
+            cull_b, ind_b, lods, ents = w1.material_outputs(mat)
+            want[(v, mat)] = (ind_b.download(np.uint32).reshape(-1, 5)[:lods].copy(), cull_b.download(np.uint32)[:lods * ents].copy())
+        if not shadow:
+            out = w1.bin_lights(cam.inv_proj_cm, scenes.colmajor(np.eye(4)), grid, screen, cam.z_near, cam.z_far, points, 200, spots, 100)
+            ctx.synchronize()
+            want_clusters.append(out.download(np.uint32).copy())
+
+    # ---- one submission ----
+    w2, mat2, keep2 = _world_from(ctx, model, layers, flags, mats, kinds=kinds)
+    pyrs = [ctx.create_pyramid(360) for _ in cams]
+    cam_descs = [dict(view_proj=c.view_proj_cm, view=scenes.colmajor(np.eye(4)), inv_proj=c.inv_proj_cm, cam_pos=c.pos, z_near=c.z_near, z_far=c.z_far,
+                      pyramid=p, depth=d, depth_wh=(640, 360), screen=screen) for c, p, d in zip(cams, pyrs, depths)]
+    launches0 = ctx.launch_count
+    w2.frame_encode(cam_descs, [(c.view_proj_cm, c.pos, 0xFFFFFFFF, True) for c in shadow_cams], [empty] * len(shadow_cams), points, 200, spots, 100, grid)
+    ctx.synchronize()
+    frame_launches = ctx.launch_count - launches0
+    t = host_tables.build_static_tables(mats)
+    ci = 0
+    for mat, m in zip(mat2, mats):
+        cull_b, ind_b, lods, ents = w2.material_outputs(mat)
+        all_ind, all_ids = ind_b.download(np.uint32).reshape(-1, 5), cull_b.download(np.uint32)
+        rng_c = range(ci, ci + len(m.commands))
+        for v in range(len(views_all)):
+            r_ind, r_ids = want[(v, mat)]
+            g_ind, g_ids = all_ind[v * lods:(v + 1) * lods], all_ids[v * lods * ents:(v + 1) * lods * ents]
+            np.testing.assert_array_equal(g_ind, r_ind)
+            # slices of one material's buffers: its cubos carry offsets relative to that material, as in the tables
+            for x, y in zip(host_tables.sorted_slices(r_ind, r_ids, t.cubos, rng_c), host_tables.sorted_slices(g_ind, g_ids, t.cubos, rng_c)):
+                np.testing.assert_array_equal(x, y)
+        ci += len(m.commands)
+    for c in range(len(cams)):
+        # index entries past a cluster's counts are never written (stale in a reused buffer, as in the reference)
+        got, ref = w2.frame_cluster_buffer(c).download(np.uint32).reshape(-1, 40), want_clusters[c].reshape(-1, 40)
+        np.testing.assert_array_equal(got[:, :8], ref[:, :8])
+        assert ref[:, 6].max() > 0 and ref[:, 7].max() > 0
+        live = np.concatenate([np.arange(16)[None, :] < ref[:, 6:7], np.arange(16)[None, :] < ref[:, 7:8]], axis=1)
+        np.testing.assert_array_equal(got[:, 8:][live], ref[:, 8:][live])
+    # 2 pyramid builds x 2 launches + (table upload + prepare + cull) + 2 x (cluster build + assign prepare/assign)
+    assert frame_launches <= 4 + 4 + 2 * 4, frame_launches
+    w1.destroy()
+    w2.destroy()
