@@ -107,6 +107,7 @@ struct UploadBlock {
 };
 // one CTA per segment; the payload is read from the parameter (constant) bank
 __global__ void upload_params_kernel(const __grid_constant__ UploadBlock blk) {
+    pdl_trigger();  // a programmatic dependent (cubo_prepare_kernel) may become resident; it waits for this grid's completion
     const uint32_t s = blockIdx.x;
     const uint32_t* src = blk.data + blk.first[s];
     uint32_t* dst = blk.dst[s];
