@@ -156,15 +156,30 @@ pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t d
     }
     const uint32_t first = uint32_t(footmin_level_offset(dim, 1));
     const uint32_t end = uint32_t(footmin_level_offset(dim, topLevel < levels ? topLevel : levels));
-    const uint32_t i = (blockIdx.x - 1) * blockDim.x + threadIdx.x + first;
-    uint32_t level = 1;
-    while (level + 1 < levels && i >= uint32_t(footmin_level_offset(dim, level + 1))) ++level;
-    const uint32_t n = dim >> level, n1 = n + 1;
-    const uint32_t local = i - uint32_t(footmin_level_offset(dim, level));
-    const float* img = pyr + pyr_level_offset(dim, level);
+    // two entries per thread (i, i + blockDim.x): the whole grid is resident in one wave at dim 1024
+    const uint32_t base = (blockIdx.x - 1) * (2 * blockDim.x) + threadIdx.x + first;
+    uint32_t idx[2], n[2], fx[2], fy[2];
+    const float* img[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const uint32_t i = base + k * blockDim.x;
+        uint32_t level = 1;
+        while (level + 1 < levels && i >= uint32_t(footmin_level_offset(dim, level + 1))) ++level;
+        n[k] = dim >> level;
+        const uint32_t local = i - uint32_t(footmin_level_offset(dim, level));
+        fx[k] = local % (n[k] + 1);
+        fy[k] = local / (n[k] + 1);
+        img[k] = pyr + pyr_level_offset(dim, level);
+        idx[k] = i;
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (i >= end) return;
-    fm[i] = footmin_entry(img, n, local % n1, local / n1);
+    float v[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+        if (idx[k] < end) v[k] = footmin_entry(img[k], n[k], fx[k], fy[k]);
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+        if (idx[k] < end) fm[idx[k]] = v[k];
 }
 
 // footprint-min chain (see PyramidRec::footmin): one thread per output, levels firstLevel.. in one launch
@@ -295,7 +310,7 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
             const uint32_t lastFm = topLevel < p->levels ? topLevel : p->levels;
             const uint32_t entries = uint32_t(footmin_level_offset(p->dim, lastFm) - footmin_level_offset(p->dim, 1));
             cudaLaunchConfig_t cfg{};
-            cfg.gridDim = dim3(1 + (entries + kPyrThreads - 1) / kPyrThreads);
+            cfg.gridDim = dim3(1 + (entries + 2 * kPyrThreads - 1) / (2 * kPyrThreads));
             cfg.blockDim = dim3(kPyrThreads);
             cfg.stream = ctx->stream;
             cudaLaunchAttribute attr{};
