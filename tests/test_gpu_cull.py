@@ -198,3 +198,30 @@ def test_c2_full_size_10m_matches_oracle(ctx):
     t, ref = _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=2160, nthreads=oracle.default_workers())
     counts = np.concatenate([b.reshape(-1, 5)[:, 1] for b in ref if b is not None and b.dtype == np.uint32 and b.ndim == 2])
     assert int(counts.sum()) == 2405721  # the bench's visible count for this seed
+
+
+@pytest.mark.parametrize("n", [909_313, 1_000_003])
+def test_dynamic_tail_rounds_mixed_paths(ctx, n):
+    """Launches just past the threshold where the cull kernel hands its last rounds out through a global counter
+    (rounds > 4 x resident warps, csrc/cull.cu next_issue): ragged total, broken id runs in the part of the dispatch the
+    tail covers, a dispatch shorter than the CUBO sum. Every round must be processed exactly once."""
+    rng = np.random.default_rng(n)
+    model = scenes.random_transforms(rng, n, 400.0, 80.0)
+    layers = np.full(n, 0xFFFFFFFF, np.uint32)
+    layers[rng.random(n) < 0.03] = 0
+    flags = np.full(n, 0xFFFF, np.uint16)
+    flags[rng.random(n) < 0.1] &= 0xFFFC
+    ids = np.arange(n, dtype=np.uint32)
+    tail = n - 60_000  # the last 60k invocations: reversed blocks of 50 ids -> no 64-id run, gathers and dense halves
+    blocks = [ids[i:i + 50] for i in range(tail, n, 50)]
+    ids[tail:] = np.concatenate(blocks[::-1])
+    cuts = [0, n // 3, n // 3 + 11, n]
+    mats = []
+    for i in range(3):
+        mesh = scenes.simple_mesh(scenes.CUBE_RADIUS, (0.0, 50.0, 140.0) if i != 1 else (math.inf,), base=i * 500)
+        mats.append(scenes.MaterialDraws([scenes.DrawCommand(mesh, ids[cuts[i]:cuts[i + 1]])]))
+    cam = scenes.default_camera(z_far=1000.0)
+    depth = scenes.synth_depth(640, 360, cam, n_occluders=25)
+    t, ref = _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=360, nthreads=oracle.default_workers())
+    if n == 1_000_003:  # and with the dispatch cut short (defaultcull.csh:166-171 bounds by the dispatch as well)
+        _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=360, groups=(n - 70_000) // 64, nthreads=oracle.default_workers())
