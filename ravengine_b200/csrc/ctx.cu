@@ -113,6 +113,28 @@ __global__ void upload_params_kernel(const __grid_constant__ UploadBlock blk) {
     uint32_t* dst = blk.dst[s];
     for (uint32_t i = threadIdx.x; i < blk.count[s]; i += blockDim.x) dst[i] = src[i];
 }
+
+int upload_batch_raw(rve_ctx* ctx, const RawSegment* segs, uint32_t n) {
+    if (n == 0) return 0;
+    if (n > kUploadMaxSegs) return RVE_ERR_UNSUPPORTED;
+    UploadBlock blk{};
+    uint32_t words = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        if ((segs[i].bytes & 3) || (reinterpret_cast<uintptr_t>(segs[i].dst) & 3) || words + segs[i].bytes / 4 > kUploadMaxWords)
+            return RVE_ERR_UNSUPPORTED;
+        blk.dst[i] = static_cast<uint32_t*>(segs[i].dst);
+        blk.first[i] = words;
+        blk.count[i] = uint32_t(segs[i].bytes / 4);
+        if (segs[i].bytes) memcpy(blk.data + words, segs[i].src, segs[i].bytes);
+        words += uint32_t(segs[i].bytes / 4);
+    }
+    if (!words) return 0;
+    blk.n = n;
+    upload_params_kernel<<<n, 128, 0, ctx->stream>>>(blk);
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
 }  // namespace rve
 
 extern "C" {
@@ -261,36 +283,22 @@ int rve_buffer_upload_batch(rve_ctx* ctx, const rve_upload_segment* segs, uint32
     DeviceGuard g(ctx->device);
     // Small tables (the per-pass CUBO and indirect-init tables) travel as KERNEL PARAMETERS: one launch writes every
     // segment, instead of one staged host->device copy (a DMA operation of ~2 us on the stream) per segment.
-    UploadBlock blk{};
-    bool viaParams = n > 0 && n <= kUploadMaxSegs;
-    uint32_t words = 0;
-    for (uint32_t i = 0; i < n && viaParams; ++i) {
+    std::vector<RawSegment> raw(n);
+    for (uint32_t i = 0; i < n; ++i) {
         BufferRec* b = get_buffer(ctx, segs[i].dst, "upload batch");
         if (!b) return RVE_ERR_BAD_HANDLE;
         if (segs[i].dst_offset + segs[i].bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "upload out of range");
-        if ((segs[i].bytes & 3) || (segs[i].dst_offset & 3) || (reinterpret_cast<uintptr_t>(b->ptr) & 3) ||
-            words + segs[i].bytes / 4 > kUploadMaxWords) {
-            viaParams = false;
-            break;
-        }
-        blk.dst[i] = reinterpret_cast<uint32_t*>(static_cast<char*>(b->ptr) + segs[i].dst_offset);
-        blk.first[i] = words;
-        blk.count[i] = uint32_t(segs[i].bytes / 4);
-        if (segs[i].bytes) memcpy(blk.data + words, segs[i].src, segs[i].bytes);
-        words += uint32_t(segs[i].bytes / 4);
+        raw[i] = RawSegment{static_cast<char*>(b->ptr) + segs[i].dst_offset, segs[i].src, segs[i].bytes};
     }
-    if (!viaParams) {
+    const int rc = upload_batch_raw(ctx, raw.data(), n);
+    if (rc == RVE_ERR_UNSUPPORTED) {  // too large or unaligned for one parameter block: plain copies
         for (uint32_t i = 0; i < n; ++i) {
-            const int rc = rve_buffer_upload(ctx, segs[i].dst, segs[i].dst_offset, segs[i].src, segs[i].bytes);
-            if (rc) return rc;
+            const int rc2 = rve_buffer_upload(ctx, segs[i].dst, segs[i].dst_offset, segs[i].src, segs[i].bytes);
+            if (rc2) return rc2;
         }
         return 0;
     }
-    if (!words) return 0;
-    blk.n = n;
-    upload_params_kernel<<<n, 128, 0, ctx->stream>>>(blk);
-    ctx->launches++;
-    RVE_CUDA(cudaGetLastError());
+    if (rc) return rc;
     for (uint32_t i = 0; i < n; ++i) pyramid_note_buffer_write(ctx, segs[i].dst);
     return 0;
 }

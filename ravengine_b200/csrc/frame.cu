@@ -87,6 +87,7 @@ int rvs_mesh_collection_create(rvs_world* w, float radius, uint32_t num_lods, co
     if (rc) return rc;
     rc = rve_buffer_upload(w->ctx, m.lodDistances, 0, lod_distances, num_lods * sizeof(float));
     if (rc) return rc;
+    m.lodDistancesHost.assign(lod_distances, lod_distances + num_lods);
     w->meshes.push_back(m);
     *out_mesh = uint32_t(w->meshes.size() - 1);
     return 0;

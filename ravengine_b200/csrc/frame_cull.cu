@@ -51,6 +51,7 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     std::vector<std::vector<RveIndirectIndexedCommand>> indirectTables;
     std::vector<rve_upload_segment> uploads;
     std::vector<RveViewStride> strides(globalCubo.numCubos);
+    std::vector<const float*> lodHost(globalCubo.numCubos, nullptr);  // per written CUBO: its mesh's LOD distances
     for (auto& m : w->materials) {
         if (!(m.kind & pass_mask)) continue;
         // :1265-1286 prepass
@@ -108,6 +109,7 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
             cubo.lodDistanceBufferBindlessHandle = rve_buffer_bindless_index(ctx, mesh.lodDistances);
             cubo.entityIDInputBufferBindlessHandle = rve_buffer_bindless_index(ctx, c.entityIds);
             strides[cuboIdx] = RveViewStride{numLODs, uint32_t(cullingbufferTotalSlots)};
+            lodHost[cuboIdx] = mesh.lodDistancesHost.data();
             cuboStaging[cuboIdx++] = cubo;
             cubo.indirectBufferOffset += lodsForThisMesh;
             cubo.cullingBufferOffset += lodsForThisMesh * c.count;
@@ -115,11 +117,36 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     }
     // :1367-1375 copy to the cubo buffer
     uploads.push_back({w->cuboBuffer, 0, cuboStaging.data(), cuboStaging.size() * sizeof(RveCullingUBOinstance)});
-    rc = rve_buffer_upload_batch(ctx, uploads.data(), uint32_t(uploads.size()));
-    if (rc) return rc;
+    // The CUBO table was built right here, so the tables the cull derives from it (prefix sums, resolved handles, squared
+    // LOD thresholds: cubo_prepare_kernel) are built on the host too and ride in the same parameter-block upload - one
+    // launch and one dependent kernel less per pass. Entries past the written ones (numCubos counts LODs) are zero:
+    // numObjects 0, never selected. Falls back to the plain path when the block would not fit.
+    uint32_t cullFlags = 0;
+    {
+        std::vector<RawSegment> raw;
+        HostCuboStaging hostTables;
+        bool ok = true;
+        for (const rve_upload_segment& u : uploads) {
+            char* base = static_cast<char*>(rve_buffer_device_ptr(ctx, u.dst));
+            if (!base || u.dst_offset + u.bytes > rve_buffer_size(ctx, u.dst)) ok = false;
+            raw.push_back(RawSegment{base + u.dst_offset, u.src, u.bytes});
+        }
+        static const float kNoLods[4] = {0.f, 0.f, 0.f, 0.f};
+        for (auto& lp : lodHost)
+            if (!lp) lp = kNoLods;
+        if (ok && cull_host_tables(ctx, cuboStaging.data(), globalCubo.numCubos, lodHost.data(), &hostTables, &raw) == 0) {
+            rc = upload_batch_raw(ctx, raw.data(), uint32_t(raw.size()));
+            if (rc == 0) cullFlags = kCullTablesPrepared;
+            else if (rc != RVE_ERR_UNSUPPORTED) return rc;
+        }
+    }
+    if (!cullFlags) {
+        rc = rve_buffer_upload_batch(ctx, uploads.data(), uint32_t(uploads.size()));
+        if (rc) return rc;
+    }
     // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
     const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));
-    if (!nviews) return rve_cull(ctx, &globalCubo, w->cuboBuffer, w->model, w->layers, w->flagsBuf, pyramids[0], groups);
+    if (!nviews) return cull_launch(ctx, &globalCubo, 0, &pyramids[0], nullptr, w->cuboBuffer, w->model, w->layers, w->flagsBuf, groups, cullFlags);
     std::vector<RveCullingUBO> ubos(nviews, globalCubo);
     for (uint32_t v = 0; v < nviews; ++v) {
         std::memcpy(ubos[v].viewProj, views[v].view_proj, 64);
@@ -127,7 +154,8 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
         ubos[v].cameraRenderLayers = views[v].camera_layers;
         ubos[v].singleInstanceModeAndShadowMode = views[v].shadow_pass ? RVE_CULL_SHADOW_MODE : 0u;
     }
-    return rve_cull_views(ctx, ubos.data(), nviews, pyramids, strides.data(), w->cuboBuffer, w->model, w->layers, w->flagsBuf, groups);
+    RVE_REQUIRE(nviews <= 128, "1..128 views per batch");
+    return cull_launch(ctx, ubos.data(), nviews, pyramids, strides.data(), w->cuboBuffer, w->model, w->layers, w->flagsBuf, groups, cullFlags);
 }
 
 extern "C" {

@@ -17,6 +17,7 @@ struct MeshCollection {
     float radius = 0;
     std::vector<LODMesh> lods;
     rve_buffer lodDistances = RVE_BUFFER_INVALID;
+    std::vector<float> lodDistancesHost;  // the same values, for the host-built cull tables
 };
 
 // MDIICommand::command (include/RavEngine/World.hpp:339-349)

@@ -108,6 +108,28 @@ PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h);
 // makes sure the device pointer table reflects the host table (enqueued on the stream)
 int sync_table(rve_ctx* ctx);
 int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes);
+// Small host tables written by ONE kernel whose payload travels as kernel parameters (ctx.cu). Raw destinations; returns
+// RVE_ERR_UNSUPPORTED (nothing enqueued) when the segments do not fit one launch.
+struct RawSegment {
+    void* dst;
+    const void* src;
+    size_t bytes;
+};
+int upload_batch_raw(rve_ctx* ctx, const RawSegment* segs, uint32_t n);
+// The tables cubo_prepare_kernel derives from a CUBO array, built on the host instead (cull.cu) for a caller that has the
+// CUBOs and the LOD distances in host memory (the shim): appended as raw segments aimed at the context's scratch tables.
+// `keep` owns the staging memory until the upload call returns.
+struct HostCuboStaging {
+    std::vector<uint32_t> start;
+    std::vector<unsigned char> res;
+    std::vector<float> lodSq;
+};
+int cull_host_tables(rve_ctx* ctx, const RveCullingUBOinstance* cubos, uint32_t n, const float* const* lodDistHost, HostCuboStaging* keep,
+                     std::vector<RawSegment>* segs);
+constexpr uint32_t kCullTablesPrepared = 1u;  // cull_launch flag: the scratch tables of this CUBO array are already uploaded
+int cull_launch(rve_ctx* ctx, const RveCullingUBO* ubo, uint32_t num_views, const rve_pyramid* pyramids, const RveViewStride* strides,
+                rve_buffer cubos, rve_buffer model_matrices, rve_buffer render_layers, rve_buffer per_object_flags, uint32_t num_groups_x,
+                uint32_t flags);
 // (re)derives the footprint-min chain of a pyramid from its texels when they changed since the last derivation
 int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel = 0);
 // marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)
