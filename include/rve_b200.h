@@ -335,6 +335,15 @@ typedef struct RveViewStride {
 RVE_API int rve_cull_views(rve_ctx* ctx, const RveCullingUBO* ubos, uint32_t num_views, const rve_pyramid* pyramids,
                            const RveViewStride* strides, rve_buffer cubos, rve_buffer model_matrices,
                            rve_buffer render_layers, rve_buffer per_object_flags, uint32_t num_groups_x);
+/* rve_cull_views with the view-projection matrices taken from DEVICE memory: view v uses the 16 floats (column-major)
+ * at view_proj_matrices[matrix_index[v] * 16]; ubos[v].viewProj is ignored, every other field of ubos[v] applies.
+ * Lets the shadow views of a frame consume rve_csm_cascades' output (the lightViewProj the reference uploads in
+ * src/RenderEngine_Draw.cpp:282 and reads back per shadow pass at :1769-1866) without a host round trip; the frustum
+ * planes are derived on the device with the same arithmetic as on the host (bit-identical results). */
+RVE_API int rve_cull_views_matrices(rve_ctx* ctx, const RveCullingUBO* ubos, uint32_t num_views, rve_buffer view_proj_matrices,
+                                    const uint32_t* matrix_index, const rve_pyramid* pyramids, const RveViewStride* strides,
+                                    rve_buffer cubos, rve_buffer model_matrices, rve_buffer render_layers,
+                                    rve_buffer per_object_flags, uint32_t num_groups_x);
 
 /* ------------------------------------------------------------------ */
 /* a-3 skinning — shaders/skinning_cs.csh                              */

@@ -105,6 +105,7 @@ PROTOTYPES = {
     "rve_depth_pyramid_texels_changed": (C.c_int, [VP, u32]),
     "rve_cull": (C.c_int, [VP, C.POINTER(CullingUBO), u32, u32, u32, u32, u32, u32]),
     "rve_cull_views": (C.c_int, [VP, C.POINTER(CullingUBO), u32, C.POINTER(u32), VP, u32, u32, u32, u32, u32]),
+    "rve_cull_views_matrices": (C.c_int, [VP, C.POINTER(CullingUBO), u32, u32, C.POINTER(u32), C.POINTER(u32), VP, u32, u32, u32, u32, u32]),
     "rve_skin": (C.c_int, [VP, C.POINTER(SkinningUBO), C.POINTER(u32), C.POINTER(u32), u32, u32]),
     "rve_skinned_drawcall_prepare": (C.c_int, [VP, C.POINTER(SkinningPrepareUBO), u32]),
     "rve_cluster_build": (C.c_int, [VP, C.POINTER(GridBuildUBO), u32]),

@@ -236,6 +236,19 @@ def cull_views(ctx: "Context", ubos: list, pyramids: list, strides, cubos: Buffe
                                            num_groups_x))
 
 
+def cull_views_matrices(ctx: "Context", ubos: list, matrices: Buffer, matrix_index, pyramids: list, strides, cubos: Buffer, model: Buffer,
+                        layers: Buffer, flags: Buffer, num_groups_x: int) -> None:
+    """rve_cull_views_matrices: as cull_views, the view-projection of view v read from `matrices` (device) at mat4 index
+    matrix_index[v] - e.g. the lightViewProj output of csm_cascades."""
+    n = len(ubos)
+    arr = (CullingUBO * n)(*ubos)
+    ph = (C.c_uint32 * n)(*[p.handle for p in pyramids])
+    ix = (C.c_uint32 * n)(*[int(i) for i in matrix_index])
+    st = np.ascontiguousarray(strides, dtype=np.uint32)
+    _check(ctx.lib, ctx.lib.rve_cull_views_matrices(ctx.h, arr, n, matrices.handle, ix, ph, st.ctypes.data, cubos.handle, model.handle,
+                                                    layers.handle, flags.handle, num_groups_x))
+
+
 # rve_b200.h RveCsmCamera / RveCsmLight as numpy record types (host staging of rve_csm_cascades)
 CSM_CAMERA = np.dtype([("viewOnly", "<f4", 16), ("zNear", "<f4"), ("zFar", "<f4"), ("tanHalfFovy", "<f4"), ("aspect", "<f4")])
 CSM_LIGHT = np.dtype([("direction", "<f4", 3), ("castsShadows", "<u4"), ("numCascades", "<u4"), ("shadowCascades", "<f4", 4),

@@ -186,6 +186,7 @@ int rve_ctx_destroy(rve_ctx* ctx) {
     if (ctx->d_cubo_start) cudaFree(ctx->d_cubo_start);
     if (ctx->d_cubo_res) cudaFree(ctx->d_cubo_res);
     if (ctx->d_cubo_lod) cudaFree(ctx->d_cubo_lod);
+    if (ctx->d_view_index) cudaFree(ctx->d_view_index);
     if (ctx->d_view_stride) cudaFree(ctx->d_view_stride);
     if (ctx->d_views) cudaFree(ctx->d_views);
     if (ctx->d_lights) cudaFree(ctx->d_lights);

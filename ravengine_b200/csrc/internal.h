@@ -83,6 +83,10 @@ struct rve_ctx {
     size_t d_cubo_start_cap = 0;
     void* d_cubo_res = nullptr;  // resolved CUBO records (cull.cu CuboRes)
     size_t d_cubo_res_cap = 0;
+    void* d_view_index = nullptr;  // rve_cull_views_matrices: per-view matrix indices
+    size_t d_view_index_cap = 0;
+    const float* view_matrices = nullptr;         // set for the duration of one rve_cull_views_matrices call
+    const uint32_t* view_matrix_index = nullptr;  // (host array of that call)
     void* d_cubo_lod = nullptr;  // per-CUBO squared LOD thresholds
     size_t d_cubo_lod_cap = 0;
     void* d_views = nullptr;  // view table of a view-batched cull

@@ -134,3 +134,92 @@ def test_cull_views_single_view_equals_rve_cull(ctx):
     ctx.synchronize()
     got = [b.download(np.uint8).view(h.dtype)[: h.size].reshape(h.shape) for b, h in zip(dev, t.bindless)]
     compare_cull_outputs(t, mats, want, got)
+
+
+def test_cascades_feed_the_view_batch_without_a_host_round_trip(ctx):
+    """rve_csm_cascades -> rve_cull_views_matrices: the shadow cascades' lightViewProj stay in device memory and drive the
+    view-batched cull (planes derived on the device). Must equal the same batch driven by host copies of the matrices,
+    which in turn is checked against the oracle per view."""
+    from ravengine_b200.api import CSM_CAMERA, CSM_LIGHT, csm_camera_params, csm_cascades, cull_views_matrices
+    from tests.golden import make_golden_csm as mg
+
+    rng = np.random.default_rng(77)
+    n = 40_000
+    model = scenes.random_transforms(rng, n, 150.0, 40.0)
+    layers = np.full(n, 0xFFFFFFFF, np.uint32)
+    flags = np.full(n, 0xFFFF, np.uint16)
+    flags[rng.random(n) < 0.2] &= 0xFFFB  # not every instance casts shadows
+    ids = np.arange(n, dtype=np.uint32)
+    mats = [scenes.MaterialDraws([scenes.DrawCommand(scenes.simple_mesh(scenes.CUBE_RADIUS, (0.0, 60.0, 200.0)), ids[: n // 2])]),
+            scenes.MaterialDraws([scenes.DrawCommand(scenes.simple_mesh(scenes.SPHERE_RADIUS, (math.inf,), base=500), ids[n // 2:])])]
+    t = host_tables.build_static_tables(mats)
+
+    # cascades of one camera x two lights on the device
+    cam = scenes.default_camera(z_near=0.5, z_far=400.0, eye=(0, 20, 120), target=(0, 0, 0))
+    cams = np.zeros(1, CSM_CAMERA)
+    cams[0]["viewOnly"] = np.asarray(cam.view_cm if hasattr(cam, "view_cm") else mg.random_view(rng), np.float32)
+    cams[0]["zNear"], cams[0]["zFar"] = 0.5, 400.0
+    cams[0]["tanHalfFovy"], cams[0]["aspect"] = csm_camera_params(60.0, 1920, 1080)
+    lights = np.zeros(2, CSM_LIGHT)
+    lights["direction"] = np.array([[0.3, -0.9, 0.2], [-0.5, -0.7, -0.4]], np.float32) / np.linalg.norm([[0.3, -0.9, 0.2], [-0.5, -0.7, -0.4]], axis=1, keepdims=True).astype(np.float32)
+    lights["castsShadows"] = 1
+    lights["numCascades"] = [4, 2]
+    lights["shadowCascades"] = np.array([[0.05, 0.15, 0.4, 1.0], [0.1, 0.5, 1.0, 1.0]], np.float32)
+    lights["maxShadowDistanceFactor"] = 1.0
+    d_vp = ctx.create_buffer(2 * 4 * 64)
+    d_vp.zero()
+    csm_cascades(ctx, ctx.buffer_from_numpy(cams.view(np.uint8)), 1, ctx.buffer_from_numpy(lights.view(np.uint8)), 2, d_vp)
+    ctx.synchronize()
+    vp_host = d_vp.download(np.float32).reshape(2, 4, 16)
+    index = [0, 1, 2, 3, 4, 5]  # light 0: cascades 0..3 (matrices 0..3), light 1: cascades 0..1 (matrices 4, 5)
+    assert all(np.isfinite(vp_host.reshape(8, 16)[i]).all() and np.any(vp_host.reshape(8, 16)[i]) for i in index)
+    V = len(index)
+
+    empty_dim, empty_levels = oracle.pyramid_dims(64)
+    empty = np.zeros((4 * empty_dim * empty_dim - 1) // 3, np.float32)
+    ubos, refs = [], []
+    for i in index:
+        ubo = make_ubo(vp_host.reshape(8, 16)[i], cam.pos, t.num_cubos, shadow=True)
+        refs.append(oracle_cull(t, ubo, model, layers, flags, empty, empty_dim, empty_levels, nthreads=4))
+        ubos.append(ubo)
+
+    def run(device_matrices: bool):
+        out_handles = {}
+        for c in t.cubos:
+            out_handles[int(c["idOutputBufferBindlessHandle"])] = "cull"
+            out_handles[int(c["indirectOutputBufferBindlessHandle"])] = "ind"
+        dev = [ctx.buffer_from_numpy(np.concatenate([b.reshape(-1)] * V)) if i in out_handles else ctx.buffer_from_numpy(b)
+               for i, b in enumerate(t.bindless)]
+        cubos = t.cubos.copy()
+        for f in ("idOutputBufferBindlessHandle", "entityIDInputBufferBindlessHandle", "indirectOutputBufferBindlessHandle",
+                  "lodDistanceBufferBindlessHandle"):
+            cubos[f] = np.array([dev[int(h)].bindless for h in t.cubos[f]], dtype=np.uint32)
+        strides = np.array([[t.bindless[int(c["indirectOutputBufferBindlessHandle"])].shape[0],
+                             t.bindless[int(c["idOutputBufferBindlessHandle"])].size] for c in t.cubos], np.uint32)
+        args = (ctx.buffer_from_numpy(cubos.view(np.uint8)), ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(layers), ctx.buffer_from_numpy(flags),
+                (t.total_entities + 63) // 64)
+        pyrs = [ctx.create_pyramid(64)] * V
+        if device_matrices:
+            blank = [make_ubo(np.zeros(16, np.float32), cam.pos, t.num_cubos, shadow=True) for _ in index]  # viewProj must be ignored
+            cull_views_matrices(ctx, blank, d_vp, index, pyrs, strides, *args)
+        else:
+            cull_views(ctx, ubos, pyrs, strides, *args)
+        ctx.synchronize()
+        per_view = []
+        for v in range(V):
+            got = []
+            for i, b in enumerate(t.bindless):
+                if b is None:
+                    got.append(None)
+                    continue
+                raw = dev[i].download(np.uint8).view(b.dtype)
+                got.append(raw[v * b.size:(v + 1) * b.size].reshape(b.shape) if i in out_handles else raw[: b.size].reshape(b.shape))
+            per_view.append(got)
+        return per_view
+
+    visible = 0
+    for device_matrices in (False, True):
+        for v, got in enumerate(run(device_matrices)):
+            compare_cull_outputs(t, mats, refs[v], got)
+            visible += sum(int(b.reshape(-1, 5)[:, 1].sum()) for b in got if b is not None and b.ndim == 2 and b.shape[1] == 5)
+    assert visible > 0
