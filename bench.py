@@ -236,6 +236,8 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     n = args.instances
     sc = DeviceScene(n, rank, local_rank)
+    # host placement before any pinned allocation: this process onto the CPUs / NUMA node of its GPU's PCIe root
+    affinity = sc.ctx.bind_host_to_device(cpus=not args.no_numa_bind, memory=not args.no_numa_bind)
     ex = None
     if world_size > 1 or args.force_exchange:
         from ravengine_b200.sharding import ShardedCull
@@ -312,11 +314,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     if args.no_e2e:
         e2e = None
     else:
-        e2e = run_e2e(sc, args, torch, barrier, dist)
-        e2e["dirty_fraction"] = 1.0
-        e2e["by_dirty_fraction"] = run_e2e_dirty(sc, args, torch, barrier, dist)
-        e2e["by_dirty_fraction_note"] = ("same step with worldTransforms in a BufferedVRAMVector: only rows flagged since the last frame "
-                                         "are uploaded (the reference's EncodeSync policy, GPU-pull variant); keys = fraction of rows flagged per step")
+        e2e = run_e2e(sc, args, torch, barrier, dist, affinity)
 
     if rank != 0:
         if dist:
@@ -355,74 +353,171 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         dist.destroy_process_group()
 
 
-def run_e2e(sc: DeviceScene, args, torch, barrier, dist):
-    """Same step, but every per-entity input starts in pinned HOST memory and is uploaded inside the timed
-    region (100 % dirty transforms: the worst case of the reference's EncodeSync), and the indirect
-    commands (the step's result) are read back to the host."""
-    n = sc.n
-    h_model = sc.t_model.cpu().pin_memory()
-    h_layers, h_flags, h_ids = sc.t_layers.cpu().pin_memory(), sc.t_flags.cpu().pin_memory(), sc.t_ids.cpu().pin_memory()
-    lib, ctx = sc.ctx.lib, sc.ctx
-    pairs = [(sc.model, h_model), (sc.layers, h_layers), (sc.flags, h_flags), (sc.ids, h_ids)]
-    h2d = sum(h.numel() * h.element_size() for _, h in pairs)
-    outs = [sc.world.material_outputs(m)[1] for m in sc.mats]
-    lods = len(C2["lod_distances"])
-    res = [np.zeros(lods * 5, np.uint32) for _ in outs]
-    d2h = sum(r.nbytes for r in res)
+def _affine48(m64: np.ndarray) -> np.ndarray:
+    """(n, 16) column-major mat4 rows -> (n, 12) mat4x3 rows (columns c0..c3, xyz each): the RVS_VECTOR_AFFINE_ROWS host layout"""
+    return np.ascontiguousarray(m64.reshape(-1, 4, 4)[:, :, :3].reshape(-1, 12))
 
-    def step():
-        for buf, h in pairs:
-            rc = lib.rve_buffer_upload(ctx.h, buf.handle, 0, h.data_ptr(), h.numel() * h.element_size())
-            assert rc == 0
-        sc.step()
-        for ind, r in zip(outs, res):
-            rc = lib.rve_buffer_download(ctx.h, ind.handle, 0, r.ctypes.data, r.nbytes)  # synchronises the stream
-            assert rc == 0
 
-    steps = max(2, min(args.steps, 10))
-    for _ in range(2):
-        step()
+class HostScene:
+    """The per-entity inputs of a DeviceScene as the engine holds them on the HOST: BufferedVRAMVector mirrors
+    (pinned host array + modification flags + device-private buffer, csrc/sync.cu) of worldTransforms (48-B affine or
+    64-B mat4 rows), renderLayers, perObjectAttributes and the entity-id list. Created after the thread was bound to
+    the GPU's NUMA node, so the pinned pages are local to the GPU's PCIe root."""
+
+    def __init__(self, sc: DeviceScene, affine: bool):
+        from ravengine_b200.vram_vector import SYNC_FULL, BufferedVRAMVector
+
+        n, ctx = sc.n, sc.ctx
+        self.sc, self.affine = sc, affine
+        m64 = sc.t_model.cpu().numpy()
+        self.model = BufferedVRAMVector(ctx, 48 if affine else 64, n, affine_rows=affine)
+        self.model.host(np.float32).reshape(n, 12 if affine else 16)[:] = _affine48(m64) if affine else m64
+        self.layers = BufferedVRAMVector(ctx, 4, n)
+        self.layers.host(np.int32)[:] = sc.t_layers.cpu().numpy()
+        self.flags = BufferedVRAMVector(ctx, 2, n)
+        self.flags.host(np.int16)[:] = sc.t_flags.cpu().numpy()
+        self.ids = BufferedVRAMVector(ctx, 4, n)
+        self.ids.host(np.int32)[:] = sc.t_ids.cpu().numpy()
+        for v in (self.model, self.layers, self.flags, self.ids):
+            v.encode_sync(SYNC_FULL)  # first sync after Resize: everything goes up once, outside any timed region
+        ctx.synchronize()
+        # the scene's commands now read the vectors' private buffers
+        sc.world.set_entity_buffers(self.model.private_buffer, self.layers.private_buffer, self.flags.private_buffer)
+        m = C2["materials"]
+        bounds = [n * i // m for i in range(m + 1)]
+        import ctypes as C
+
+        self._id_views = []
+        idbuf = self.ids.private_buffer
+        for i, mat in enumerate(sc.mats):
+            cnt = bounds[i + 1] - bounds[i]
+            if cnt:
+                view = ctx.wrap_pointer(idbuf.ptr + 4 * bounds[i], 4 * cnt, keepalive=self.ids)
+                sc.world.set_command_entities(mat, 0, view, cnt)
+                self._id_views.append(view)
+
+    def bytes_model(self) -> int:
+        return self.sc.n * (48 if self.affine else 64)
+
+    def close(self):
+        sc = self.sc
+        sc.world.set_entity_buffers(sc.model, sc.layers, sc.flags)
+        for i, mat in enumerate(sc.mats):
+            if i < len(sc.id_slices):
+                m = C2["materials"]
+                cnt = sc.n * (i + 1) // m - sc.n * i // m
+                if cnt:
+                    sc.world.set_command_entities(mat, 0, sc.id_slices[i], cnt)
+        sc.ctx.synchronize()
+        for view in self._id_views:
+            view.destroy()
+        for v in (self.model, self.layers, self.flags, self.ids):
+            v.destroy()
+
+
+def _timed_host_loop(step, steps, barrier, torch, dist):
+    for i in range(2):
+        step(i)
     barrier()
     t0 = time.perf_counter()
-    for _ in range(steps):
-        step()
+    for i in range(steps):
+        step(i)
     barrier()
     dt = time.perf_counter() - t0
+    ws = 1
+    by_rank = [dt / steps * 1e3]
     if dist:
-        t = torch.tensor([dt], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dt = float(t.item())
         ws = dist.get_world_size()
-    else:
-        ws = 1
-    # what bounds it: the same 640 MB transform array copied alone, timed with events (the PCIe link's practical rate here)
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    best = 0.0
-    for _ in range(3):
-        e0.record(sc.stream)
-        lib.rve_buffer_upload(ctx.h, sc.model.handle, 0, h_model.data_ptr(), h_model.numel() * h_model.element_size())
-        e1.record(sc.stream)
-        e1.synchronize()
-        best = max(best, h_model.numel() * h_model.element_size() / (e0.elapsed_time(e1) * 1e-3) / 1e9)
-    return {"value": n * ws * steps / dt, "unit": "instances/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-            "ms_per_step": dt / steps * 1e3, "steps": steps, "h2d_gbs_achieved": h2d / (dt / steps) / 1e9, "h2d_gbs_copy_alone": best,
-            "note": "all per-entity inputs re-uploaded from pinned host memory every step (100% dirty), indirect commands read back; "
-                    "PCIe-bound: compare h2d_gbs_achieved with h2d_gbs_copy_alone (one 640 MB pinned copy timed alone)"}
+        t = torch.tensor([dt], device="cuda")
+        allt = torch.zeros(ws, device="cuda")
+        dist.all_gather_into_tensor(allt, t)
+        by_rank = [float(x) / steps * 1e3 for x in allt.tolist()]
+        dt = float(allt.max().item())  # MAX over ranks
+    return dt, ws, by_rank
 
 
-def run_e2e_dirty(sc: DeviceScene, args, torch, barrier, dist, fractions=(0.10, 0.01)):
-    """e2e with the reference's own upload policy: worldTransforms live in a BufferedVRAMVector (host-shared array +
-    modification flags, include/RavEngine/BufferedVRAMVector.hpp) and only rows flagged since the last frame are
-    uploaded by EncodeSync - here the GPU-pull variant (csrc/sync.cu: one kernel reads the flags and the flagged rows
-    from the pinned host arrays over PCIe; no host scan). Per step, inside the timed region: flag a random `fraction` of the rows,
-    EncodeSync, the hot-path step, read the indirect commands back."""
-    from ravengine_b200.vram_vector import SYNC_PACKED, SYNC_PULL, BufferedVRAMVector
+def run_e2e(sc: DeviceScene, args, torch, barrier, dist, affinity):
+    """The same step through the shim with HOST inputs, H2D + D2H inside the timed region.
+    Headline leg: every transform is dirty every step (the worst case of the reference's EncodeSync: all entities moved)
+    and goes up as a 48-B affine row (RVS_VECTOR_AFFINE_ROWS: glm::mat4x3 on the host, the reference's 64-B mat4 in the
+    private buffer); renderLayers / perObjectAttributes / entity ids live in flag-tracked vectors like the reference's
+    (src/World.cpp:330-378 touches only worldTransforms for entities that moved), are synced every step and upload only
+    what was written - nothing in steady state. The indirect commands (the step's result) are read back.
+    by_layout repeats the leg with the reference's unmodified 64-B host rows; by_dirty_fraction with 10 % / 1 % of the rows
+    flagged per step (GPU-pull sync)."""
+    from ravengine_b200.vram_vector import SYNC_FULL, SYNC_FULL_PULL, SYNC_PULL
 
     n = sc.n
-    vec = BufferedVRAMVector(sc.ctx, 64, n)
-    vec.host(np.float32).reshape(n, 16)[:] = sc.t_model.cpu().numpy()
-    vec.encode_sync(SYNC_PACKED)
-    sc.world.set_entity_buffers(vec.private_buffer, sc.layers, sc.flags)
+    lib, ctx = sc.ctx.lib, sc.ctx
+    lods = len(C2["lod_distances"])
+    steps = max(2, min(args.steps, 10))
+    out = {}
+    full_mode = {"copy": SYNC_FULL, "pull": SYNC_FULL_PULL}[args.e2e_upload]
+    legs = [("affine48", True)] + ([("mat4_64", False)] if not args.e2e_headline_only else [])
+    for name, affine in legs:
+        hs = HostScene(sc, affine)
+        outs = [sc.world.material_outputs(m)[1] for m in sc.mats]
+        res = [np.zeros(lods * 5, np.uint32) for _ in outs]
+        d2h = sum(r.nbytes for r in res)
+
+        def step(_i):
+            hs.model.encode_sync(full_mode)   # 100 % of the transforms
+            hs.layers.encode_sync(SYNC_PULL)  # flag-tracked: nothing written -> nothing uploaded
+            hs.flags.encode_sync(SYNC_PULL)
+            hs.ids.encode_sync(SYNC_PULL)
+            sc.step()
+            for ind, r in zip(outs, res):
+                rc = lib.rve_buffer_download(ctx.h, ind.handle, 0, r.ctypes.data, r.nbytes)  # synchronises the stream
+                assert rc == 0
+
+        dt, ws, by_rank = _timed_host_loop(step, steps, barrier, torch, dist)
+        counts = np.concatenate([r.reshape(-1, 5)[:, 1] for r in res])
+        # the link's practical rate for this buffer: the transform upload alone, timed with events on the stream
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        best = 0.0
+        for _ in range(3):
+            barrier()
+            e0.record(sc.stream)
+            hs.model.encode_sync(full_mode)
+            e1.record(sc.stream)
+            e1.synchronize()
+            best = max(best, hs.bytes_model() / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+        h2d = hs.bytes_model()
+        leg = {"value": n * ws * steps / dt, "unit": "instances/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "ms_per_step": dt / steps * 1e3, "ms_per_step_by_rank": by_rank, "steps": steps, "h2d_gbs_achieved": h2d / (dt / steps) / 1e9,
+               "h2d_gbs_upload_alone": best, "visible": int(counts.sum()), "upload": args.e2e_upload}
+        if dist:
+            allb = torch.zeros(ws, device="cuda")
+            dist.all_gather_into_tensor(allb, torch.tensor([best], device="cuda"))
+            leg["h2d_gbs_upload_alone_by_rank"] = [float(x) for x in allb.tolist()]
+        out[name] = leg
+        if name == "affine48" and not args.e2e_headline_only:
+            out["by_dirty_fraction"] = run_e2e_dirty(sc, hs, args, torch, barrier, dist)
+        hs.close()
+    e2e = dict(out["affine48"])
+    e2e["dirty_fraction"] = 1.0
+    e2e["note"] = ("per step: 100 % of the transforms re-uploaded from pinned host memory as 48-B affine rows (expanded to the reference's "
+                   "64-B mat4 layout on the device; exact h2d_bytes_per_step = 48 x instances), renderLayers / perObjectAttributes / entity "
+                   "ids in flag-tracked vectors synced every step (unchanged -> 0 B, the reference's policy), indirect commands read back; "
+                   "PCIe-bound: compare h2d_gbs_achieved with h2d_gbs_upload_alone")
+    e2e["host_affinity"] = affinity
+    if "mat4_64" in out:
+        e2e["by_layout"] = {"mat4_64": out["mat4_64"]}
+        e2e["by_layout_note"] = "same leg with the reference's unmodified 64-B mat4 host rows (no host-side change at all)"
+    if "by_dirty_fraction" in out:
+        e2e["by_dirty_fraction"] = out["by_dirty_fraction"]
+        e2e["by_dirty_fraction_note"] = ("same step, only rows flagged since the last frame are uploaded (the reference's EncodeSync policy, "
+                                         "GPU-pull variant: one kernel reads the flags and the flagged 48-B rows over PCIe); keys = fraction flagged per step")
+    return e2e
+
+
+def run_e2e_dirty(sc: DeviceScene, hs: HostScene, args, torch, barrier, dist, fractions=(0.10, 0.01)):
+    """Per step, inside the timed region: flag a random `fraction` of the rows (the simulation's SetValueAt calls), EncodeSync (GPU pull),
+    the hot-path step, read the indirect commands back."""
+    from ravengine_b200.vram_vector import SYNC_PULL
+
+    n = sc.n
+    vec = hs.model
     lib, ctx = sc.ctx.lib, sc.ctx
     outs = [sc.world.material_outputs(m)[1] for m in sc.mats]
     lods = len(C2["lod_distances"])
@@ -433,37 +528,23 @@ def run_e2e_dirty(sc: DeviceScene, args, torch, barrier, dist, fractions=(0.10, 
     for frac in fractions:
         k = max(1, int(n * frac))
         sets = [np.sort(rng.choice(n, size=k, replace=False)) for _ in range(4)]
-        stats = []
 
         def step(i):
             vec.tracking()[sets[i % 4]] = 1  # the simulation's SetValueAt calls of this frame
             vec.encode_sync(SYNC_PULL)
-            stats.append((k * 64 + n, 0))  # flagged rows + the flag bytes, read over PCIe by the pull kernel
+            hs.layers.encode_sync(SYNC_PULL)
+            hs.flags.encode_sync(SYNC_PULL)
+            hs.ids.encode_sync(SYNC_PULL)
             sc.step()
             for ind, r in zip(outs, res):
                 rc = lib.rve_buffer_download(ctx.h, ind.handle, 0, r.ctypes.data, r.nbytes)  # synchronises the stream
                 assert rc == 0
 
         steps = max(2, min(args.steps, 10))
-        for i in range(2):
-            step(i)
-        stats.clear()
-        barrier()
-        t0 = time.perf_counter()
-        for i in range(steps):
-            step(i)
-        barrier()
-        dt = time.perf_counter() - t0
-        ws = 1
-        if dist:
-            t = torch.tensor([dt], device="cuda")
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            dt, ws = float(t.item()), dist.get_world_size()
+        dt, ws, _ = _timed_host_loop(step, steps, barrier, torch, dist)
         out[f"{frac:g}"] = {"value": n * ws * steps / dt, "unit": "instances/s", "ms_per_step": dt / steps * 1e3,
-                            "dirty_rows_per_step": k, "h2d_bytes_per_step": int(np.mean([b for b, _ in stats])),
+                            "dirty_rows_per_step": k, "h2d_bytes_per_step": int(k * vec.elem_bytes + n),  # flagged rows + 1 B of flag per row
                             "sync": "RVS_SYNC_PULL", "d2h_bytes_per_step": int(d2h), "steps": steps}
-    sc.world.set_entity_buffers(sc.model, sc.layers, sc.flags)
-    vec.destroy()
     return out
 
 
@@ -477,6 +558,10 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer e2e legs (C5-sized shards: 9 GB of pinned host memory per rank)")
+    ap.add_argument("--e2e-upload", default="copy", choices=["copy", "pull"],
+                    help="100 %-dirty transform upload: copy engine into staging + expand kernels (RVS_SYNC_FULL) or one zero-copy kernel (RVS_SYNC_FULL_PULL)")
+    ap.add_argument("--e2e-headline-only", action="store_true", help="skip the by_layout / by_dirty_fraction e2e variants")
+    ap.add_argument("--no-numa-bind", action="store_true", help="leave the process where the launcher put it (diagnostics)")
     ap.add_argument("--force-exchange", action="store_true", help="N=1: run the count exchange machinery anyway (diagnostics)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: per-slot count exchange")
     args = ap.parse_args()

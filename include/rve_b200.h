@@ -237,6 +237,25 @@ RVE_API int rve_ctx_sm_count(rve_ctx* ctx);
 /* how many kernels this context has launched so far (bench.py "gpu_launches") */
 RVE_API uint64_t rve_ctx_launch_count(rve_ctx* ctx);
 
+/* Host placement for the upload path that feeds this one (the reference's per-frame EncodeSync of the host-shared
+ * worldTransforms / renderLayers / perObjectAttributes arrays, src/BufferedVRAMVector.cpp:27-144, from Shared-access
+ * RGL buffers, deps/RGL/include/RGL/Buffer.hpp:25-35): binds the CALLING thread (threads it spawns inherit) to the CPUs
+ * local to the context's GPU and makes the GPU's NUMA node the preferred source of the pages it allocates next - i.e.
+ * of the pinned host arrays. One process per GPU on a multi-socket box otherwise pins wherever the scheduler put it and
+ * every frame's upload crosses the socket interconnect. Linux sysfs only (no libnuma / NVML); a box without NUMA
+ * information is left as it is (numa_node -1, nothing bound). Call it before creating rvs_vector objects. */
+typedef struct rve_host_affinity {
+    int32_t numa_node;      /* node of the GPU's PCIe root, -1 when the kernel does not say */
+    uint32_t cpus_allowed;  /* CPUs the thread could use before the call */
+    uint32_t cpus_local;    /* ... of which local to the GPU */
+    uint32_t cpus_bound;    /* 1 when the thread's affinity was narrowed to the local CPUs */
+    uint32_t memory_bound;  /* 1 when the preferred-node memory policy was set */
+    char pci_bus_id[32];
+} rve_host_affinity;
+#define RVE_BIND_CPUS 0x1u
+#define RVE_BIND_MEMORY 0x2u
+RVE_API int rve_ctx_bind_host_to_device(rve_ctx* ctx, uint32_t flags, rve_host_affinity* out);
+
 /* Per-kernel device timing (bench.py roofline): while enabled, the dominant kernel of each
  * stage is bracketed by CUDA events on the context's stream. kernel: 0 = cull, 1 = depth pyramid,
  * 2 = skinning, 3 = cluster assign. rve_ctx_profile_read synchronises, returns the summed

@@ -162,14 +162,29 @@ typedef struct rvs_sync_stats {
                               block is double-buffered: rvs_vector_tracking() changes at every such sync. Like the
                               reference's shared-buffer copies, rows must not be rewritten before the stream got there. */
 
+#define RVS_SYNC_FULL 3u   /* every row is uploaded, flags are not consulted (and end up clear): the first sync after a
+                              Resize (src/BufferedVRAMVector.cpp:31-81 copies the whole buffer) and frames in which
+                              every entity moved. One copy-engine copy; affine vectors: chunked copies into device
+                              staging, each chunk expanded on a second stream while the next crosses PCIe */
+#define RVS_SYNC_FULL_PULL 4u /* the same by ONE kernel that reads the pinned host rows over PCIe (no staging at all) */
+
 RVE_API int rvs_vector_create(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, rvs_vector** out);
+/* World::RenderData::worldTransforms is a BufferedVRAMVector<matrix4> (include/RavEngine/World.hpp:440) written once per
+ * moved entity by SetValueAt(id, GetWorldMatrix()) (src/World.cpp:346,385). A world matrix is affine: its fourth row is
+ * (0,0,0,1). With RVS_VECTOR_AFFINE_ROWS the HOST rows are glm::mat4x3 (elem_bytes must be 48: columns c0..c3, xyz each)
+ * while the private buffer keeps the reference's 64-B mat4 rows (w = 0,0,0,1 filled in on the device), so every consumer
+ * of the private buffer is unchanged and 25 % fewer bytes cross PCIe. Every sync mode works; byte-identical to a 64-B
+ * vector holding the same matrices. */
+#define RVS_VECTOR_AFFINE_ROWS 0x1u
+RVE_API int rvs_vector_create_ex(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, uint32_t flags, rvs_vector** out);
 RVE_API int rvs_vector_destroy(rvs_vector* v);
 /* Resize: new elements are zero and start out modified (BufferedVRAMVector.hpp:64-69) */
 RVE_API int rvs_vector_resize(rvs_vector* v, uint32_t count);
 RVE_API uint32_t rvs_vector_size(rvs_vector* v);
 /* GetHostBuffer(): pinned host memory, count * elem_bytes; valid until the next growth */
 RVE_API void* rvs_vector_host(rvs_vector* v);
-/* syncTrackingBuffer: one byte per element, non-zero = modified since the last sync */
+/* syncTrackingBuffer: one byte per element, non-zero = modified since the last sync. A vector nobody wrote to (no
+ * rvs_vector_set / _mark / _resize and no call of this accessor since the last sync) syncs without touching its flags. */
 RVE_API uint8_t* rvs_vector_tracking(rvs_vector* v);
 /* SetValueAt / GetValueAtForWriting (hpp:113-121) */
 RVE_API int rvs_vector_set(rvs_vector* v, uint32_t index, const void* value);

@@ -62,6 +62,11 @@ class SceneGenParams(C.Structure):
                 ("frac_layer_zero", f32), ("frac_no_cull_bits", f32), ("id_base", u32)]
 
 
+class HostAffinity(C.Structure):  # rve_host_affinity
+    _fields_ = [("numa_node", i32), ("cpus_allowed", u32), ("cpus_local", u32), ("cpus_bound", u32), ("memory_bound", u32),
+                ("pci_bus_id", C.c_char * 32)]
+
+
 assert C.sizeof(IndirectIndexedCommand) == 20
 assert C.sizeof(CullingUBO) == 88
 assert C.sizeof(CullingUBOinstance) == 36
@@ -85,6 +90,7 @@ PROTOTYPES = {
     "rve_version": (C.c_char_p, []),
     "rve_ctx_sm_count": (C.c_int, [VP]),
     "rve_ctx_launch_count": (u64, [VP]),
+    "rve_ctx_bind_host_to_device": (C.c_int, [VP, u32, VP]),
     "rve_ctx_set_profiling": (C.c_int, [VP, C.c_int]),
     "rve_ctx_profile_read": (C.c_int, [VP, C.c_int, C.POINTER(C.c_double), C.POINTER(u32)]),
     "rve_buffer_create": (C.c_int, [VP, C.c_size_t, C.POINTER(u32)]),
@@ -185,9 +191,11 @@ class SyncStats(C.Structure):
                 ("direct_bytes", u64), ("packed_bytes", u64)]
 
 
-SYNC_RANGES, SYNC_PACKED, SYNC_PULL = 0, 1, 2
+SYNC_RANGES, SYNC_PACKED, SYNC_PULL, SYNC_FULL, SYNC_FULL_PULL = 0, 1, 2, 3, 4
+VECTOR_AFFINE_ROWS = 1
 PROTOTYPES.update({
     "rvs_vector_create": (C.c_int, [VP, u32, u32, C.POINTER(VP)]),
+    "rvs_vector_create_ex": (C.c_int, [VP, u32, u32, u32, C.POINTER(VP)]),
     "rvs_vector_destroy": (C.c_int, [VP]),
     "rvs_vector_resize": (C.c_int, [VP, u32]),
     "rvs_vector_size": (u32, [VP]),

@@ -102,6 +102,13 @@ class Context:
     def launch_count(self) -> int:
         return int(self.lib.rve_ctx_launch_count(self.h))
 
+    def bind_host_to_device(self, cpus: bool = True, memory: bool = True) -> dict:
+        """rve_ctx_bind_host_to_device: this thread onto the GPU's local CPUs, its next (pinned) allocations onto the GPU's NUMA node."""
+        info = _abi.HostAffinity()
+        _check(self.lib, self.lib.rve_ctx_bind_host_to_device(self.h, (1 if cpus else 0) | (2 if memory else 0), C.byref(info)))
+        return {"numa_node": info.numa_node, "cpus_allowed": info.cpus_allowed, "cpus_local": info.cpus_local,
+                "cpus_bound": bool(info.cpus_bound), "memory_bound": bool(info.memory_bound), "pci_bus_id": info.pci_bus_id.decode()}
+
     def set_profiling(self, on: bool) -> None:
         _check(self.lib, self.lib.rve_ctx_set_profiling(self.h, 1 if on else 0))
 

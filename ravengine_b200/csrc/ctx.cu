@@ -1,9 +1,14 @@
 // ctx.cu — context, buffer table ("bindless" handles) and error plumbing of the C-ABI.
 // Replaces the RGL objects the render-prep path touches: IDevice/ICommandQueue
 // (src/RenderEngine.cpp:304-307) and IBuffer (deps/RGL/include/RGL/Buffer.hpp:50-81).
+#include <cctype>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+
+#include <sched.h>
+#include <sys/syscall.h>
+#include <unistd.h>
 
 #include "internal.h"
 
@@ -224,6 +229,59 @@ int rve_ctx_profile_read(rve_ctx* ctx, int kernel, double* total_ms, uint32_t* l
     if (total_ms) *total_ms = sum;
     if (launches) *launches = uint32_t(ctx->prof[kernel].size());
     ctx->prof[kernel].clear();
+    return 0;
+}
+
+// Host-side placement for the upload path: the pinned host arrays a rank uploads from every frame should live on the
+// NUMA node its GPU hangs off, and the thread that fills them should run there. Reads the GPU's PCI address from the
+// runtime and the node / CPU list from sysfs; no libnuma, no NVML.
+int rve_ctx_bind_host_to_device(rve_ctx* ctx, uint32_t flags, rve_host_affinity* out) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    rve_host_affinity info{};
+    info.numa_node = -1;
+    char bus[32] = {0};
+    RVE_CUDA(cudaDeviceGetPCIBusId(bus, sizeof(bus), ctx->device));
+    for (char* c = bus; *c; ++c) *c = char(tolower(*c));
+    snprintf(info.pci_bus_id, sizeof(info.pci_bus_id), "%s", bus);
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/numa_node", bus);
+    if (FILE* f = fopen(path, "r")) {
+        if (fscanf(f, "%d", &info.numa_node) != 1) info.numa_node = -1;
+        fclose(f);
+    }
+    // CPUs local to the device, intersected with what this thread may use (cgroup / launcher restrictions)
+    cpu_set_t allowed, want;
+    CPU_ZERO(&allowed);
+    CPU_ZERO(&want);
+    sched_getaffinity(0, sizeof(allowed), &allowed);
+    info.cpus_allowed = uint32_t(CPU_COUNT(&allowed));
+    snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/local_cpulist", bus);
+    if (FILE* f = fopen(path, "r")) {
+        char line[4096] = {0};
+        if (fgets(line, sizeof(line), f)) {
+            for (char* tok = strtok(line, ",\n"); tok; tok = strtok(nullptr, ",\n")) {
+                int a = 0, b = 0;
+                const int k = sscanf(tok, "%d-%d", &a, &b);
+                if (k == 1) b = a;
+                if (k >= 1)
+                    for (int c = a; c <= b && c < CPU_SETSIZE; ++c)
+                        if (CPU_ISSET(c, &allowed)) CPU_SET(c, &want);
+            }
+        }
+        fclose(f);
+    }
+    info.cpus_local = uint32_t(CPU_COUNT(&want));
+    if ((flags & RVE_BIND_CPUS) && info.cpus_local > 0 && info.cpus_local < info.cpus_allowed)
+        info.cpus_bound = sched_setaffinity(0, sizeof(want), &want) == 0 ? 1u : 0u;
+    if ((flags & RVE_BIND_MEMORY) && info.numa_node >= 0 && info.numa_node < 1024) {
+        // set_mempolicy(MPOL_PREFERRED, {node}): pages this thread touches first - the pinned allocations that follow -
+        // come from the GPU's node when it has room, from elsewhere otherwise (never fails an allocation)
+        unsigned long mask[16] = {0};
+        mask[info.numa_node / (8 * sizeof(unsigned long))] |= 1ul << (info.numa_node % (8 * sizeof(unsigned long)));
+        constexpr int kMpolPreferred = 1;
+        info.memory_bound = syscall(SYS_set_mempolicy, kMpolPreferred, mask, sizeof(mask) * 8) == 0 ? 1u : 0u;
+    }
+    if (out) *out = info;
     return 0;
 }
 

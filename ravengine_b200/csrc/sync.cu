@@ -106,6 +106,136 @@ int launch_pull(rve_ctx* ctx, uint8_t* flags, const unsigned char* host, unsigne
     return 0;
 }
 
+
+// ---- affine rows (RVS_VECTOR_AFFINE_ROWS): host rows are glm::mat4x3 (48 B: columns c0..c3, xyz each), the private
+// buffer keeps the reference's mat4 rows (64 B, column-major, w = 0,0,0,1) - the layout defaultcull.csh and the vertex
+// shaders read. A world matrix is affine, so the fourth row carries no information: 25 % fewer bytes over PCIe. ----
+
+// column `col` (0..3) of a 64-B row from the 12 floats of a 48-B row
+__device__ __forceinline__ float4 affine_column(const float* r12, uint32_t col) {
+    return make_float4(r12[col * 3], r12[col * 3 + 1], r12[col * 3 + 2], col == 3 ? 1.0f : 0.0f);
+}
+
+// Whole-array upload, one warp per 32 rows: three fully coalesced 512-B loads of the 48-B rows (device staging memory,
+// or pinned HOST memory read over PCIe - no staging copy at all), re-formed through shared memory into four fully
+// coalesced 512-B stores of 64-B rows. EXPAND = false: plain coalesced copy of 16-B chunks (any row size).
+template <bool EXPAND>
+__global__ void __launch_bounds__(256) full_rows_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, uint64_t rows, uint64_t chunks) {
+    if constexpr (EXPAND) {
+        __shared__ uint4 s_buf[8][96];
+        const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        const uint64_t warpsTotal = uint64_t(gridDim.x) * 8u;
+        const uint64_t groups = (rows + 31) / 32;
+        const float* sf = reinterpret_cast<const float*>(s_buf[warp]);
+        for (uint64_t g = uint64_t(blockIdx.x) * 8u + warp; g < groups; g += warpsTotal) {
+            const uint64_t c0 = g * 96;  // first 16-B chunk of the group
+            const uint64_t cEnd = rows * 3;
+            uint4 v[3];
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const uint64_t c = c0 + uint64_t(j * 32) + lane;
+                v[j] = c < cEnd ? __ldg(src + c) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int j = 0; j < 3; ++j) s_buf[warp][j * 32 + lane] = v[j];
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t idx = uint32_t(j * 32) + lane;
+                const uint64_t row = g * 32 + (idx >> 2);
+                if (row < rows) {
+                    const float4 o = affine_column(sf + (idx >> 2) * 12, idx & 3);
+                    reinterpret_cast<float4*>(dst)[row * 4 + (idx & 3)] = o;
+                }
+            }
+            __syncwarp();
+        }
+    } else {
+        const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+        for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < chunks; i += stride) dst[i] = __ldg(src + i);
+    }
+}
+
+// packed staging block [48-B rows][u32 indices] -> 64-B rows at dst[idx[r]]: one thread per (row, column)
+__global__ void scatter_rows_affine_kernel(float4* __restrict__ dst, const uint32_t* __restrict__ idx, const float* __restrict__ rows,
+                                           uint32_t count) {
+    const uint64_t total = uint64_t(count) * 4;
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += uint64_t(gridDim.x) * blockDim.x) {
+        const uint32_t r = uint32_t(i >> 2), c = uint32_t(i & 3);
+        dst[uint64_t(__ldg(idx + r)) * 4 + c] = affine_column(rows + uint64_t(r) * 12, c);
+    }
+}
+
+// contiguous run of 48-B rows in device staging memory -> 64-B rows dst[first ..) (the direct-copy ranges of an affine vector)
+__global__ void expand_range_affine_kernel(float4* __restrict__ dst, const float* __restrict__ rows, uint64_t first, uint32_t count) {
+    const uint64_t total = uint64_t(count) * 4;
+    for (uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += uint64_t(gridDim.x) * blockDim.x)
+        dst[first * 4 + i] = affine_column(rows + (i >> 2) * 12, uint32_t(i & 3));
+}
+
+// RVS_SYNC_PULL for affine rows: like pull_rows_kernel, four lanes per flagged row; lanes 0..2 fetch the row's three
+// 16-B chunks from the pinned host array, the group shares them by shuffle and every lane writes one 64-B-row column.
+__global__ void pull_rows_affine_kernel(uint8_t* __restrict__ flags, const uint4* __restrict__ src, float4* __restrict__ dst, uint32_t n,
+                                        uint32_t* __restrict__ rowsCopied) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warpsTotal = gridDim.x * (blockDim.x >> 5);
+    const uint32_t groups = (n + 31) / 32;
+    uint32_t copied = 0;
+    for (uint32_t grp = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); grp < groups; grp += warpsTotal) {
+        const uint32_t row0 = grp * 32;
+        uint8_t f = 0;
+        if (row0 + lane < n) f = flags[row0 + lane];
+        const uint32_t mask = __ballot_sync(0xffffffffu, f != 0);
+        if (mask == 0) continue;
+        if (f) flags[row0 + lane] = 0;
+        const uint32_t cnt = __popc(mask);
+        copied += cnt;
+        for (uint32_t i = 0; i < cnt; i += 8) {  // eight rows per iteration, four lanes each
+            const uint32_t j = i + (lane >> 2), c = lane & 3;
+            const bool on = j < cnt;
+            const uint64_t row = on ? row0 + __fns(mask, 0, int(j) + 1) : 0;
+            uint4 ch = make_uint4(0, 0, 0, 0);
+            if (on && c < 3) ch = src[row * 3 + c];
+            float r12[12];
+            const uint32_t base = lane & ~3u;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                r12[4 * k + 0] = __uint_as_float(__shfl_sync(0xffffffffu, ch.x, int(base) + k));
+                r12[4 * k + 1] = __uint_as_float(__shfl_sync(0xffffffffu, ch.y, int(base) + k));
+                r12[4 * k + 2] = __uint_as_float(__shfl_sync(0xffffffffu, ch.z, int(base) + k));
+                r12[4 * k + 3] = __uint_as_float(__shfl_sync(0xffffffffu, ch.w, int(base) + k));
+            }
+            if (on) {
+                // column c without dynamic register indexing
+                float4 o;
+                if (c == 0) o = make_float4(r12[0], r12[1], r12[2], 0.0f);
+                else if (c == 1) o = make_float4(r12[3], r12[4], r12[5], 0.0f);
+                else if (c == 2) o = make_float4(r12[6], r12[7], r12[8], 0.0f);
+                else o = make_float4(r12[9], r12[10], r12[11], 1.0f);
+                dst[row * 4 + c] = o;
+            }
+        }
+    }
+    if (lane == 0 && copied) atomicAdd(rowsCopied, copied);
+}
+
+int launch_full(rve_ctx* ctx, cudaStream_t stream, const unsigned char* src, unsigned char* dst, uint64_t rows, uint32_t srcRowBytes, bool expand) {
+    if (!rows) return 0;
+    const uint32_t maxBlocks = uint32_t(ctx->sm_count) * 8u;
+    if (expand) {
+        const uint64_t groups = (rows + 31) / 32;
+        const uint32_t blocks = uint32_t(std::min<uint64_t>((groups + 7) / 8, maxBlocks));
+        full_rows_kernel<true><<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), rows, 0);
+    } else {
+        const uint64_t chunks = rows * srcRowBytes / 16;
+        const uint32_t blocks = uint32_t(std::min<uint64_t>((chunks + 255) / 256, maxBlocks));
+        full_rows_kernel<false><<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(src), reinterpret_cast<uint4*>(dst), rows, chunks);
+    }
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace rve
 
 using namespace rve;
@@ -154,9 +284,19 @@ extern "C" int rve_scatter_rows(rve_ctx* ctx, rve_buffer dst, uint32_t elem_byte
 // ---------------------------------------------------------------------------------------------------------
 struct rvs_vector {
     rve_ctx* ctx = nullptr;
-    uint32_t elemBytes = 0;
+    uint32_t elemBytes = 0;     // host row
+    uint32_t devElemBytes = 0;  // private-buffer row: elemBytes, or 64 for affine rows (48-B host rows)
+    bool affine = false;
+    bool anyDirty = false;  // some flag may be set (SetValueAt / mark / a caller holding the tracking pointer): a clean vector syncs for free
     uint32_t count = 0, capacity = 0;
     unsigned char* host = nullptr;  // pinned: VRAMVector's host-mapped Shared buffer
+    // RVS_SYNC_FULL of an affine vector: copy-engine chunks into device staging, expanded on a second stream while
+    // the next chunk is in flight
+    rve_buffer fullStage = RVE_BUFFER_INVALID;
+    size_t fullStageBytes = 0;
+    cudaStream_t copyStream = nullptr, expandStream = nullptr;
+    cudaEvent_t evBegin = nullptr, evDone = nullptr;
+    std::vector<cudaEvent_t> evChunk;
     // syncTrackingBuffer: pinned, capacity rounded up to 32 flags, double-buffered so that RVS_SYNC_PULL can hand
     // the flags of this frame to the GPU while the host already records the next frame's modifications
     uint8_t* trackBuf[2] = {nullptr, nullptr};
@@ -256,11 +396,19 @@ void compute_ranges(const uint8_t* track, uint32_t n, std::vector<uint32_t>& out
 extern "C" {
 
 int rvs_vector_create(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, rvs_vector** out) {
+    return rvs_vector_create_ex(ctx, elem_bytes, count, 0u, out);
+}
+
+int rvs_vector_create_ex(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, uint32_t flags, rvs_vector** out) {
     if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
     RVE_REQUIRE(elem_bytes == 2 || (elem_bytes % 4 == 0 && elem_bytes > 0), "element size must be 2 or a multiple of 4 bytes");
+    RVE_REQUIRE(!(flags & ~RVS_VECTOR_AFFINE_ROWS), "unknown vector flags");
+    RVE_REQUIRE(!(flags & RVS_VECTOR_AFFINE_ROWS) || elem_bytes == 48, "affine rows are 48-byte mat4x3 host rows");
     auto* v = new rvs_vector();
     v->ctx = ctx;
     v->elemBytes = elem_bytes;
+    v->affine = (flags & RVS_VECTOR_AFFINE_ROWS) != 0;
+    v->devElemBytes = v->affine ? 64u : elem_bytes;
     {
         DeviceGuard g(ctx->device);
         if (cudaEventCreateWithFlags(&v->stageFree, cudaEventDisableTiming) != cudaSuccess ||
@@ -282,6 +430,14 @@ int rvs_vector_destroy(rvs_vector* v) {
     cudaStreamSynchronize(v->ctx->stream);
     if (v->priv != RVE_BUFFER_INVALID) rve_buffer_destroy(v->ctx, v->priv);
     if (v->stageDev != RVE_BUFFER_INVALID) rve_buffer_destroy(v->ctx, v->stageDev);
+    if (v->copyStream) cudaStreamSynchronize(v->copyStream);
+    if (v->expandStream) cudaStreamSynchronize(v->expandStream);
+    if (v->fullStage != RVE_BUFFER_INVALID) rve_buffer_destroy(v->ctx, v->fullStage);
+    if (v->copyStream) cudaStreamDestroy(v->copyStream);
+    if (v->expandStream) cudaStreamDestroy(v->expandStream);
+    if (v->evBegin) cudaEventDestroy(v->evBegin);
+    if (v->evDone) cudaEventDestroy(v->evDone);
+    for (cudaEvent_t e : v->evChunk) cudaEventDestroy(e);
     if (v->host) cudaFreeHost(v->host);
     if (v->stageHost) cudaFreeHost(v->stageHost);
     if (v->stageFree) cudaEventDestroy(v->stageFree);
@@ -306,6 +462,7 @@ int rvs_vector_resize(rvs_vector* v, uint32_t count) {
     if (count > old) {
         std::memset(v->host + size_t(old) * v->elemBytes, 0, size_t(count - old) * v->elemBytes);
         std::memset(v->track + old, 1, count - old);
+        v->anyDirty = true;
     } else {
         std::memset(v->track + count, 0, old - count);
     }
@@ -315,7 +472,11 @@ int rvs_vector_resize(rvs_vector* v, uint32_t count) {
 
 uint32_t rvs_vector_size(rvs_vector* v) { return v ? v->count : 0; }
 void* rvs_vector_host(rvs_vector* v) { return v ? v->host : nullptr; }
-uint8_t* rvs_vector_tracking(rvs_vector* v) { return v ? v->track : nullptr; }
+uint8_t* rvs_vector_tracking(rvs_vector* v) {
+    if (!v) return nullptr;
+    v->anyDirty = true;  // the caller may set flags through this pointer: the next sync looks at them
+    return v->track;
+}
 rve_buffer rvs_vector_private_buffer(rvs_vector* v) { return v ? v->priv : RVE_BUFFER_INVALID; }
 
 // SetValueAt (BufferedVRAMVector.hpp:113-116)
@@ -324,6 +485,7 @@ int rvs_vector_set(rvs_vector* v, uint32_t index, const void* value) {
     RVE_REQUIRE(index < v->count, "index out of range");
     std::memcpy(v->host + size_t(index) * v->elemBytes, value, v->elemBytes);
     v->track[index] = 1;
+    v->anyDirty = true;
     return 0;
 }
 
@@ -332,6 +494,7 @@ int rvs_vector_mark(rvs_vector* v, uint32_t begin, uint32_t end) {
     if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
     RVE_REQUIRE(begin <= end && end <= v->count, "range out of bounds");
     std::memset(v->track + begin, 1, end - begin);
+    if (end > begin) v->anyDirty = true;
     return 0;
 }
 
@@ -355,17 +518,86 @@ uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max
     return n;
 }
 
+// RVS_SYNC_FULL / RVS_SYNC_FULL_PULL: every row goes up, flags are not consulted (and cleared when any may be set)
+static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st) {
+    rve_ctx* ctx = v->ctx;
+    auto* dev = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
+    if (!dev) return RVE_ERR_BAD_HANDLE;
+    const size_t eb = v->elemBytes;
+    const size_t bytes = size_t(v->count) * eb;
+    const bool chunked16 = (eb % 16 == 0) && ((reinterpret_cast<uintptr_t>(v->host) | reinterpret_cast<uintptr_t>(dev)) & 15) == 0;
+    if (mode == RVS_SYNC_FULL_PULL && (v->affine || chunked16)) {
+        // one kernel reads the pinned host rows over PCIe and writes the private rows: no copy-engine operation, no staging
+        const int rc = launch_full(ctx, ctx->stream, v->host, dev, v->count, v->elemBytes, v->affine);
+        if (rc) return rc;
+    } else if (!v->affine) {
+        RVE_CUDA(cudaMemcpyAsync(dev, v->host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        st->direct_copies = 1;
+    } else {
+        // copy engine -> device staging (48-B rows) in chunks on a copy stream; each chunk is expanded into the 64-B
+        // private rows on a second stream while the next chunk is still crossing PCIe
+        if (!v->copyStream) {
+            RVE_CUDA(cudaStreamCreateWithFlags(&v->copyStream, cudaStreamNonBlocking));
+            RVE_CUDA(cudaStreamCreateWithFlags(&v->expandStream, cudaStreamNonBlocking));
+            RVE_CUDA(cudaEventCreateWithFlags(&v->evBegin, cudaEventDisableTiming));
+            RVE_CUDA(cudaEventCreateWithFlags(&v->evDone, cudaEventDisableTiming));
+        }
+        const size_t want = size_t(v->capacity) * eb;
+        if (v->fullStage == RVE_BUFFER_INVALID || v->fullStageBytes != want) {
+            if (v->fullStage != RVE_BUFFER_INVALID) {
+                RVE_CUDA(cudaStreamSynchronize(v->expandStream));
+                rve_buffer_destroy(ctx, v->fullStage);
+            }
+            const int rc = rve_buffer_create(ctx, want, &v->fullStage);
+            if (rc) return rc;
+            v->fullStageBytes = want;
+        }
+        auto* stage = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->fullStage));
+        constexpr uint32_t kChunkRows = 1u << 20;  // 48 MB per copy: ~0.9 ms on the link, ~25 us to expand
+        const uint32_t nChunks = (v->count + kChunkRows - 1) / kChunkRows;
+        while (v->evChunk.size() < nChunks) {
+            cudaEvent_t e;
+            RVE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            v->evChunk.push_back(e);
+        }
+        // everything enqueued so far (last frame's readers of the private buffer, this buffer's creation) comes first
+        RVE_CUDA(cudaEventRecord(v->evBegin, ctx->stream));
+        RVE_CUDA(cudaStreamWaitEvent(v->copyStream, v->evBegin, 0));
+        RVE_CUDA(cudaStreamWaitEvent(v->expandStream, v->evBegin, 0));
+        for (uint32_t c = 0; c < nChunks; ++c) {
+            const uint32_t r0 = c * kChunkRows;
+            const uint32_t rows = v->count - r0 < kChunkRows ? v->count - r0 : kChunkRows;
+            RVE_CUDA(cudaMemcpyAsync(stage + size_t(r0) * eb, v->host + size_t(r0) * eb, size_t(rows) * eb, cudaMemcpyHostToDevice, v->copyStream));
+            RVE_CUDA(cudaEventRecord(v->evChunk[c], v->copyStream));
+            RVE_CUDA(cudaStreamWaitEvent(v->expandStream, v->evChunk[c], 0));
+            const int rc = launch_full(ctx, v->expandStream, stage + size_t(r0) * eb, dev + size_t(r0) * 64, rows, v->elemBytes, true);
+            if (rc) return rc;
+        }
+        RVE_CUDA(cudaEventRecord(v->evDone, v->expandStream));
+        RVE_CUDA(cudaStreamWaitEvent(ctx->stream, v->evDone, 0));
+        st->direct_copies = nChunks;
+    }
+    st->direct_bytes = bytes;
+    st->rows_in_ranges = v->count;
+    st->ranges = 1;
+    v->ranges.assign({0u, v->count});
+    if (v->anyDirty) std::memset(v->track, 0, v->count);
+    v->anyDirty = false;
+    pyramid_note_buffer_write(ctx, v->priv);
+    return 0;
+}
+
 // BufferedVRAMStructureBase::EncodeSync (src/BufferedVRAMVector.cpp:27-144)
 int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_rows, rvs_sync_stats* stats) {
     if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
-    RVE_REQUIRE(mode == RVS_SYNC_RANGES || mode == RVS_SYNC_PACKED || mode == RVS_SYNC_PULL, "unknown sync mode");
+    RVE_REQUIRE(mode <= RVS_SYNC_FULL_PULL, "unknown sync mode");
     rve_ctx* ctx = v->ctx;
     DeviceGuard g(ctx->device);
     rvs_sync_stats st{};
-    const size_t eb = v->elemBytes;
+    const size_t eb = v->elemBytes, deb = v->devElemBytes;
 
     // private buffer follows the host buffer's size; old contents are carried over (:31-81)
-    const size_t wantBytes = size_t(v->capacity) * eb;
+    const size_t wantBytes = size_t(v->capacity) * deb;
     if (wantBytes && (v->priv == RVE_BUFFER_INVALID || v->privBytes != wantBytes)) {
         rve_buffer nb;
         int rc = rve_buffer_create(ctx, wantBytes, &nb);
@@ -379,16 +611,39 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
         v->priv = nb;
         v->privBytes = wantBytes;
     }
+    if (v->count == 0) {
+        v->ranges.clear();
+        if (stats) *stats = st;
+        return 0;
+    }
+    if (mode == RVS_SYNC_FULL || mode == RVS_SYNC_FULL_PULL) {
+        const int rc = sync_full(v, mode, &st);
+        if (stats) *stats = st;
+        return rc;
+    }
+    if (!v->anyDirty) {  // nothing was written since the last sync (the common state of ids / layers / attributes)
+        v->ranges.clear();
+        if (stats) *stats = st;
+        return 0;
+    }
 
     if (mode == RVS_SYNC_PULL) {
         v->ranges.clear();
-        if (v->count == 0) {
-            if (stats) *stats = st;
-            return 0;
-        }
         auto* devp = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
         if (!devp) return RVE_ERR_BAD_HANDLE;
-        const int rc = launch_pull(ctx, v->track, v->host, devp, v->count, v->elemBytes, v->pullRows);
+        int rc = 0;
+        if (v->affine) {
+            const uint32_t groups = (v->count + 31) / 32;
+            uint32_t blocks = (groups + 7) / 8;
+            const uint32_t maxBlocks = uint32_t(ctx->sm_count) * 8u;
+            if (blocks > maxBlocks) blocks = maxBlocks;
+            pull_rows_affine_kernel<<<blocks, 256, 0, ctx->stream>>>(v->track, reinterpret_cast<const uint4*>(v->host), reinterpret_cast<float4*>(devp),
+                                                                    v->count, v->pullRows);
+            ctx->launches++;
+            RVE_CUDA(cudaGetLastError());
+        } else {
+            rc = launch_pull(ctx, v->track, v->host, devp, v->count, v->elemBytes, v->pullRows);
+        }
         if (rc) return rc;
         RVE_CUDA(cudaEventRecord(v->pullDone[v->cur], ctx->stream));
         v->pullBusy[v->cur] = true;
@@ -398,12 +653,15 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
         if (v->pullBusy[v->cur]) RVE_CUDA(cudaEventSynchronize(v->pullDone[v->cur]));
         v->pullBusy[v->cur] = false;
         v->track = v->trackBuf[v->cur];
+        v->anyDirty = false;
         st.packed_bytes = uint64_t(v->count);  // flag bytes the kernel reads; row bytes depend on the flags (rvs_vector_pulled_rows)
+        pyramid_note_buffer_write(ctx, v->priv);
         if (stats) *stats = st;
         return 0;
     }
 
     compute_ranges(v->track, v->count, v->ranges);
+    v->anyDirty = false;
     const uint32_t nRanges = uint32_t(v->ranges.size() / 2);
     st.ranges = nRanges;
     if (nRanges == 0) {
@@ -413,20 +671,28 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
     auto* dev = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
     if (!dev) return RVE_ERR_BAD_HANDLE;
 
-    uint64_t packedRows = 0;
+    // Affine rows cannot be copied range by range into the 64-B private rows: every mode stages. Short ranges (PACKED)
+    // stage only their modified rows + indices; direct ranges stage all their rows, contiguously, behind them.
+    const bool packShort = mode == RVS_SYNC_PACKED;
+    uint64_t packedRows = 0, directRows = 0;
     for (uint32_t r = 0; r < nRanges; ++r) {
         const uint32_t len = v->ranges[2 * r + 1] - v->ranges[2 * r];
         st.rows_in_ranges += len;
-        if (mode == RVS_SYNC_PACKED && len < direct_min_rows)
+        if (packShort && len < direct_min_rows) {
             for (uint32_t k = v->ranges[2 * r]; k < v->ranges[2 * r + 1]; ++k) packedRows += v->track[k] ? 1u : 0u;
+        } else {
+            directRows += len;
+        }
     }
+    const uint64_t stagedDirect = v->affine ? directRows : 0;  // rows of direct ranges that travel through the staging block
     unsigned char* rowsDst = nullptr;
     uint32_t* idxDst = nullptr;
-    size_t idxOffset = 0;
-    if (packedRows) {
+    size_t idxOffset = 0, directOffset = 0;
+    if (packedRows || stagedDirect) {
         RVE_REQUIRE(packedRows <= 0xFFFFFFFFull, "too many packed rows");
         idxOffset = (size_t(packedRows) * eb + 15) & ~size_t(15);
-        const size_t need = idxOffset + size_t(packedRows) * 4;
+        directOffset = (idxOffset + size_t(packedRows) * 4 + 15) & ~size_t(15);
+        const size_t need = directOffset + size_t(stagedDirect) * eb;
         if (need > v->stageHostBytes) {
             if (v->stageBusy) RVE_CUDA(cudaEventSynchronize(v->stageFree));
             v->stageBusy = false;
@@ -447,15 +713,26 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
         rowsDst = v->stageHost;
         idxDst = reinterpret_cast<uint32_t*>(v->stageHost + idxOffset);
     }
-    uint64_t pr = 0;
+    uint64_t pr = 0, dr = 0;
+    struct DirectRun {
+        uint32_t first, rows;
+        uint64_t stagedAt;
+    };
+    std::vector<DirectRun> runs;
     for (uint32_t r = 0; r < nRanges; ++r) {
         const uint32_t b = v->ranges[2 * r], e = v->ranges[2 * r + 1], len = e - b;
-        if (mode == RVS_SYNC_PACKED && len < direct_min_rows) {
+        if (packShort && len < direct_min_rows) {
             for (uint32_t k = b; k < e; ++k)
                 if (v->track[k]) {
                     std::memcpy(rowsDst + pr * eb, v->host + size_t(k) * eb, eb);
                     idxDst[pr++] = k;
                 }
+        } else if (v->affine) {
+            std::memcpy(v->stageHost + directOffset + dr * eb, v->host + size_t(b) * eb, size_t(len) * eb);
+            runs.push_back({b, len, dr});
+            dr += len;
+            st.direct_copies++;
+            st.direct_bytes += uint64_t(len) * eb;
         } else {
             RVE_CUDA(cudaMemcpyAsync(dev + size_t(b) * eb, v->host + size_t(b) * eb, size_t(len) * eb, cudaMemcpyHostToDevice, ctx->stream));
             st.direct_copies++;
@@ -463,17 +740,36 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
         }
         std::memset(v->track + b, 0, len);
     }
-    if (packedRows) {
+    if (packedRows || stagedDirect) {
         auto* sdev = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->stageDev));
-        const size_t bytes = idxOffset + size_t(packedRows) * 4;
+        const size_t bytes = directOffset + size_t(stagedDirect) * eb;
         RVE_CUDA(cudaMemcpyAsync(sdev, v->stageHost, bytes, cudaMemcpyHostToDevice, ctx->stream));
         RVE_CUDA(cudaEventRecord(v->stageFree, ctx->stream));
         v->stageBusy = true;
-        const int rc = rve_scatter_rows(ctx, v->priv, v->elemBytes, v->stageDev, idxOffset, 0, uint32_t(packedRows));
-        if (rc) return rc;
+        const uint32_t maxBlocks = uint32_t(ctx->sm_count) * 8u;
+        if (packedRows) {
+            if (v->affine) {
+                const uint32_t blocks = uint32_t(std::min<uint64_t>((packedRows * 4 + 255) / 256, maxBlocks));
+                scatter_rows_affine_kernel<<<blocks, 256, 0, ctx->stream>>>(reinterpret_cast<float4*>(dev), reinterpret_cast<const uint32_t*>(sdev + idxOffset),
+                                                                           reinterpret_cast<const float*>(sdev), uint32_t(packedRows));
+                ctx->launches++;
+                RVE_CUDA(cudaGetLastError());
+            } else {
+                const int rc = rve_scatter_rows(ctx, v->priv, v->elemBytes, v->stageDev, idxOffset, 0, uint32_t(packedRows));
+                if (rc) return rc;
+            }
+        }
+        for (const DirectRun& d : runs) {
+            const uint32_t blocks = uint32_t(std::min<uint64_t>((uint64_t(d.rows) * 4 + 255) / 256, maxBlocks));
+            expand_range_affine_kernel<<<blocks, 256, 0, ctx->stream>>>(reinterpret_cast<float4*>(dev),
+                                                                       reinterpret_cast<const float*>(sdev + directOffset + d.stagedAt * eb), d.first, d.rows);
+            ctx->launches++;
+            RVE_CUDA(cudaGetLastError());
+        }
         st.packed_rows = uint32_t(packedRows);
         st.packed_bytes = bytes;
     }
+    pyramid_note_buffer_write(ctx, v->priv);
     if (stats) *stats = st;
     return 0;
 }

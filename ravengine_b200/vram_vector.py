@@ -12,13 +12,15 @@ from . import _abi
 from .api import Buffer, Context, _check
 
 SYNC_RANGES, SYNC_PACKED, SYNC_PULL = _abi.SYNC_RANGES, _abi.SYNC_PACKED, _abi.SYNC_PULL
+SYNC_FULL, SYNC_FULL_PULL = _abi.SYNC_FULL, _abi.SYNC_FULL_PULL
 
 
 class BufferedVRAMVector:
-    def __init__(self, ctx: Context, elem_bytes: int, count: int = 0):
-        self.ctx, self.elem_bytes = ctx, elem_bytes
+    def __init__(self, ctx: Context, elem_bytes: int, count: int = 0, affine_rows: bool = False):
+        """affine_rows: host rows are 48-B mat4x3 (columns c0..c3, xyz each); the private buffer keeps 64-B mat4 rows."""
+        self.ctx, self.elem_bytes, self.affine_rows = ctx, elem_bytes, affine_rows
         h = C.c_void_p()
-        _check(ctx.lib, ctx.lib.rvs_vector_create(ctx.h, elem_bytes, count, C.byref(h)))
+        _check(ctx.lib, ctx.lib.rvs_vector_create_ex(ctx.h, elem_bytes, count, _abi.VECTOR_AFFINE_ROWS if affine_rows else 0, C.byref(h)))
         self.h = h
 
     def __len__(self) -> int:

@@ -114,3 +114,80 @@ def test_growth_keeps_contents_and_marks_new_rows(ctx):
     assert np.array_equal(got[:5000], keep) and np.all(got[5000:] == -7.25)
     assert v.pulled_rows() == 15001
     v.destroy()
+
+
+def _affine48(m64: np.ndarray) -> np.ndarray:
+    """(n, 16) column-major mat4 rows -> (n, 12) mat4x3 rows (columns c0..c3, xyz each)."""
+    return np.ascontiguousarray(m64.reshape(-1, 4, 4)[:, :, :3].reshape(-1, 12))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 31, 50_003, 1_200_001])
+def test_affine_rows_are_byte_identical_to_mat4_rows(ctx, n):
+    """RVS_VECTOR_AFFINE_ROWS: 48-B host rows, 64-B private rows. Every sync mode must leave the private buffer
+    byte-identical to a plain 64-B vector that holds the same (affine) matrices."""
+    from ravengine_b200 import scenes
+    from ravengine_b200.vram_vector import (SYNC_FULL, SYNC_FULL_PULL, SYNC_PACKED, SYNC_PULL, SYNC_RANGES, BufferedVRAMVector)
+
+    rng = np.random.default_rng(n)
+    want = scenes.random_transforms(rng, n, 500.0, 50.0).reshape(n, 16)
+    assert np.all(want[:, 3::4] == np.array([0, 0, 0, 1], np.float32))  # the generator's matrices are affine
+    for mode in (SYNC_RANGES, SYNC_PACKED, SYNC_PULL, SYNC_FULL, SYNC_FULL_PULL):
+        v = BufferedVRAMVector(ctx, 48, n, affine_rows=True)
+        ref = BufferedVRAMVector(ctx, 64, n)
+        h = v.host(np.float32).reshape(n, 12)
+        cur = want.copy()
+        h[:] = _affine48(cur)
+        ref.host(np.float32).reshape(n, 16)[:] = cur
+        v.encode_sync(mode, 64)
+        ref.encode_sync(SYNC_FULL)
+        got = v.private_buffer.download(np.float32).reshape(-1, 16)[:n]
+        assert got.tobytes() == ref.private_buffer.download(np.float32).reshape(-1, 16)[:n].tobytes() == cur.tobytes()
+        for frame in range(2):
+            dirty = rng.random(n) < (0.02 if frame == 0 else 0.7)
+            if n > 5000:
+                dirty[1000:3000] = True  # a long run: direct range in packed mode
+            idx = np.nonzero(dirty)[0]
+            cur[idx] = scenes.random_transforms(rng, len(idx), 100.0, 10.0).reshape(-1, 16) if len(idx) else cur[idx]
+            h[idx] = _affine48(cur[idx]) if len(idx) else h[idx]
+            if mode in (SYNC_FULL, SYNC_FULL_PULL):
+                v.encode_sync(mode)  # flags are not consulted
+            else:
+                v.tracking()[idx] = 1
+                st = v.encode_sync(mode, 64)
+                if mode != SYNC_PULL:
+                    assert np.array_equal(v.last_ranges(), host_tables.sync_ranges(dirty.astype(np.uint8)))
+                assert not v.tracking().any()
+            got = v.private_buffer.download(np.float32).reshape(-1, 16)[:n]
+            assert got.tobytes() == cur.tobytes()
+        v.destroy()
+        ref.destroy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("elem_bytes,dtype", [(64, np.float32), (4, np.uint32), (2, np.uint16)])
+def test_full_modes_and_clean_vectors(ctx, elem_bytes, dtype):
+    """RVS_SYNC_FULL / _FULL_PULL upload every row without reading flags; a vector nobody wrote to syncs without work."""
+    from ravengine_b200.vram_vector import SYNC_FULL, SYNC_FULL_PULL, SYNC_PACKED, SYNC_PULL, BufferedVRAMVector
+
+    rng = np.random.default_rng(elem_bytes)
+    n = 70_001
+    per = elem_bytes // np.dtype(dtype).itemsize
+    for mode in (SYNC_FULL, SYNC_FULL_PULL):
+        v = BufferedVRAMVector(ctx, elem_bytes, n)
+        h = v.host(dtype).reshape(n, per)
+        for _ in range(2):
+            h[:] = rng.integers(0, 60000, size=(n, per)).astype(dtype)
+            st = v.encode_sync(mode)
+            assert st.direct_bytes == n * elem_bytes
+            assert np.array_equal(v.private_buffer.download(dtype).reshape(-1, per)[:n], h)
+        launches = ctx.launch_count
+        for m in (SYNC_PACKED, SYNC_PULL):  # clean: no scan, no launch, no copy
+            st = v.encode_sync(m)
+            assert st.ranges == 0 and st.packed_bytes == 0 and ctx.launch_count == launches
+        v.set_value_at(5, h[7].copy())
+        h2 = h.copy()
+        h2[5] = h[7]
+        v.encode_sync(SYNC_PACKED)
+        assert np.array_equal(v.private_buffer.download(dtype).reshape(-1, per)[:n], h2)
+        v.destroy()
