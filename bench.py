@@ -223,19 +223,31 @@ def run_reference(args, rank: int):
     print(json.dumps(line), flush=True)
 
 
+def place_rank(local_rank: int, world_size: int, device_count: int, mode: str) -> int:
+    """Which GPU a rank drives. "spread" (default): ranks are spread evenly over the box's GPUs (stride
+    device_count / world_size) instead of packed onto the first N, so that a job smaller than the box uses every PCIe root /
+    socket it can: host->device uploads are the e2e bound, and on the 8-GPU pool boxes GPUs 0-3 share one ~115 GB/s path to
+    host memory while 0,2,4,6 reach 4 x 54 GB/s (profiles/r02_h2d_probe2_n8.jsonl). NVSwitch makes every pair of GPUs
+    equally near for the count exchange. "packed": device = local rank."""
+    if mode == "spread" and 0 < world_size < device_count and device_count % world_size == 0:
+        return local_rank * (device_count // world_size)
+    return local_rank
+
+
 def run_ours(args, rank: int, world_size: int, local_rank: int):
     import torch
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the render-prep path has no CPU fallback (use --impl reference)")
-    torch.cuda.set_device(local_rank)
+    device = place_rank(local_rank, world_size, torch.cuda.device_count(), args.placement)
+    torch.cuda.set_device(device)
     dist = None
     if world_size > 1:
         import torch.distributed as dist
 
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.init_process_group("nccl", device_id=torch.device("cuda", device))
     n = args.instances
-    sc = DeviceScene(n, rank, local_rank)
+    sc = DeviceScene(n, rank, device)
     # host placement before any pinned allocation: this process onto the CPUs / NUMA node of its GPU's PCIe root
     affinity = sc.ctx.bind_host_to_device(cpus=not args.no_numa_bind, memory=not args.no_numa_bind)
     ex = None
@@ -257,7 +269,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
 
     for _ in range(max(args.warmup, 3)):
         one_step()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(device)
     if rank == 0:
         sampler.start()  # before the barrier: spawning nvidia-smi takes milliseconds and would skew rank 0's start
     barrier()
@@ -335,6 +347,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                                "1024^2 pyramid, rebuilt every step) + LOD + indirect compaction",
                    "instances_per_gpu": n, "ids": "identity order", "visible": visible,
                    "l2": f"inputs (74 B x {n / 1e6:g}M = {n * 74 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
+                   "device_of_rank0": device, "placement": args.placement,
                    "sharding": ("instance range per rank; per-slot counts exchanged by "
                                 + ("one kernel over NVLink peer memory (peer stores + flags + scan)" if ex and ex.mode == "p2p"
                                    else "NCCL all-gather + device offset scan")) if world_size > 1 else "single GPU"},
@@ -561,6 +574,7 @@ def main():
     ap.add_argument("--e2e-upload", default="copy", choices=["copy", "pull"],
                     help="100 %-dirty transform upload: copy engine into staging + expand kernels (RVS_SYNC_FULL) or one zero-copy kernel (RVS_SYNC_FULL_PULL)")
     ap.add_argument("--e2e-headline-only", action="store_true", help="skip the by_layout / by_dirty_fraction e2e variants")
+    ap.add_argument("--placement", default="spread", choices=["spread", "packed"], help="rank -> GPU mapping when the box has more GPUs than ranks")
     ap.add_argument("--no-numa-bind", action="store_true", help="leave the process where the launcher put it (diagnostics)")
     ap.add_argument("--force-exchange", action="store_true", help="N=1: run the count exchange machinery anyway (diagnostics)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: per-slot count exchange")

@@ -460,7 +460,9 @@ RVE_API int rve_gather_instance_counts_multi(rve_ctx* ctx, const rve_buffer* ind
  * dense u32[dense_slots] array `dense_counts`), stores them into every rank's mailbox, signals, waits for every
  * peer's signal of the same `epoch` (1, 2, 3, ... - one per exchange, the same on all ranks) and writes
  * offsets_out[world][slots] (exclusive scan over ranks) and totals_out[slots]. mailboxes[q] is rank q's mailbox
- * (mailboxes[rank] = the local one). status (u32) is set to 1 if a peer did not arrive within ~2 s. world <= 8. */
+ * (mailboxes[rank] = the local one). status (u32): bit 0 is set if a peer did not arrive within ~2 s, bit 1 if a peer
+ * announced a different slot count; offsets / totals then hold 0xFFFFFFFF instead of values derived from stale counts.
+ * The mailbox geometry (64 header words, then counts) does not depend on the slot count of a call. world <= 8. */
 RVE_API size_t rve_count_mailbox_bytes(uint32_t world, uint32_t total_slots);
 RVE_API int rve_ipc_export(rve_ctx* ctx, rve_buffer buf, unsigned char out_handle[64]);
 RVE_API int rve_ipc_import(rve_ctx* ctx, const unsigned char handle[64], size_t bytes, rve_buffer* out);
@@ -468,6 +470,22 @@ RVE_API int rve_exchange_counts_p2p(rve_ctx* ctx, const rve_buffer* indirect, co
                                     const uint32_t* num_slots, uint32_t n_buffers, rve_buffer dense_counts,
                                     uint32_t dense_slots, const rve_buffer* mailboxes, uint32_t rank, uint32_t world,
                                     uint32_t epoch, rve_buffer offsets_out, rve_buffer totals_out, rve_buffer status);
+
+/* Device-side gather of the compacted ids for a single consumer (north_star: "all-gathered over NVLink only when a
+ * single consumer needs them"): after rve_exchange_counts_p2p of the same `epoch` produced offsets / totals, every rank
+ * writes its visible ids straight into the consumers' GLOBAL culling buffers over the mapped peer memory, at the slice
+ * the single-GPU cull would have used - cubo.cullingBufferOffset + numObjects * lod of the GLOBAL command
+ * (shaders/defaultcull.csh:305-312; consumed by the draw at src/RenderEngine_Draw.cpp:1537-1545) - displaced by
+ * offsets[rank][slot]; order inside a slice is rank order, then this rank's arrival order. Enqueue it behind the
+ * exchange on the same stream. Per slot s (<= 64): slot_buffer[s] indexes src_culling (<= 16 local culling buffers),
+ * src_start[s] / dst_start[s] are the first id slots of the local / global slice. dst_culling[q * n_buffers + b] is
+ * rank q's global buffer b, mapped with rve_ipc_import (own rank: the local handle); entries of ranks outside the
+ * `consumers` bit mask are ignored. id_base is added to every id (local -> global entity ids). A consumer's kernel
+ * returns when every rank's ids have landed; status bit 0 = timeout. NVLink traffic: 4 B x visible per remote consumer. */
+RVE_API int rve_gather_ids_p2p(rve_ctx* ctx, const rve_buffer* src_culling, uint32_t n_buffers, const uint32_t* slot_buffer,
+                               const uint32_t* src_start, const uint32_t* dst_start, uint32_t slots, const rve_buffer* dst_culling,
+                               uint32_t consumers, uint32_t id_base, rve_buffer offsets, rve_buffer totals, const rve_buffer* mailboxes,
+                               uint32_t rank, uint32_t world, uint32_t epoch, rve_buffer status);
 
 /* ------------------------------------------------------------------ */
 /* synthetic scene generation on the device (bench / C5)  */

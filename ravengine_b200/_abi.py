@@ -124,6 +124,8 @@ PROTOTYPES = {
     "rve_ipc_import": (C.c_int, [VP, VP, C.c_size_t, C.POINTER(u32)]),
     "rve_exchange_counts_p2p": (C.c_int, [VP, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), u32, u32, u32, C.POINTER(u32), u32, u32, u32,
                                           u32, u32, u32]),
+    "rve_gather_ids_p2p": (C.c_int, [VP, C.POINTER(u32), u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32), u32, C.POINTER(u32), u32, u32,
+                                     u32, u32, C.POINTER(u32), u32, u32, u32, u32]),
     "rve_scatter_rows": (C.c_int, [VP, u32, u32, u32, u64, u64, u32]),
     "rve_csm_camera_params": (None, [f32, u32, u32, C.POINTER(f32), C.POINTER(f32)]),
     "rve_csm_cascades": (C.c_int, [VP, u32, u32, u32, u32, u32, u32, u32, u32]),

@@ -214,6 +214,20 @@ class Context:
         _check(self.lib, self.lib.rve_exchange_counts_p2p(self.h, h, f, c, n, 0xFFFFFFFF, 0, m, rank, world, epoch, offsets.handle,
                                                           totals.handle, status.handle))
 
+    def gather_ids_p2p(self, src: list[Buffer], plan, dst: list[list], consumers: int, id_base: int, offsets: Buffer, totals: Buffer,
+                       mailboxes: list[Buffer], rank: int, world: int, epoch: int, status: Buffer) -> None:
+        """rve_gather_ids_p2p: `plan` is a sharding.GatherPlan, dst[q][b] rank q's global culling buffer b (None for non-consumers)."""
+        nb, ns = len(src), len(plan.slot_buffer)
+        sh = (C.c_uint32 * nb)(*[x.handle for x in src])
+        inv = 0xFFFFFFFF
+        dh = (C.c_uint32 * (world * nb))(*[(dst[q][b].handle if dst[q] and dst[q][b] is not None else inv) for q in range(world) for b in range(nb)])
+        sb = (C.c_uint32 * ns)(*plan.slot_buffer)
+        ss = (C.c_uint32 * ns)(*plan.src_start)
+        ds = (C.c_uint32 * ns)(*plan.dst_start)
+        m = (C.c_uint32 * world)(*[x.handle for x in mailboxes])
+        _check(self.lib, self.lib.rve_gather_ids_p2p(self.h, sh, nb, sb, ss, ds, ns, dh, consumers, id_base, offsets.handle, totals.handle, m,
+                                                     rank, world, epoch, status.handle))
+
     def wrap_pointer(self, ptr: int, nbytes: int, keepalive=None) -> Buffer:
         """Register device memory owned elsewhere (another context of the same device) as a buffer of this context."""
         out = C.c_uint32()

@@ -91,7 +91,7 @@ static int alloc_slot(rve_ctx* ctx, void* ptr, size_t bytes, bool owned, rve_buf
         slot = uint32_t(ctx->buffers.size());
         ctx->buffers.emplace_back();
     }
-    ctx->buffers[slot] = BufferRec{ptr, bytes, owned, true};
+    ctx->buffers[slot] = BufferRec{ptr, bytes, owned, true, false};
     ctx->table_dirty = true;
     *out = slot;
     return 0;
@@ -177,6 +177,13 @@ int rve_ctx_create(int device_ordinal, void* cuda_stream, rve_ctx** out_ctx) {
     }
     ctx->sm_count = prop.multiProcessorCount;
     ctx->l2_bytes = size_t(prop.l2CacheSize);
+    rc = check_cuda(cudaMalloc(reinterpret_cast<void**>(&ctx->d_gather_ticket), sizeof(uint32_t)), "cudaMalloc");
+    if (rc == 0) rc = check_cuda(cudaMemset(ctx->d_gather_ticket, 0, sizeof(uint32_t)), "cudaMemset");
+    if (rc == 0) rc = p2p_preload();
+    if (rc) {
+        delete ctx;
+        return rc;
+    }
     *out_ctx = ctx;
     return 0;
 }
@@ -196,6 +203,9 @@ int rve_ctx_destroy(rve_ctx* ctx) {
     if (ctx->d_views) cudaFree(ctx->d_views);
     if (ctx->d_lights) cudaFree(ctx->d_lights);
     if (ctx->d_slices) cudaFree(ctx->d_slices);
+    if (ctx->d_gather_ticket) cudaFree(ctx->d_gather_ticket);
+    for (auto& b : ctx->buffers)
+        if (b.live && b.ipc_imported && b.ptr) cudaIpcCloseMemHandle(b.ptr);
     if (ctx->owns_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
     return 0;
@@ -319,6 +329,10 @@ int rve_buffer_destroy(rve_ctx* ctx, rve_buffer buf) {
     if (!b) return RVE_ERR_BAD_HANDLE;
     // stream-ordered release: work already enqueued may still read the memory
     if (b->owned && b->ptr) RVE_CUDA(cudaFreeAsync(b->ptr, ctx->stream));
+    if (b->ipc_imported && b->ptr) {  // a peer's allocation: work enqueued so far may still touch it
+        RVE_CUDA(cudaStreamSynchronize(ctx->stream));
+        RVE_CUDA(cudaIpcCloseMemHandle(b->ptr));
+    }
     *b = BufferRec{};
     ctx->free_slots.push_back(buf);
     ctx->table_dirty = true;

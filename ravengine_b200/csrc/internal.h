@@ -16,6 +16,7 @@ struct BufferRec {
     size_t bytes = 0;
     bool owned = false;
     bool live = false;
+    bool ipc_imported = false;  // mapped by rve_ipc_import: unmapped (cudaIpcCloseMemHandle) when the handle is destroyed
 };
 
 struct PyramidRec {
@@ -94,6 +95,8 @@ struct rve_ctx {
     void* d_view_stride = nullptr;  // per-CUBO output strides of a view-batched cull
     size_t d_view_stride_cap = 0;
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
+    bool views_attr_set = false;  // cull_views_kernel's dynamic shared memory opt-in (per device, hence per context)
+    uint32_t* d_gather_ticket = nullptr;  // rve_gather_ids_p2p: CTAs-done counter
     // scratch: view-space light records for rve_cluster_assign
     float4* d_lights = nullptr;
     size_t d_lights_cap = 0;
@@ -105,6 +108,7 @@ struct rve_ctx {
 namespace rve {
 
 int set_error(int code, const char* fmt, ...);
+int p2p_preload();  // p2p.cu: forces the exchange / gather kernels to be loaded
 int check_cuda(cudaError_t e, const char* what);
 // resolves a handle; returns nullptr (and sets the error) when invalid
 BufferRec* get_buffer(rve_ctx* ctx, rve_buffer h, const char* role);

@@ -2,13 +2,15 @@
 is the plumbing. Every rank culls its slice of each command's entity list into rank-local compact slices; the only
 exchange step is the per-slot visible counts (all-gather, a few dozen bytes) followed by an exclusive scan over ranks,
 which gives each rank's offset inside the global per-(draw, LOD) slice and the global instanceCount. The compacted ids
-are gathered only when a single consumer needs them.
+are gathered only when a single consumer needs them - by a kernel that writes them straight into the consumer's global
+culling buffers over NVLink peer memory (csrc/p2p.cu, rve_gather_ids_p2p), chained behind the count exchange.
+Partition B (independent camera views) and the 2-D split (view range x instance range) are planned here too.
 
 Slot layout (identical to the single-GPU one, shaders/defaultcull.csh:305-312, src/RenderEngine_Draw.cpp:1334-1362):
 per material, command c with n_c entities and L_c LODs owns indirect slots [sum L_<c, +L_c) and the culling-buffer
 range starting at sum_{c'<c} L_c' * n_c', LOD l at + n_c * l.
 
-This module holds host logic only (integer plans + collectives); the scan itself is `rve_shard_offsets` on the device.
+This module holds host logic only (integer plans + process-group plumbing); the scan and the gather run on the device.
 """
 from __future__ import annotations
 
@@ -74,50 +76,89 @@ def exchange_counts(local_counts, world: int):
     return out
 
 
-def gather_ids(local_ids, local_plan: list[SlotPlan], global_plan: list[SlotPlan], counts_all, offsets_all, rank: int, world: int,
-               id_base_of_rank):
-    """All-gather of the compacted id slices into the global culling-buffer layout (only when one consumer needs them).
+@dataclass(frozen=True)
+class GatherPlan:
+    """Where every slot's ids travel in the device-side gather (rve_gather_ids_p2p): slot s reads this rank's slice at
+    src_start[s] of local culling buffer slot_buffer[s] (= material index) and lands in the consumer's GLOBAL buffer of
+    the same material at dst_start[s] + offsets[rank][s]."""
+    slot_buffer: tuple[int, ...]
+    src_start: tuple[int, ...]
+    dst_start: tuple[int, ...]
+    global_slots: tuple[int, ...]  # id slots of each material's global culling buffer (numEntities * numLODs)
 
-    local_ids[m]: this rank's culling buffer of material m (torch int32/uint32-as-int32 tensor);
-    counts_all / offsets_all: [world, total_slots] from exchange_counts / the exclusive scan (slots of all materials
-    concatenated in material order); id_base_of_rank(r): value added to rank r's local ids to make them global.
-    Returns one global culling buffer per material (filled with -1 where nothing was written)."""
-    import torch
-    import torch.distributed as dist
 
-    dev = local_ids[0].device
-    counts_host = counts_all.cpu().numpy().astype(np.int64)
-    offs_host = offsets_all.cpu().numpy().astype(np.int64)
-    # pack this rank's visible ids slot by slot, pad to the largest rank, all-gather
-    packed, s = [], 0
-    for m, plan in enumerate(local_plan):
-        for start in plan.slot_starts():
-            c = int(counts_host[rank, s])
-            packed.append(local_ids[m][start:start + c])
-            s += 1
-    mine = torch.cat(packed) if packed else torch.empty(0, dtype=torch.int32, device=dev)
-    per_rank = counts_host.sum(axis=1)
-    cap = int(per_rank.max()) if per_rank.size else 0
-    buf = torch.zeros(max(cap, 1), dtype=mine.dtype, device=dev)
-    buf[: mine.numel()] = mine
-    if world > 1:
-        parts = [torch.empty_like(buf) for _ in range(world)]
-        dist.all_gather(parts, buf)
-    else:
-        parts = [buf]
-    out = [torch.full((max(p.culling_slots, 1),), -1, dtype=mine.dtype, device=dev) for p in global_plan]
-    for r in range(world):
-        pos, s = 0, 0
-        base = id_base_of_rank(r)
-        for m, plan in enumerate(global_plan):
-            for gstart in plan.slot_starts():
-                c = int(counts_host[r, s])
-                if c:
-                    dst = gstart + int(offs_host[r, s])
-                    out[m][dst:dst + c] = parts[r][pos:pos + c] + base
-                pos += c
-                s += 1
-    return out
+def gather_plan(local_plan: list[SlotPlan], global_plan: list[SlotPlan]) -> GatherPlan:
+    """Slot layout on both sides of the gather. The global side is the single-GPU layout of the whole scene
+    (shaders/defaultcull.csh:305-312: cullingBufferOffset + numObjects * lod with GLOBAL numObjects)."""
+    buf, src, dst = [], [], []
+    for m, (lp, gp) in enumerate(zip(local_plan, global_plan)):
+        assert lp.lods == gp.lods, "local and global plans must describe the same commands"
+        ls, gs = lp.slot_starts(), gp.slot_starts()
+        buf += [m] * len(ls)
+        src += ls
+        dst += gs
+    return GatherPlan(tuple(buf), tuple(src), tuple(dst), tuple(p.culling_slots for p in global_plan))
+
+
+def split_views(num_views: int, world: int) -> list[tuple[int, int]]:
+    """Partition B: rank r owns the contiguous view range [r*V/R, (r+1)*V/R) - views are independent, no collective."""
+    return split_range(num_views, world)
+
+
+@dataclass(frozen=True)
+class Grid2D:
+    """View range x instance range (C5: 512 views over 1 B instances). world = view_groups * instance_groups; rank
+    r = vg * instance_groups + ig owns views split_views(V, view_groups)[vg] of instances split_range(n, instance_groups)[ig].
+    The per-slot count exchange (and the optional id gather) runs among the instance_groups ranks that share a view group
+    (`peers`), once per owned view; ranks of different view groups never talk."""
+    world: int
+    view_groups: int
+
+    def __post_init__(self):
+        assert self.view_groups >= 1 and self.world % self.view_groups == 0, "view groups must divide the world size"
+
+    @property
+    def instance_groups(self) -> int:
+        return self.world // self.view_groups
+
+    def coords(self, rank: int) -> tuple[int, int]:
+        return rank // self.instance_groups, rank % self.instance_groups
+
+    def peers(self, rank: int) -> list[int]:
+        vg, _ = self.coords(rank)
+        return [vg * self.instance_groups + i for i in range(self.instance_groups)]
+
+    def owned(self, rank: int, num_views: int, num_instances: int) -> tuple[tuple[int, int], tuple[int, int]]:
+        vg, ig = self.coords(rank)
+        return split_views(num_views, self.view_groups)[vg], split_range(num_instances, self.instance_groups)[ig]
+
+
+class ShardedViews:
+    """Partition B on one rank: cull this rank's view range of a batch with the view-batched kernel (rve_cull_views through
+    the shim, <= 128 views per call; the reference runs one cull per view, src/RenderEngine_Draw.cpp:1769-1866,
+    1870-1987). No data-path collective. After `cull_chunk(i)` each material's buffers hold the chunk's views as consecutive
+    copies of the single-view layout (view v of the chunk at v * numEntities*numLODs ids / v * numLODs commands), exactly
+    what rvs_cull_static_views produces for those views on one GPU."""
+
+    MAX_VIEWS_PER_CALL = 128
+
+    def __init__(self, world_obj, views: list, pyramids: list, rank: int, world_size: int):
+        assert len(views) == len(pyramids)
+        self.world_obj, self.rank, self.ws = world_obj, rank, world_size
+        self.lo, self.hi = split_views(len(views), world_size)[rank]
+        self.views, self.pyramids = views[self.lo:self.hi], pyramids[self.lo:self.hi]
+        k = self.MAX_VIEWS_PER_CALL
+        self.chunks = [(i, min(i + k, len(self.views))) for i in range(0, len(self.views), k)]
+
+    def cull_chunk(self, i: int) -> tuple[int, int]:
+        """Enqueues the cull of chunk i; returns the GLOBAL view range it covers."""
+        a, b = self.chunks[i]
+        self.world_obj.cull_static_views(self.views[a:b], self.pyramids[a:b])
+        return self.lo + a, self.lo + b
+
+    def cull_all(self) -> None:
+        for i in range(len(self.chunks)):
+            self.cull_chunk(i)
 
 
 class ShardedCull:
@@ -202,6 +243,57 @@ class ShardedCull:
             self.peers, self.mode = peers, "p2p"
         elif strict:
             raise RuntimeError(f"peer-memory count exchange unavailable: {err}")
+
+    def setup_gather(self, local_plan: list[SlotPlan], global_plan: list[SlotPlan], consumers: list[int], id_base: int) -> None:
+        """Device-side gather for `consumers` (ranks that need the whole compacted id lists). Consumers allocate one
+        global culling buffer per material (global numEntities * numLODs ids, the single-GPU layout) and publish it to
+        their peers as CUDA IPC handles; requires the peer-memory exchange (mode "p2p"), or world size 1."""
+        import torch.distributed as dist
+
+        assert self.ws == 1 or self.mode == "p2p", "the device-side gather runs over the peer-memory mailboxes"
+        self.gplan = gather_plan(local_plan, global_plan)
+        assert len(self.gplan.slot_buffer) == self.slots
+        self.consumers, self.id_base = sorted(consumers), id_base
+        self.global_ids = None
+        if self.rank in self.consumers:
+            self.global_ids = [self.ctx2.create_buffer(max(4 * n, 16)) for n in self.gplan.global_slots]
+            self.ctx2.synchronize()
+        nb = len(self.gplan.global_slots)
+        self._dst = [[None] * nb for _ in range(self.ws)]
+        if self.ws == 1:
+            self._dst[0] = self.global_ids
+            self._gather_boxes = getattr(self, "peers", None) or [self._solo_mailbox()]
+        else:
+            mine = [self.ctx2.ipc_export(b) for b in self.global_ids] if self.global_ids else []
+            allh = [None] * self.ws
+            dist.all_gather_object(allh, mine)
+            for q in self.consumers:
+                self._dst[q] = self.global_ids if q == self.rank else [self.ctx2.ipc_import(h, max(4 * n, 16))
+                                                                        for h, n in zip(allh[q], self.gplan.global_slots)]
+            self._gather_boxes = self.peers
+        self._local_ids2 = None
+
+    def _solo_mailbox(self):
+        self.mailbox = self.ctx2.create_buffer(self.ctx2.mailbox_bytes(1, self.slots))
+        self.mailbox.zero()
+        self.status = self.ctx2.create_buffer(16)
+        self.status.zero()
+        self.peers = [self.mailbox]
+        return self.mailbox
+
+    def gather(self, b: int) -> None:
+        """Enqueue the id gather of the exchange that just filled buffer set `b` (side stream, behind the exchange kernel)."""
+        import torch
+
+        if self._local_ids2 is None:  # this rank's culling buffers, seen from the side-stream context
+            bufs = [self.world_obj.material_outputs(m)[0] for m in self.mats]
+            self._local_ids2 = [self.ctx2.wrap_pointer(x.ptr, x.nbytes, keepalive=x) for x in bufs]
+        mask = sum(1 << q for q in self.consumers)
+        self.ctx2.gather_ids_p2p(self._local_ids2, self.gplan, self._dst, mask, self.id_base, self.b_off[b], self.b_tot[b],
+                                 self._gather_boxes, self.rank, self.ws, self.k, self.status)
+        self.done[b] = torch.cuda.Event()
+        self.done[b].record(self.side)
+        self.pending = self.done[b]  # the next cull rewrites the local slices: it must wait for this gather too
 
     def _indirect_buffers(self):
         bufs = [self.world_obj.material_outputs(m)[1] for m in self.mats]

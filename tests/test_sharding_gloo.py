@@ -91,8 +91,21 @@ def _worker(rank, world, port, q):
         totals = c.sum(axis=0)
         bases = [r[0] for r in sharding.split_range(E, world)]
         global_lists = [np.concatenate([lists[r][i] for r in range(world)]) for i in range(3)]
-        gathered = sharding.gather_ids([torch.from_numpy(ids.view(np.int32).copy()) for _, ids in local], _plans(local_lists),
-                                       _plans(global_lists), counts_all, offsets, rank, world, lambda r: bases[r])
+        # the device-side gather (rve_gather_ids_p2p) emulated with numpy from the same plan: every rank's slot slices land
+        # in the consumer's global buffers at dst_start[s] + offsets[rank][s], ids shifted by the rank's id base
+        plans_by_rank = [None] * world
+        dist.all_gather_object(plans_by_rank, (sharding.gather_plan(_plans(local_lists), _plans(global_lists)), [ids for _, ids in local]))
+        gathered = None
+        if rank == 0:
+            gp0 = plans_by_rank[0][0]
+            gathered = [np.full(max(n, 1), 0xFFFFFFFF, np.uint32) for n in gp0.global_slots]
+            offs = offsets.numpy().astype(np.int64)
+            for r, (gp, ids_r) in enumerate(plans_by_rank):
+                assert gp.dst_start == gp0.dst_start and gp.slot_buffer == gp0.slot_buffer
+                for s_, (b, src, dst) in enumerate(zip(gp.slot_buffer, gp.src_start, gp.dst_start)):
+                    n = int(c[r, s_])
+                    gathered[b][dst + offs[r, s_]: dst + offs[r, s_] + n] = ids_r[b][src:src + n] + np.uint32(bases[r])
+            gathered = [torch.from_numpy(g.view(np.int32)) for g in gathered]
         if rank == 0:
             ref = _cull(_materials(global_lists), model, layers, flags, cam, depth)
             ref_counts = np.concatenate([ind[:, 1] for ind, _ in ref]).astype(np.int64)
@@ -108,6 +121,27 @@ def _worker(rank, world, port, q):
             q.put((ok, int(totals.sum()), totals.tolist()))
     finally:
         dist.destroy_process_group()
+
+
+def test_gather_plan_view_split_and_2d_grid():
+    lp = [SlotPlan((5, 2), (3, 1)), SlotPlan((3,), (2,))]
+    gp = [SlotPlan((10, 4), (3, 1)), SlotPlan((7,), (2,))]
+    g = sharding.gather_plan(lp, gp)
+    assert g.slot_buffer == (0, 0, 0, 0, 1, 1)
+    assert g.src_start == (0, 5, 10, 15, 0, 3) and g.dst_start == (0, 10, 20, 30, 0, 7)
+    assert g.global_slots == (56, 14)
+    assert sharding.split_views(512, 8)[3] == (192, 256) and sharding.split_views(5, 2) == [(0, 2), (2, 5)]
+    grid = sharding.Grid2D(8, 2)  # 2 view groups x 4 instance groups
+    assert grid.instance_groups == 4 and grid.coords(5) == (1, 1) and grid.peers(5) == [4, 5, 6, 7]
+    assert grid.owned(5, 512, 1_000_000_000) == ((256, 512), (250_000_000, 500_000_000))
+    # every (view, instance) pair is owned exactly once
+    cover = np.zeros((16, 40), np.int32)
+    for r in range(8):
+        (v0, v1), (i0, i1) = grid.owned(r, 16, 40)
+        cover[v0:v1, i0:i1] += 1
+    assert (cover == 1).all()
+    with pytest.raises(AssertionError):
+        sharding.Grid2D(8, 3)
 
 
 def test_split_range_and_slot_plan():
