@@ -102,7 +102,7 @@ class DeviceScene:
     """C2 scene resident in HBM on one rank: per-entity arrays generated on the device from
     (seed, global index); 4 materials x 1 mesh collection x 3 LODs over contiguous id ranges."""
 
-    def __init__(self, n: int, rank: int, device: int):
+    def __init__(self, n: int, rank: int, device: int, first_index: int | None = None):
         import torch
 
         from ravengine_b200 import Context
@@ -120,7 +120,7 @@ class DeviceScene:
         c = self.ctx
         self.model, self.layers = c.wrap_tensor(self.t_model), c.wrap_tensor(self.t_layers)
         self.flags, self.ids = c.wrap_tensor(self.t_flags), c.wrap_tensor(self.t_ids)
-        c.gen_instances(gen_params(C2["seed"]), rank * n, n, self.model, self.layers, self.flags, self.ids)
+        c.gen_instances(gen_params(C2["seed"]), rank * n if first_index is None else first_index, n, self.model, self.layers, self.flags, self.ids)
         self.cam, depth = camera_and_depth()
         self.depth_host = depth
         self.t_depth = torch.from_numpy(depth).to(dev)
@@ -158,11 +158,29 @@ class DeviceScene:
             out.append(ind.download(np.uint32).reshape(-1, 5)[:lods, 1])
         return np.concatenate(out)
 
+    def slot_plans(self, n: int | None = None):
+        """sharding.SlotPlan per material for `n` instances split over the materials like this scene's"""
+        from ravengine_b200.sharding import SlotPlan
 
-def cpu_sample_run(sample: int, reps: int, cam, depth, workers: int | None = None):
-    """The oracle (CPU restatement; taskflow executor when the reference's vendored taskflow was
-    available at build time) on `sample` instances of the same generator / camera / pyramid.
-    Returns (instances_per_s, cores, kind, sample_desc, per-rep seconds)."""
+        n = self.n if n is None else n
+        m = C2["materials"]
+        return [SlotPlan((n * (i + 1) // m - n * i // m,), (len(C2["lod_distances"]),)) for i in range(m)]
+
+    def release(self):
+        """free the scene's device memory (the C5 scene needs the room at N = 1)"""
+        self.ctx.synchronize()
+        self.world.destroy()
+        self.ctx.close()
+        for k in ("t_model", "t_layers", "t_flags", "t_ids", "t_depth"):
+            setattr(self, k, None)
+        self.torch.cuda.empty_cache()
+
+
+def cpu_sample_run(sample: int, reps: int, cam, depth, workers: int | None = None, warmup: int = 0):
+    """The CPU path of the same step on the host cores: the oracle (CPU restatement of depthpyramidcopy.fsh / depthpyramid.csh /
+    defaultcull.csh; TEST INFRASTRUCTURE, timed here as the reported baseline) through the reference's own executor (vendored
+    taskflow) with the engine's worker count. One step = pyramid build + indirect re-init + cull/LOD/append over `sample`
+    instances of the C2 generator. Returns (instances_per_s, cores, kind, sample_desc, per-step seconds after warm-up)."""
     import oracle
     from oracle import host_tables
     from ravengine_b200 import scenes
@@ -182,21 +200,24 @@ def cpu_sample_run(sample: int, reps: int, cam, depth, workers: int | None = Non
         mats.append(scenes.MaterialDraws([scenes.DrawCommand(mesh, ids[bounds[i]:bounds[i + 1]])]))
     t = host_tables.build_static_tables(mats)
     ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos)
-    t0 = time.perf_counter()
-    pyr, dim, levels = oracle.pyramid_build(depth, min(C2["depth"]))
-    t_pyr = time.perf_counter() - t0
     groups = (t.total_entities + 63) // 64
-    times = []
-    for _ in range(reps):
+    times, t_pyr = [], []
+    for _ in range(warmup + reps):
+        t0 = time.perf_counter()
+        pyr, dim, levels = oracle.pyramid_build(depth, min(C2["depth"]), nthreads=workers, taskflow=tf)
+        t1 = time.perf_counter()
         for b in t.bindless:  # indirect re-init, like the reference's per-pass CopyBufferToBuffer
             if b is not None and b.ndim == 2:
                 b[:, 1] = 0
-        t0 = time.perf_counter()
         oracle.cull(ubo, t.cubos, model, layers, flags, pyr, dim, levels, t.bindless, groups, workers, tf)
         times.append(time.perf_counter() - t0)
+        t_pyr.append(t1 - t0)
+    times, t_pyr = times[warmup:], t_pyr[warmup:]
     best = float(np.median(times))
-    desc = (f"{sample} instances of the C2 generator (seed {C2['seed']}), cull+LOD+append only, median of {reps}; "
-            f"pyramid build (serial, {t_pyr:.2f}s) excluded; {'taskflow' if tf else 'std::thread'} executor")
+    visible = int(sum(int(b[:, 1].sum()) for b in t.bindless if b is not None and b.ndim == 2))
+    desc = (f"{sample} instances of the C2 generator (seed {C2['seed']}){' = the full C2 scene' if sample == C2['instances'] else ''}; per step: "
+            f"pyramid build ({float(np.median(t_pyr)) * 1e3:.1f} ms) + indirect re-init + cull/LOD/append, median of {reps}; "
+            f"{'taskflow' if tf else 'std::thread'} executor, {workers} workers; visible {visible}")
     return sample / best, workers, "port", desc, times
 
 
@@ -204,22 +225,22 @@ def run_reference(args, rank: int):
     if rank != 0:
         return
     cam, depth = camera_and_depth()
-    sample = args.cpu_sample or 2_000_000
-    v, cores, kind, desc, times = cpu_sample_run(sample, args.warmup + args.steps, cam, depth)
-    times = times[args.warmup:]
+    sample = args.cpu_sample or C2["instances"]
+    v, cores, kind, desc, times = cpu_sample_run(sample, args.steps, cam, depth, warmup=args.warmup)
     ms = float(np.mean(times)) * 1e3
     v = sample / (ms / 1e3)
     line = {"impl": "reference", "metric": "culled instances/s", "value": v, "unit": "instances/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2 (bounded sample): frustum + Hi-Z + LOD cull with indirect compaction, CPU restatement of "
-                                   "defaultcull.csh on host cores", "instances_per_step": sample, "lods": 3,
-                       "depth": list(C2["depth"])},
+            "config": {"workload": "C2: 10M instances, 4 materials x 3 LODs {0,40,120}, frustum + Hi-Z (3840x2160 depth -> 1024^2 pyramid, "
+                                   "rebuilt every step) + LOD + indirect compaction; CPU restatement of the shaders on host cores",
+                       "instances_per_step": sample, "lods": 3, "depth": list(C2["depth"]), "same_config_as_gpu_arm": sample == C2["instances"]},
             "cpu_baseline": {"value": v, "unit": "instances/s", "cores": cores, "kind": kind, "sample": desc},
             "e2e": {"value": v, "unit": "instances/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0,
             "note": "the reference's own implementation needs a graphics API (unavailable on this box); this is the "
-                    "CPU oracle port on all host worker threads the engine would use (hardware_concurrency-2)"}
+                    "CPU oracle port on all host worker threads the engine would use (hardware_concurrency-2), one rank "
+                    "regardless of --gpus (the CPU path does not shard)"}
     print(json.dumps(line), flush=True)
 
 
@@ -328,16 +349,44 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     else:
         e2e = run_e2e(sc, args, torch, barrier, dist, affinity)
 
+    ex_mode = ex.mode if ex else None
+    sc_slots, pyr_dim = sc.slots, sc.pyr.dim
+    # --- device-side gather of the compacted ids for one consumer (rank 0), N > 1 only ---
+    gather = run_gather(sc, ex, args, torch, barrier, dist, rank, world_size) if (ex and world_size > 1 and ex.mode == "p2p" and not args.no_gather) else None
+
+    # --- C5: 512 camera views sharded by view range, 1 B instances sharded by instance range (fixed totals: strong scaling) ---
+    c5 = None
+    if not args.no_c5 and n == C2["instances"]:
+        c5 = {"views512": run_c5_views(sc, args, torch, barrier, dist, rank, world_size)}
+        cam, depth_host = sc.cam, sc.depth_host
+        if ex:
+            ex.close()
+        sc.release()
+        sc = ex = None
+        c5["instances_1B"] = run_c5_instances(args, torch, barrier, dist, rank, world_size, device)
+    else:
+        cam, depth_host = sc.cam, sc.depth_host
+
     if rank != 0:
         if dist:
             dist.destroy_process_group()
         return
-    cpu_v, cores, kind, desc, _ = (None, None, None, None, None)
+    stages = None
+    if world_size == 1 and not args.no_stages and n == C2["instances"]:
+        from tools import stage_bench
+
+        st_stream = torch.cuda.Stream(device=device)
+        from ravengine_b200 import Context
+
+        st_ctx = Context(device, st_stream.cuda_stream)
+        stages = list(stage_bench.run_stages(st_ctx, st_stream, reps=10, only={"c1", "c2s", "pyramid", "c3", "c4"}, cpu=not args.no_cpu_baseline))
+        st_ctx.close()
     cpu = None
-    if world_size == 1 and not args.no_cpu_baseline:
-        cpu_v, cores, kind, desc, _ = cpu_sample_run(args.cpu_sample or 1_000_000, 5, sc.cam, sc.depth_host)
+    if not args.no_cpu_baseline:
+        cpu_v, cores, kind, desc, _ = cpu_sample_run(args.cpu_sample or C2["instances"], 5, cam, depth_host, warmup=1)
         cpu = {"value": cpu_v, "unit": "instances/s", "cores": cores, "kind": kind, "sample": desc}
     total_instances = n * world_size
+    slots = C2["materials"] * len(C2["lod_distances"])
     line = {
         "metric": "culled instances/s", "value": total_instances / (ms_step * 1e-3), "unit": "instances/s",
         "n_gpus": world_size, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms_step,
@@ -349,11 +398,11 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                    "l2": f"inputs (74 B x {n / 1e6:g}M = {n * 74 / 1e6:.0f} MB) exceed the 126 MB L2; no explicit flush",
                    "device_of_rank0": device, "placement": args.placement,
                    "sharding": ("instance range per rank; per-slot counts exchanged by "
-                                + ("one kernel over NVLink peer memory (peer stores + flags + scan)" if ex and ex.mode == "p2p"
+                                + ("one kernel over NVLink peer memory (peer stores + flags + scan)" if ex_mode == "p2p"
                                    else "NCCL all-gather + device offset scan")) if world_size > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "kernel": "cull_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": cull_avg_ms,
+                     "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": cull_avg_ms, "slots": slots,
                      "frac_of_8000_datasheet": achieved / 8000.0, "pyramid_kernel_ms": pyr_ms / max(pyr_n, 1)},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
         "ms_per_step_by_rank": by_rank, "cull_kernel_ms_by_rank": cull_by_rank,
@@ -361,14 +410,214 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     }
     if cpu:
         line["cpu_baseline"] = cpu
+    if gather:
+        line["gather"] = gather
+    if c5:
+        line["c5"] = c5
+    if stages:
+        line["stages"] = stages
     print(json.dumps(line), flush=True)
     if dist:
         dist.destroy_process_group()
 
 
-def _affine48(m64: np.ndarray) -> np.ndarray:
-    """(n, 16) column-major mat4 rows -> (n, 12) mat4x3 rows (columns c0..c3, xyz each): the RVS_VECTOR_AFFINE_ROWS host layout"""
-    return np.ascontiguousarray(m64.reshape(-1, 4, 4)[:, :, :3].reshape(-1, 12))
+def run_gather(sc, ex, args, torch, barrier, dist, rank, world_size):
+    """N > 1: the step followed by the device-side gather of every rank's compacted ids into rank 0's GLOBAL culling buffers
+    (rve_gather_ids_p2p over NVLink peer memory, chained behind the count exchange on the side stream; no host sync).
+    Checked in place: per slot, the ids that landed on rank 0 are exactly `total` distinct values whose sum and sum of squares
+    (mod 2^64) equal the all-reduced sums of every rank's local slices shifted by its id base."""
+    n = sc.n
+    from ravengine_b200.sharding import SlotPlan
+
+    local_plan = sc.slot_plans(n)
+    global_plan = [SlotPlan(tuple(c * world_size for c in p.counts), p.lods) for p in local_plan]  # every rank holds the same split
+    # entity-id lists of the bench are contiguous per material on every rank: rank r's material m holds local ids
+    # [n*m/M, n*(m+1)/M); globally that is NOT one contiguous range, so the "global id" of a local id is rank*n + id
+    ex.setup_gather(local_plan, global_plan, [0], rank * n)
+    steps = max(3, min(args.steps, 10))
+
+    def one():
+        sc.step(ex.begin_cull)
+        b = ex.exchange()
+        ex.gather(b)
+        return b
+
+    for _ in range(2):
+        one()
+    ex.finish()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(sc.stream)
+    for _ in range(steps):
+        b = one()
+    ex.finish()
+    ev1.record(sc.stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1) / steps
+    # the gather alone: exchange + gather on an otherwise idle GPU, events on the side stream
+    g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    g0.record(ex.side)
+    b = ex.exchange()
+    ex.gather(b)
+    g1.record(ex.side)
+    ex.finish()
+    barrier()
+    ms_alone = g0.elapsed_time(g1)
+    t = torch.tensor([ms, ms_alone], device="cuda")
+    allt = torch.zeros((world_size, 2), device="cuda")
+    dist.all_gather_into_tensor(allt.view(-1), t)
+    ms, ms_alone = float(allt[:, 0].max().item()), float(allt[:, 1].max().item())
+    # verification
+    totals = ex.t_tot[b].cpu().numpy().view(np.uint32).astype(np.int64)
+    offs = ex.t_off[b].cpu().numpy().view(np.uint32).astype(np.int64)
+    sums = np.zeros((len(totals), 2), np.uint64)
+    s = 0
+    mine = 0
+    for m, plan in enumerate(local_plan):
+        ids = sc.world.material_outputs(sc.mats[m])[0].download(np.uint32)
+        for start in plan.slot_starts():
+            cnt = int((offs[rank + 1, s] if rank + 1 < world_size else totals[s]) - offs[rank, s])
+            v = ids[start:start + cnt].astype(np.uint64) + np.uint64(rank * n)
+            sums[s] = (v.sum(dtype=np.uint64), (v * v).sum(dtype=np.uint64))
+            mine += cnt
+            s += 1
+    ts = torch.from_numpy(sums.view(np.int64)).cuda()
+    parts = torch.zeros((world_size,) + tuple(ts.shape), dtype=torch.int64, device="cuda")
+    dist.all_gather_into_tensor(parts.view(-1), ts.view(-1))
+    want = parts.cpu().numpy().view(np.uint64).sum(axis=0, dtype=np.uint64)
+    ok, landed = None, None
+    if rank == 0:
+        ok, landed, s = True, 0, 0
+        for m, plan in enumerate(global_plan):
+            got = ex.global_ids[m].download(np.uint32)
+            for start in plan.slot_starts():
+                v = got[start:start + int(totals[s])].astype(np.uint64)
+                ok = ok and len(np.unique(v)) == len(v) and v.sum(dtype=np.uint64) == want[s, 0] and (v * v).sum(dtype=np.uint64) == want[s, 1]
+                landed += len(v)
+                s += 1
+        ok = bool(ok) and not ex.timed_out()
+    return {"ms_per_step_with_gather": ms, "ms_exchange_plus_gather_alone": ms_alone, "steps": steps, "consumer": 0,
+            "ids_landed_on_consumer": landed, "nvlink_bytes_per_step": None if landed is None else 4 * (landed - mine),
+            "verified": ok, "check": "per slot: distinct ids, sum and sum of squares (mod 2^64) equal the all-reduced local slices",
+            "note": "one gather kernel per rank writes its slices straight into rank 0's global culling buffers "
+                    "(cullingBufferOffset + numObjects*lod + offset[rank][slot], defaultcull.csh:305-312) over peer memory"}
+
+
+def c5_cameras(num_views: int):
+    """BASELINE C5's 32 x 16 camera grid over the scene, every camera looking down -Z like the C2 camera"""
+    from ravengine_b200 import scenes
+
+    grid = [(x, z) for z in np.linspace(-400, 400, 16) for x in np.linspace(-400, 400, 32)]
+    return [scenes.default_camera(z_near=C2["z_near"], z_far=C2["z_far"], eye=(grid[i % 512][0], 5.0, grid[i % 512][1]),
+                                  target=(grid[i % 512][0], 5.0, grid[i % 512][1] - 1.0)) for i in range(num_views)]
+
+
+def run_c5_views(sc, args, torch, barrier, dist, rank, world_size):
+    """Partition B: `--c5-views` (512) independent camera views over the 10 M-instance C2 scene, every rank holding the whole
+    scene and culling its own view range with the view-batched kernel (no collective). Fixed total work: strong scaling."""
+    from ravengine_b200.sharding import ShardedViews
+
+    V = args.c5_views
+    cams = c5_cameras(V)
+    views = [(c.view_proj_cm, c.pos, 0xFFFFFFFF, False) for c in cams]
+    sv = ShardedViews(sc.world, views, [sc.pyr] * V, rank, world_size)
+    sc.step()
+    sv.cull_chunk(0)  # warm-up: buffers for 128 views per material
+    barrier()
+    reps = 2
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(sc.stream)
+    for _ in range(reps):
+        sv.cull_all()
+    ev1.record(sc.stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1) / reps
+    vis = 0
+    for i in range(len(sv.chunks)):  # visible (instance, view) pairs, outside the timed region
+        g0, g1 = sv.cull_chunk(i)
+        sc.ctx.synchronize()
+        for m in sc.mats:
+            _, ind, lods, _ = sc.world.material_outputs(m)
+            vis += int(ind.download(np.uint32).reshape(-1, 5)[:(g1 - g0) * lods, 1].sum())
+    by_rank = [ms]
+    if dist:
+        t = torch.tensor([ms, float(vis)], device="cuda", dtype=torch.float64)
+        allt = torch.zeros((world_size, 2), device="cuda", dtype=torch.float64)
+        dist.all_gather_into_tensor(allt.view(-1), t)
+        by_rank = [float(x) for x in allt[:, 0].tolist()]
+        ms, vis = float(allt[:, 0].max().item()), int(allt[:, 1].sum().item())
+    # release the 128-view buffers (15 GB per rank) before the 1 B-instance scene
+    sc.world.cull_static(sc.vp, sc.cam_pos, sc.pyr)
+    sc.ctx.synchronize()
+    return {"value": sc.n * V / (ms * 1e-3), "unit": "instance-views/s", "views": V, "instances": sc.n, "ms_per_pass": ms,
+            "ms_per_pass_by_rank": by_rank, "views_per_rank": sv.hi - sv.lo, "visible_instance_views": vis, "scaling": "strong",
+            "sharding": "view range per rank (partition B), no collective; every rank holds the whole scene",
+            "check": "visible_instance_views is the same at every N (tests/test_gpu_sharding.py pins the per-rank slices to the one-GPU batch)"}
+
+
+def run_c5_instances(args, torch, barrier, dist, rank, world_size, device):
+    """Partition A at C5 size: a FIXED scene of `--c5-instances` (1 B) instances split by instance range over the ranks
+    (strong scaling; 74 GB of inputs at N = 1), per-slot counts exchanged by the peer-memory kernel."""
+    total = args.c5_instances
+    lo, hi = rank * total // world_size, (rank + 1) * total // world_size
+    n = hi - lo
+    sc = DeviceScene(n, 0, device, first_index=lo)
+    ex = None
+    if world_size > 1:
+        from ravengine_b200.sharding import ShardedCull
+
+        ex = ShardedCull(sc.ctx, sc.world, sc.mats, [len(C2["lod_distances"])] * len(sc.mats), world_size, sc.stream, rank=rank, exchange=args.exchange)
+
+    def one():
+        sc.step(ex.begin_cull if ex else None)
+        return ex.exchange() if ex else 0
+
+    for _ in range(2):
+        one()
+    barrier()
+    steps = 5
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(sc.stream)
+    for _ in range(steps):
+        b = one()
+    if ex:
+        ex.finish()
+    ev1.record(sc.stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1) / steps
+    sc.ctx.set_profiling(True)
+    for _ in range(3):
+        sc.step()
+    k_ms, k_n = sc.ctx.profile_read(0)
+    sc.ctx.set_profiling(False)
+    k_ms /= max(k_n, 1)
+    counts = sc.visible_counts().astype(np.int64)
+    by_rank, k_by_rank = [ms], [k_ms]
+    if dist:
+        t = torch.tensor([ms, k_ms], device="cuda")
+        allt = torch.zeros((world_size, 2), device="cuda")
+        dist.all_gather_into_tensor(allt.view(-1), t)
+        by_rank, k_by_rank = [float(x) for x in allt[:, 0].tolist()], [float(x) for x in allt[:, 1].tolist()]
+        ms = float(allt[:, 0].max().item())
+        totals = ex.t_tot[b].cpu().numpy().view(np.uint32).astype(np.int64)  # the exchange's global instanceCount per slot
+        tc = torch.from_numpy(counts).cuda()
+        dist.all_reduce(tc)
+        assert np.array_equal(tc.cpu().numpy(), totals), "count exchange totals differ from the all-reduced local counts"
+        counts = totals
+    peak, _ = peaks()
+    vis_local = int(sc.visible_counts().sum())
+    algo = n * BYTES_PER_INSTANCE + vis_local * 4 + 4 * (4 * sc.pyr.dim ** 2 - 1) // 3
+    out = {"value": total / (ms * 1e-3), "unit": "instances/s", "instances_total": total, "instances_per_rank": n, "ms_per_step": ms,
+           "ms_per_step_by_rank": by_rank, "cull_kernel_ms_by_rank": k_by_rank, "steps": steps, "scaling": "strong",
+           "cull_kernel_frac_of_measured_peak_rank0": algo / (k_ms * 1e-3) / 1e9 / peak,
+           "visible_per_slot_global": counts.tolist(), "visible_total": int(counts.sum()),
+           "sharding": "instance range per rank (partition A); per-slot counts by one peer-memory kernel" if world_size > 1 else "single GPU",
+           "check": "visible_per_slot_global is the same at every N (same generator, same camera)"}
+    if ex:
+        ex.close()
+    sc.release()
+    return out
 
 
 class HostScene:
@@ -382,9 +631,11 @@ class HostScene:
 
         n, ctx = sc.n, sc.ctx
         self.sc, self.affine = sc, affine
-        m64 = sc.t_model.cpu().numpy()
         self.model = BufferedVRAMVector(ctx, 48 if affine else 64, n, affine_rows=affine)
-        self.model.host(np.float32).reshape(n, 12 if affine else 16)[:] = _affine48(m64) if affine else m64
+        host = self.model.host(np.float32).reshape(n, 12 if affine else 16)
+        for a in range(0, n, 1 << 20):  # device -> pinned host in 1 M-row pieces (no second host copy of the scene)
+            rows = sc.t_model[a:a + (1 << 20)]
+            host[a:a + rows.shape[0]] = (rows.view(-1, 4, 4)[:, :, :3].reshape(-1, 12) if affine else rows).cpu().numpy()
         self.layers = BufferedVRAMVector(ctx, 4, n)
         self.layers.host(np.int32)[:] = sc.t_layers.cpu().numpy()
         self.flags = BufferedVRAMVector(ctx, 2, n)
@@ -576,6 +827,11 @@ def main():
     ap.add_argument("--e2e-headline-only", action="store_true", help="skip the by_layout / by_dirty_fraction e2e variants")
     ap.add_argument("--placement", default="spread", choices=["spread", "packed"], help="rank -> GPU mapping when the box has more GPUs than ranks")
     ap.add_argument("--no-numa-bind", action="store_true", help="leave the process where the launcher put it (diagnostics)")
+    ap.add_argument("--no-gather", action="store_true", help="N>1: skip the device-side id gather leg")
+    ap.add_argument("--no-c5", action="store_true", help="skip the C5 sub-results (512 views / 1 B instances)")
+    ap.add_argument("--no-stages", action="store_true", help="N=1: skip the per-stage block (C1, C2 shuffled, pyramid, C3, C4)")
+    ap.add_argument("--c5-instances", type=int, default=1_000_000_000, help="total instances of the C5 instance-range scene")
+    ap.add_argument("--c5-views", type=int, default=512)
     ap.add_argument("--force-exchange", action="store_true", help="N=1: run the count exchange machinery anyway (diagnostics)")
     ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"], help="N>1: per-slot count exchange")
     args = ap.parse_args()

@@ -78,13 +78,16 @@ def pyramid_level_offset(dim: int, level: int) -> int:
     return int(lib().orc_pyramid_level_offset(u32(dim), u32(level)))
 
 
-def pyramid_build(depth: np.ndarray, width_for_dim: int | None = None) -> tuple[np.ndarray, int, int]:
-    """depth: (h, w) float32. Returns (flat mip chain, dim, levels)."""
+def pyramid_build(depth: np.ndarray, width_for_dim: int | None = None, nthreads: int = 1, taskflow: bool = False) -> tuple[np.ndarray, int, int]:
+    """depth: (h, w) float32. Returns (flat mip chain, dim, levels). nthreads > 1: rows dealt to worker threads (same values)."""
     h, w = depth.shape
     dim, levels = pyramid_dims(min(w, h) if width_for_dim is None else width_for_dim)
     out = np.zeros(int(lib().orc_pyramid_texel_count(u32(dim))), dtype=np.float32)
     depth = np.ascontiguousarray(depth, dtype=np.float32)
-    lib().orc_pyramid_build(_p(depth), u32(w), u32(h), _p(out), u32(dim), u32(levels))
+    if nthreads > 1:
+        lib(taskflow).orc_pyramid_build_mt(_p(depth), u32(w), u32(h), _p(out), u32(dim), u32(levels), C.c_int(nthreads))
+    else:
+        lib().orc_pyramid_build(_p(depth), u32(w), u32(h), _p(out), u32(dim), u32(levels))
     return out, dim, levels
 
 

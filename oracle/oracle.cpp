@@ -424,6 +424,30 @@ void orc_pyramid_build(const float* depth, uint32_t width, uint32_t height, floa
     }
 }
 
+// the same build with rows dealt to worker threads (the CPU baseline uses every host thread the engine would)
+void orc_pyramid_build_mt(const float* depth, uint32_t width, uint32_t height, float* pyramid, uint32_t dim, uint32_t num_levels,
+                          int nthreads) {
+    parallel_chunks(dim, nthreads, [&](uint64_t y) {
+        for (uint32_t x = 0; x < dim; ++x) {
+            const float u = (float(x) + 0.5f) / float(dim);
+            const float v = (float(y) + 0.5f) / float(dim);
+            pyramid[uint64_t(y) * dim + x] = sample_min(depth, width, height, u, v);
+        }
+    });
+    for (uint32_t l = 1; l < num_levels; ++l) {
+        const uint32_t din = dim >> (l - 1), dout = dim >> l;
+        const float* src = pyramid + level_offset(dim, l - 1);
+        float* dst = pyramid + level_offset(dim, l);
+        parallel_chunks(dout, dout >= 64 ? nthreads : 1, [&](uint64_t y) {
+            for (uint32_t x = 0; x < dout; ++x) {
+                const float u = (float(x) + 0.5f) / float(dout);
+                const float v = (float(y) + 0.5f) / float(dout);
+                dst[uint64_t(y) * dout + x] = sample_min(src, din, din, u, v);
+            }
+        });
+    }
+}
+
 void orc_cull(const RveCullingUBO* ubo, const RveCullingUBOinstance* cubos, const float* model_matrices,
               const uint32_t* render_layers, const uint16_t* per_object_flags, const float* pyramid,
               uint32_t pyr_dim, uint32_t pyr_levels, void* const* bindless, uint32_t num_groups_x, int nthreads) {

@@ -30,6 +30,8 @@ uint64_t orc_pyramid_level_offset(uint32_t dim, uint32_t level);
 /* depthpyramidcopy.fsh:10-20 + depthpyramid.csh:9-28 */
 void orc_pyramid_build(const float* depth, uint32_t width, uint32_t height, float* pyramid, uint32_t dim,
                        uint32_t num_levels);
+void orc_pyramid_build_mt(const float* depth, uint32_t width, uint32_t height, float* pyramid, uint32_t dim, uint32_t num_levels,
+                          int nthreads);
 /* the min-reduction sampler model (src/RenderEngine.cpp:323-331), exposed for unit tests */
 float orc_sample_min(const float* image, uint32_t w, uint32_t h, float u, float v);
 float orc_ceil_log2(float v);

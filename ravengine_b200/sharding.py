@@ -355,6 +355,12 @@ class ShardedCull:
     def finish(self) -> None:
         self.stream.wait_stream(self.side)
 
+    def close(self) -> None:
+        """Joins the side stream and releases the side-stream context (peer mappings are unmapped with it)."""
+        self.finish()
+        self.ctx2.synchronize()
+        self.ctx2.close()
+
     def timed_out(self) -> bool:
         """True when a peer failed to arrive within the exchange kernel's timeout (p2p mode; synchronises)."""
         if self.mode != "p2p":

@@ -2,9 +2,12 @@
 """Per-stage timings of the render-prep path against each kernel's roofline, one JSON line per stage:
 C1 (100 k cull, frustum+LOD), C2 variants (shuffled ids), pyramid (3840x2160), C3 (skinning 10 k x 20 k verts, or a
 scaled-down object count with --c3-objects), skinned draw-call prep, C4 (cluster build + assign, 65 536 lights, 5 views).
-`python bench.py` stays the headline (C2); this tool fills profiles/ with the other rows.
+Every stage line carries the CPU number of the same stage (the oracle on the host cores, taskflow executor, core count
+stated; bounded sample where the full stage would take too long) - `cpu: false` skips those legs.
 
-  python tools/stage_bench.py [--reps 20] [--c3-objects 10000] > profiles/rNN_stages.jsonl
+`python bench.py` imports run_stages() for the `stages` block of its N=1 line; run alone this tool fills profiles/:
+
+  python tools/stage_bench.py [--reps 20] [--c3-objects 10000] [--no-cpu] > profiles/rNN_stages.jsonl
 """
 from __future__ import annotations
 
@@ -12,6 +15,7 @@ import argparse
 import json
 import math
 import sys
+import time
 from pathlib import Path
 
 import numpy as np
@@ -52,10 +56,52 @@ def line(stage, workload, ms_med, ms_best, algo_bytes, bound, extra=None):
          "achieved_gbs": algo_bytes / (ms_med * 1e-3) / 1e9, "peak_gbs": PEAK, "frac_of_measured_peak": algo_bytes / (ms_med * 1e-3) / 1e9 / PEAK,
          "bound": bound}
     d.update(extra or {})
-    print(json.dumps(d), flush=True)
+    return d
 
 
-def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush):
+def _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats, reps=3):
+    """the same cull on the host cores: oracle (CPU restatement, TEST INFRASTRUCTURE) with the engine's worker count"""
+    import oracle
+    from oracle import host_tables
+    from tests.helpers import make_ubo
+
+    tf = oracle.LIB_TF.exists()
+    workers = oracle.default_workers()
+    model = np.zeros((n, 16), np.float32)
+    layers, flags, ids = np.zeros(n, np.uint32), np.zeros(n, np.uint16), np.zeros(n, np.uint32)
+    ext = (500.0, 50.0) if occlusion else (200.0, 200.0)
+    oracle.gen_instances(SceneGenParams(20240, ext[0], ext[1], 0.5, 2.0, 0.05 if occlusion else 0.0, 0.05 if occlusion else 0.0, 0), 0, n,
+                         model, layers, flags, ids)
+    if not occlusion:
+        flags[:] = 0xFFFD
+    if shuffle:
+        ids = np.random.default_rng(1).permutation(n).astype(np.uint32)
+    bounds = [n * i // n_mats for i in range(n_mats + 1)]
+    mats = []
+    for i in range(n_mats):
+        mesh = scenes.simple_mesh(1.7320508 if i % 2 == 0 else 1.74, lods)
+        mats.append(scenes.MaterialDraws([scenes.DrawCommand(mesh, ids[bounds[i]:bounds[i + 1]])]))
+    t = host_tables.build_static_tables(mats)
+    ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos)
+    if depth is not None:
+        pyr, dim, levels = oracle.pyramid_build(depth, min(depth.shape))
+    else:
+        pyr, dim, levels = np.zeros(int(oracle.lib().orc_pyramid_texel_count(64)), np.float32), 64, 7
+    groups = (t.total_entities + 63) // 64
+    ts = []
+    for _ in range(reps):
+        for b in t.bindless:
+            if b is not None and b.ndim == 2:
+                b[:, 1] = 0
+        t0 = time.perf_counter()
+        oracle.cull(ubo, t.cubos, model, layers, flags, pyr, dim, levels, t.bindless, groups, workers, tf)
+        ts.append(time.perf_counter() - t0)
+    ms = float(np.median(ts)) * 1e3
+    return {"ms": ms, "ginst_per_s": n / ms / 1e6, "cores": workers, "kind": "port", "executor": "taskflow" if tf else "std::thread",
+            "sample": f"{n} instances (the full stage), median of {reps}"}
+
+
+def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu=True):
     dev = torch.device("cuda", ctx.device)
     st = torch.cuda.ExternalStream(ctx.stream)
     with torch.cuda.stream(st):
@@ -69,7 +115,8 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush):
                       model, layers, flags, ids)
     ctx.synchronize()
     if not occlusion:
-        t_flags.fill_(-3)  # 0xFFFD: occlusion bit cleared (C1 is frustum + LOD only)
+        with torch.cuda.stream(st):
+            t_flags.fill_(-3)  # 0xFFFD: occlusion bit cleared (C1 is frustum + LOD only)
     cam = scenes.default_camera(z_near=0.1, z_far=far)
     w = World(ctx)
     w.set_entity_buffers(model, layers, flags)
@@ -77,8 +124,9 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush):
     bounds = [n * i // n_mats for i in range(n_mats + 1)]
     keep = []
     if shuffle:
-        perm = torch.randperm(n, device=dev, generator=torch.Generator(device=dev).manual_seed(1)).to(torch.int32)
-        t_ids.copy_(perm)
+        perm = torch.from_numpy(np.random.default_rng(1).permutation(n).astype(np.int32)).to(dev)
+        with torch.cuda.stream(st):
+            t_ids.copy_(perm)
         torch.cuda.synchronize()
     for i in range(n_mats):
         sl = ctx.wrap_tensor(t_ids[bounds[i]:bounds[i + 1]])
@@ -89,6 +137,7 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush):
         w.add_command(m, mesh, sl, bounds[i + 1] - bounds[i])
         keep.append(m)
     pyr = ctx.create_pyramid(min(depth_wh) if depth_wh else 64)
+    depth = None
     if depth_wh:
         depth = scenes.synth_depth(depth_wh[0], depth_wh[1], cam)
         d = ctx.buffer_from_numpy(depth)
@@ -101,46 +150,58 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush):
         w.cull_static(cam.view_proj_cm, cam.pos, pyr)
     ms, cnt = ctx.profile_read(0)
     ctx.set_profiling(False)
-    vis = sum(int(w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:len(lods), 1].sum()) for m in keep if isinstance(m, int))
+    counts = [w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:len(lods), 1] for m in keep if isinstance(m, int)]
+    vis = int(sum(int(c.sum()) for c in counts))
     algo = n * 74 + vis * 4 + 36 * n_mats + 20 * n_mats * len(lods) + (4 * (4 * pyr.dim ** 2 - 1) // 3 if depth_wh else 0)
     k_ms = ms / cnt
-    line("cull", name, k_ms, k_ms, algo, "hbm", {"instances": n, "visible": vis, "ginst_per_s": n / (k_ms * 1e-3) / 1e9,
-                                                 "l2": "flushed between launches" if flush is not None else "inputs exceed L2"})
+    extra = {"instances": n, "visible": vis, "ginst_per_s": n / (k_ms * 1e-3) / 1e9,
+             "l2": "flushed between launches" if flush is not None else "inputs exceed L2"}
+    if cpu:
+        extra["cpu"] = _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats)
     w.destroy()
+    return line("cull", name, k_ms, k_ms, algo, "hbm", extra)
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--reps", type=int, default=20)
-    ap.add_argument("--c3-objects", type=int, default=10_000)
-    ap.add_argument("--only", default="")
-    args = ap.parse_args()
-    only = set(args.only.split(",")) if args.only else None
-    want = lambda s: only is None or s in only
-    torch.cuda.set_device(0)
-    stream = torch.cuda.Stream()
-    ctx = Context(0, stream.cuda_stream)
-    dev = torch.device("cuda", 0)
+def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
+    """Generator of stage dicts (see module docstring)."""
+    want = lambda s: only is None or s in only  # noqa: E731
+    dev = torch.device("cuda", ctx.device)
     with torch.cuda.stream(stream):
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     if want("c1"):
-        cull_case(ctx, 100_000, (math.inf,), False, False, None, args.reps, "C1: 100k instances, 2 materials, 1 LOD, frustum+LOD only", flush)
+        yield cull_case(ctx, 100_000, (math.inf,), False, False, None, reps, "C1: 100k instances, 2 materials, 1 LOD, frustum+LOD only", flush, cpu)
     if want("c2"):
-        cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, False, (3840, 2160), args.reps, "C2: 10M instances, dense ids (TMA path)", None)
-        cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, True, (3840, 2160), args.reps, "C2 variant: 10M instances, shuffled ids (cp.async gather path)", None)
+        yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, False, (3840, 2160), reps, "C2: 10M instances, dense ids (TMA path)", None, False)
+    if want("c2s"):
+        yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, True, (3840, 2160), reps,
+                        "C2 variant: 10M instances, shuffled ids (cp.async gather path)", None, cpu)
 
     if want("pyramid"):
         cam = scenes.default_camera(z_far=1000.0)
         depth = scenes.synth_depth(3840, 2160, cam)
         d = ctx.buffer_from_numpy(depth)
         pyr = ctx.create_pyramid(2160)
-        med, best = timed(ctx, lambda: ctx.build_pyramid(pyr, d, 3840, 2160), args.reps, flush)
+        med, best = timed(ctx, lambda: ctx.build_pyramid(pyr, d, 3840, 2160), reps, flush)
         algo = min(4 * 3840 * 2160, 16 * pyr.dim ** 2) + 4 * (4 * pyr.dim ** 2 - 1) // 3
-        line("pyramid", "3840x2160 depth -> 1024^2, 11 levels, one launch", med, best, algo, "hbm", {"dim": pyr.dim, "levels": pyr.levels})
+        extra = {"dim": pyr.dim, "levels": pyr.levels, "l2": "flushed between launches",
+                 "dram_bytes_expected": 4 * 3840 * 2160 + 2 * 4 * (4 * pyr.dim ** 2 - 1) // 3,
+                 "dram_note": "the 2x2 footprints of the 1024^2 samples touch nearly every 32-B sector of the 33 MB source, and the "
+                              "footprint-min chain (5.6 MB) is written beside the texels"}
+        if cpu:
+            import oracle
+
+            workers = oracle.default_workers()
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                oracle.pyramid_build(depth, 2160, nthreads=workers, taskflow=oracle.LIB_TF.exists())
+                ts.append(time.perf_counter() - t0)
+            extra["cpu"] = {"ms": float(np.median(ts)) * 1e3, "cores": workers, "kind": "port", "sample": "the full stage, median of 3"}
+        yield line("pyramid", "3840x2160 depth -> 1024^2, 11 levels", med, best, algo, "hbm", extra)
 
     if want("c3"):
-        nv, no, nb = 20_000, args.c3_objects, 64
+        nv, no, nb = 20_000, c3_objects, 64
         rng = np.random.default_rng(3)
         dd = scenes.skinning_inputs(rng, nv, 1, nb, coherent_joints=True)
         ins = [ctx.buffer_from_numpy(dd[k]) for k in ("pos", "nrm", "tan", "bit", "uv")]
@@ -152,15 +213,31 @@ def main():
         pose = ctx.wrap_tensor(t_pose)
         outs = [ctx.wrap_tensor(t) for t in t_out]
         ubo = SkinningUBO(no, nv, nb, 0, 0, 0)
-        med, best = timed(ctx, lambda: ctx.skin(ubo, outs, ins, pose, wts), max(args.reps // 2, 5))
+        med, best = timed(ctx, lambda: ctx.skin(ubo, outs, ins, pose, wts), max(reps // 2, 5))
         algo = no * nv * 56 + no * nb * 64 + nv * 88
-        line("skinning", f"C3: {no} objects x {nb} joints x {nv} verts (output {no * nv * 56 / 1e9:.2f} GB)", med, best, algo, "hbm",
-             {"gverts_per_s": no * nv / (med * 1e-3) / 1e9})
+        extra = {"gverts_per_s": no * nv / (med * 1e-3) / 1e9}
+        if cpu:
+            import oracle
+
+            workers = oracle.default_workers()
+            so = min(no, 256)  # bounded sample: 256 characters = 5.1 M vertices
+            h_pose = t_pose[: so * nb].cpu().numpy()
+            h_outs = [np.zeros((so * nv, k), np.float32) for k in (3, 3, 3, 3, 2)]
+            h_ins = [dd[k] for k in ("pos", "nrm", "tan", "bit", "uv")]
+            ts = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                oracle.skin(SkinningUBO(so, nv, nb, 0, 0, 0), h_outs, h_ins, h_pose, dd["weights"], nthreads=workers)
+                ts.append(time.perf_counter() - t0)
+            ms = float(np.median(ts)) * 1e3
+            extra["cpu"] = {"ms": ms, "gverts_per_s": so * nv / ms / 1e6, "cores": workers, "kind": "port",
+                            "sample": f"{so} of the {no} characters ({so * nv} vertices), median of 3"}
+        yield line("skinning", f"C3: {no} objects x {nb} joints x {nv} verts (output {no * nv * 56 / 1e9:.2f} GB)", med, best, algo, "hbm", extra)
         del t_out, outs
         pu = SkinningPrepareUBO(0, 0, 60_000, nv, no, 0, 0)
         ind = ctx.create_buffer(no * 20)
-        med, best = timed(ctx, lambda: ctx.skinned_drawcall_prepare(pu, ind), args.reps)
-        line("skinned_drawcall_prepare", f"{no} objects", med, best, no * 20, "launch latency")
+        med, best = timed(ctx, lambda: ctx.skinned_drawcall_prepare(pu, ind), reps)
+        yield line("skinned_drawcall_prepare", f"{no} objects", med, best, no * 20, "launch latency")
 
     if want("c4"):
         for grid in ((16, 9, 24), (12, 12, 24)):
@@ -170,7 +247,8 @@ def main():
             z = -rng.uniform(0.2, 100.0, size=nl)
             pos = np.stack([rng.uniform(-1, 1, size=nl) * (-z) * 1.03, rng.uniform(-1, 1, size=nl) * (-z) * 0.6, z], 1).astype(np.float32)
             inten = np.exp(rng.uniform(np.log(0.05), np.log(5.0), size=nl)).astype(np.float32)
-            pts = ctx.buffer_from_numpy(scenes.point_lights_bytes(pos, inten))
+            h_pts = scenes.point_lights_bytes(pos, inten)
+            pts = ctx.buffer_from_numpy(h_pts)
             n = grid[0] * grid[1] * grid[2]
             cl = ctx.create_buffer(n * 160)
             u = GridBuildUBO()
@@ -181,17 +259,45 @@ def main():
             a = GridAssignUBO()
             a.pointLightCount, a.spotLightCount = nl, 0
             views = [np.eye(4)] + [scenes.look_at((10.0 * i, 5.0, 3.0), (0.0, 0.0, -30.0)) for i in range(1, 5)]
-            med, best = timed(ctx, lambda: ctx.cluster_build(u, cl), args.reps)
-            line("cluster_build", f"C4 grid {grid}", med, best, n * 24, "launch latency")
+            med, best = timed(ctx, lambda: ctx.cluster_build(u, cl), reps)
+            yield line("cluster_build", f"C4 grid {grid}", med, best, n * 24, "launch latency")
 
             def five_views():
                 for v in views:
                     a.viewMat[:] = [float(x) for x in scenes.colmajor(v)]
                     ctx.cluster_assign(a, cl, pts, None, n)
-            med, best = timed(ctx, five_views, args.reps)
+            med, best = timed(ctx, five_views, reps)
             tests = 5 * n * nl
-            line("cluster_assign", f"C4 grid {grid}, {nl} point lights, 5 views (prepare + assign per view)", med, best,
-                 5 * (nl * 64 + n * 320), "fp32/lsu issue (not HBM)", {"sphere_aabb_tests": tests, "gtests_per_s": tests / (med * 1e-3) / 1e9, "ms_per_view": med / 5})
+            extra = {"sphere_aabb_tests": tests, "gtests_per_s": tests / (med * 1e-3) / 1e9, "ms_per_view": med / 5}
+            if cpu and grid == (16, 9, 24):
+                import oracle
+
+                workers = oracle.default_workers()
+                h_cl = np.zeros(n * 160, np.uint8)
+                oracle.cluster_build(u, h_cl)
+                a.viewMat[:] = [float(x) for x in scenes.colmajor(views[1])]
+                t0 = time.perf_counter()
+                oracle.cluster_assign(a, h_cl, h_pts, None, n, nthreads=workers)
+                ms = (time.perf_counter() - t0) * 1e3
+                extra["cpu"] = {"ms_per_view": ms, "gtests_per_s": n * nl / ms / 1e6, "cores": workers, "kind": "port",
+                                "sample": "one of the five views (the oracle exits a cluster early once it holds 16 lights, like the shader)"}
+            yield line("cluster_assign", f"C4 grid {grid}, {nl} point lights, 5 views (prepare + assign per view)", med, best,
+                       5 * (nl * 64 + n * 320), "fp32 issue + shared-memory bandwidth (not HBM)", extra)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--reps", type=int, default=20)
+    ap.add_argument("--c3-objects", type=int, default=10_000)
+    ap.add_argument("--only", default="")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    only = set(args.only.split(",")) if args.only else None
+    torch.cuda.set_device(0)
+    stream = torch.cuda.Stream()
+    ctx = Context(0, stream.cuda_stream)
+    for d in run_stages(ctx, stream, args.reps, args.c3_objects, only, not args.no_cpu):
+        print(json.dumps(d), flush=True)
     ctx.close()
 
 
