@@ -102,7 +102,11 @@ class DeviceScene:
     """C2 scene resident in HBM on one rank: per-entity arrays generated on the device from
     (seed, global index); 4 materials x 1 mesh collection x 3 LODs over contiguous id ranges."""
 
-    def __init__(self, n: int, rank: int, device: int, first_index: int | None = None):
+    def __init__(self, n: int, rank: int, device: int, first_index: int | None = None, shard_of: tuple[int, int] | None = None):
+        """first_index: global index of this scene's first instance (default rank * n: every rank its own 10 M instances).
+        shard_of = (total, world): this rank's instance-range shard of ONE global scene of `total` instances - material m of
+        the global scene owns global indices [total*m/M, total*(m+1)/M) and every rank holds its contiguous share of each
+        material's list (SURVEY 8e partition A), so an instance keeps its material whatever the world size."""
         import torch
 
         from ravengine_b200 import Context
@@ -120,7 +124,21 @@ class DeviceScene:
         c = self.ctx
         self.model, self.layers = c.wrap_tensor(self.t_model), c.wrap_tensor(self.t_layers)
         self.flags, self.ids = c.wrap_tensor(self.t_flags), c.wrap_tensor(self.t_ids)
-        c.gen_instances(gen_params(C2["seed"]), rank * n if first_index is None else first_index, n, self.model, self.layers, self.flags, self.ids)
+        m_ = C2["materials"]
+        if shard_of is None:
+            c.gen_instances(gen_params(C2["seed"]), rank * n if first_index is None else first_index, n, self.model, self.layers, self.flags, self.ids)
+        else:
+            total, world = shard_of
+            assert total % (m_ * world) == 0 and n == total // world, "the C5 scene splits evenly over materials and ranks"
+            per = total // m_ // world  # instances of one material on one rank
+            for i in range(m_):
+                lo = i * per
+                ids_view = c.wrap_tensor(self.t_ids[lo:lo + per])
+                p_ = gen_params(C2["seed"])
+                p_.id_base = lo  # local entity id = position in this rank's arrays (the generator writes entity arrays at id_base + i)
+                c.gen_instances(p_, (total // m_) * i + rank * per, per, self.model, self.layers, self.flags, ids_view)
+                c.synchronize()
+                ids_view.destroy()
         self.cam, depth = camera_and_depth()
         self.depth_host = depth
         self.t_depth = torch.from_numpy(depth).to(dev)
@@ -357,12 +375,12 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
     # --- C5: 512 camera views sharded by view range, 1 B instances sharded by instance range (fixed totals: strong scaling) ---
     c5 = None
     if not args.no_c5 and n == C2["instances"]:
-        c5 = {"views512": run_c5_views(sc, args, torch, barrier, dist, rank, world_size)}
         cam, depth_host = sc.cam, sc.depth_host
         if ex:
             ex.close()
         sc.release()
         sc = ex = None
+        c5 = {"views512": run_c5_views(args, torch, barrier, dist, rank, world_size, device)}
         c5["instances_1B"] = run_c5_instances(args, torch, barrier, dist, rank, world_size, device)
     else:
         cam, depth_host = sc.cam, sc.depth_host
@@ -513,17 +531,19 @@ def c5_cameras(num_views: int):
                                   target=(grid[i % 512][0], 5.0, grid[i % 512][1] - 1.0)) for i in range(num_views)]
 
 
-def run_c5_views(sc, args, torch, barrier, dist, rank, world_size):
-    """Partition B: `--c5-views` (512) independent camera views over the 10 M-instance C2 scene, every rank holding the whole
-    scene and culling its own view range with the view-batched kernel (no collective). Fixed total work: strong scaling."""
+def run_c5_views(args, torch, barrier, dist, rank, world_size, device):
+    """Partition B: `--c5-views` (512) independent camera views over ONE 10 M-instance scene (the C2 scene of rank 0, held by every
+    rank), each rank culling its share of the views with the view-batched kernel (no collective; views dealt round-robin so
+    the visible work balances). Fixed total work: strong scaling."""
     from ravengine_b200.sharding import ShardedViews
 
+    sc = DeviceScene(C2["instances"], 0, device, first_index=0)
     V = args.c5_views
     cams = c5_cameras(V)
     views = [(c.view_proj_cm, c.pos, 0xFFFFFFFF, False) for c in cams]
     sv = ShardedViews(sc.world, views, [sc.pyr] * V, rank, world_size)
     sc.step()
-    sv.cull_chunk(0)  # warm-up: buffers for 128 views per material
+    sv.cull_chunk(0)  # warm-up: buffers for up to 128 views per material
     barrier()
     reps = 2
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -535,11 +555,11 @@ def run_c5_views(sc, args, torch, barrier, dist, rank, world_size):
     ms = ev0.elapsed_time(ev1) / reps
     vis = 0
     for i in range(len(sv.chunks)):  # visible (instance, view) pairs, outside the timed region
-        g0, g1 = sv.cull_chunk(i)
+        owned = sv.cull_chunk(i)
         sc.ctx.synchronize()
         for m in sc.mats:
             _, ind, lods, _ = sc.world.material_outputs(m)
-            vis += int(ind.download(np.uint32).reshape(-1, 5)[:(g1 - g0) * lods, 1].sum())
+            vis += int(ind.download(np.uint32).reshape(-1, 5)[:len(owned) * lods, 1].astype(np.int64).sum())
     by_rank = [ms]
     if dist:
         t = torch.tensor([ms, float(vis)], device="cuda", dtype=torch.float64)
@@ -547,22 +567,20 @@ def run_c5_views(sc, args, torch, barrier, dist, rank, world_size):
         dist.all_gather_into_tensor(allt.view(-1), t)
         by_rank = [float(x) for x in allt[:, 0].tolist()]
         ms, vis = float(allt[:, 0].max().item()), int(allt[:, 1].sum().item())
-    # release the 128-view buffers (15 GB per rank) before the 1 B-instance scene
-    sc.world.cull_static(sc.vp, sc.cam_pos, sc.pyr)
-    sc.ctx.synchronize()
-    return {"value": sc.n * V / (ms * 1e-3), "unit": "instance-views/s", "views": V, "instances": sc.n, "ms_per_pass": ms,
-            "ms_per_pass_by_rank": by_rank, "views_per_rank": sv.hi - sv.lo, "visible_instance_views": vis, "scaling": "strong",
-            "sharding": "view range per rank (partition B), no collective; every rank holds the whole scene",
-            "check": "visible_instance_views is the same at every N (tests/test_gpu_sharding.py pins the per-rank slices to the one-GPU batch)"}
+    out = {"value": sc.n * V / (ms * 1e-3), "unit": "instance-views/s", "views": V, "instances": sc.n, "ms_per_pass": ms,
+           "ms_per_pass_by_rank": by_rank, "views_per_rank": len(sv.owned), "visible_instance_views": vis, "scaling": "strong",
+           "sharding": "views dealt round-robin over the ranks (partition B), no collective; every rank holds the whole scene",
+           "check": "visible_instance_views is the same at every N (tests/test_gpu_sharding.py pins the per-rank views to the one-GPU batch)"}
+    sc.release()
+    return out
 
 
 def run_c5_instances(args, torch, barrier, dist, rank, world_size, device):
     """Partition A at C5 size: a FIXED scene of `--c5-instances` (1 B) instances split by instance range over the ranks
     (strong scaling; 74 GB of inputs at N = 1), per-slot counts exchanged by the peer-memory kernel."""
     total = args.c5_instances
-    lo, hi = rank * total // world_size, (rank + 1) * total // world_size
-    n = hi - lo
-    sc = DeviceScene(n, 0, device, first_index=lo)
+    n = total // world_size
+    sc = DeviceScene(n, rank, device, shard_of=(total, world_size))
     ex = None
     if world_size > 1:
         from ravengine_b200.sharding import ShardedCull

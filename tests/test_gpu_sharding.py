@@ -174,10 +174,10 @@ def test_sharded_cull_gather_world_size_1(ctx):
     w.destroy()
 
 
-@pytest.mark.parametrize("world", [1, 2, 4])
-def test_view_ranges_per_rank_equal_the_single_gpu_view_batch(ctx, world):
-    """Partition B: rank r culls views [r*V/R, (r+1)*V/R) with ShardedViews; its per-view layouts must equal the slices of
-    one rve_cull_views batch over all views on a single GPU (which tests/test_gpu_views.py pins against the oracle)."""
+@pytest.mark.parametrize("world,policy", [(1, "range"), (2, "strided"), (4, "strided"), (4, "range")])
+def test_views_per_rank_equal_the_single_gpu_view_batch(ctx, world, policy):
+    """Partition B: rank r culls its share of the views with ShardedViews; its per-view layouts must equal the corresponding
+    views of one rve_cull_views batch over all views on a single GPU (which tests/test_gpu_views.py pins against the oracle)."""
     rng, model, layers, flags, cam, depth = _scene()
     lists = _lists(rng, 0, E)
     keep = []
@@ -195,27 +195,27 @@ def test_view_ranges_per_rank_equal_the_single_gpu_view_batch(ctx, world):
     for m in mats:
         ids, ind, lods, ents = w.material_outputs(m)
         full.append((ind.download(np.uint32).reshape(V, lods, 5), ids.download(np.uint32).reshape(V, ents * lods), lods, ents))
-    seen = 0
+    seen = []
     for r in range(world):
-        sv = sharding.ShardedViews(w, views, pyrs, r, world)
-        assert (sv.lo, sv.hi) == sharding.split_views(V, world)[r]
+        sv = sharding.ShardedViews(w, views, pyrs, r, world, policy)
+        assert sv.owned == sharding.assign_views(V, world, policy)[r]
         for i in range(len(sv.chunks)):
-            g0, g1 = sv.cull_chunk(i)
+            owned = sv.cull_chunk(i)
             ctx.synchronize()
             for m, (find, fids, lods, ents) in zip(mats, full):
                 ids, ind, _, _ = w.material_outputs(m)
-                gi = ind.download(np.uint32).reshape(-1, lods, 5)[: g1 - g0]
-                gids = ids.download(np.uint32).reshape(-1, ents * lods)[: g1 - g0]
-                assert np.array_equal(gi, find[g0:g1])
+                gi = ind.download(np.uint32).reshape(-1, lods, 5)[: len(owned)]
+                gids = ids.download(np.uint32).reshape(-1, ents * lods)[: len(owned)]
                 plan_starts = []
                 off = 0
                 for cmd_n, cmd_l in ((len(lists[j]), len(LODS[j])) for j in range(3) if mats[MAT_OF_CMD[j]] == m):
                     plan_starts += [(off + cmd_n * k) for k in range(cmd_l)]
                     off += cmd_n * cmd_l
-                for v in range(g1 - g0):
+                for v, g in enumerate(owned):
+                    assert np.array_equal(gi[v], find[g])
                     for slot, start in enumerate(plan_starts):
                         n = int(gi[v, slot, 1])
-                        assert np.array_equal(np.sort(gids[v, start:start + n]), np.sort(fids[g0 + v, start:start + n]))
-            seen += g1 - g0
-    assert seen == V
+                        assert np.array_equal(np.sort(gids[v, start:start + n]), np.sort(fids[g, start:start + n]))
+            seen += owned
+    assert sorted(seen) == list(range(V))
     w.destroy()

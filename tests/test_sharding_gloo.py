@@ -131,6 +131,8 @@ def test_gather_plan_view_split_and_2d_grid():
     assert g.src_start == (0, 5, 10, 15, 0, 3) and g.dst_start == (0, 10, 20, 30, 0, 7)
     assert g.global_slots == (56, 14)
     assert sharding.split_views(512, 8)[3] == (192, 256) and sharding.split_views(5, 2) == [(0, 2), (2, 5)]
+    assert sharding.assign_views(7, 3) == [[0, 3, 6], [1, 4], [2, 5]] and sharding.assign_views(5, 2, "range") == [[0, 1], [2, 3, 4]]
+    assert sorted(v for r in sharding.assign_views(512, 8) for v in r) == list(range(512))
     grid = sharding.Grid2D(8, 2)  # 2 view groups x 4 instance groups
     assert grid.instance_groups == 4 and grid.coords(5) == (1, 1) and grid.peers(5) == [4, 5, 6, 7]
     assert grid.owned(5, 512, 1_000_000_000) == ((256, 512), (250_000_000, 500_000_000))
