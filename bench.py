@@ -163,11 +163,17 @@ class DeviceScene:
         c.synchronize()
 
     def step(self, before_cull=None):
-        """one pass of the hot path for one view"""
-        self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
+        """one pass of the hot path for one view: pyramid build + table build/upload + indirect re-init + cull, as one encode
+        (rvs_cull_static_with_pyramid); RVE_BENCH_SPLIT_STEP=1 issues the two reference-shaped calls instead"""
+        if os.environ.get("RVE_BENCH_SPLIT_STEP") == "1":
+            self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
+            if before_cull:
+                before_cull()
+            self.world.cull_static(self.vp, self.cam_pos, self.pyr)
+            return
         if before_cull:
             before_cull()
-        self.world.cull_static(self.vp, self.cam_pos, self.pyr)
+        self.world.cull_static_with_pyramid(self.vp, self.cam_pos, self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
 
     def visible_counts(self) -> np.ndarray:
         out = []

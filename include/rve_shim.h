@@ -59,6 +59,13 @@ RVE_API int rvs_material_set_command_entities(rvs_world* w, uint32_t material, u
 /* cullTheRenderData(staticMeshRenderData) — src/RenderEngine_Draw.cpp:1221-1407. */
 RVE_API int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
                             uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid);
+/* generatePyramid for the camera's target (src/RenderEngine_Draw.cpp:2475-2514) and cullTheRenderData for that camera
+ * (:1221-1407) as ONE encode: the pass tables go up first, then the pyramid kernels, then the cull as a programmatic
+ * dependent launch whose table look-ups, tile loads and frustum phase overlap the pyramid's tail (only its Hi-Z batches
+ * wait for the pyramid). Same results as rve_depth_pyramid_build followed by rvs_cull_static. */
+RVE_API int rvs_cull_static_with_pyramid(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
+                                         uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid, rve_buffer depth,
+                                         uint32_t depth_width, uint32_t depth_height);
 /* All views of a frame in one pass: the reference calls cullTheRenderData once per view - main camera,
  * shadow cascades, spot / point shadow faces (src/RenderEngine_Draw.cpp:1769-1866, 1875-1987) - re-walking the scene
  * each time and reusing the material buffers between culls. Here the tables are built once and rve_cull_views tests

@@ -144,6 +144,7 @@ PROTOTYPES.update({
     "rvs_material_add_command": (C.c_int, [VP, u32, u32, u32, u32]),
     "rvs_material_set_command_entities": (C.c_int, [VP, u32, u32, u32, u32]),
     "rvs_cull_static": (C.c_int, [VP, FP, FP, u32, u32, u32, u32]),
+    "rvs_cull_static_with_pyramid": (C.c_int, [VP, FP, FP, u32, u32, u32, u32, u32, u32, u32]),
     "rvs_cull_static_views": (C.c_int, [VP, u32, VP, UP, u32]),
     "rvs_material_outputs": (C.c_int, [VP, u32, UP, UP, UP, UP]),
     "rvs_last_cull_info": (C.c_int, [VP, UP, UP, UP]),

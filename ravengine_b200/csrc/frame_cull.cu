@@ -1,6 +1,7 @@
 // frame_cull.cu — cullTheRenderData (src/RenderEngine_Draw.cpp:1221-1407) and the clustered-light
 // prologue of renderFromPerspective (:928-974), restated over the rve_* C-ABI. Host C++ only.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "frame_internal.h"
@@ -15,8 +16,14 @@ extern "C" {
 
 // cullTheRenderData for `nviews` views at once (nviews == 0: the reference's single pass through rve_cull). With
 // views, every per-material output buffer holds nviews consecutive copies of the single-view layout.
+struct PyramidSource {  // generatePyramid to run between the table upload and the cull (single-view pass only)
+    rve_buffer depth = RVE_BUFFER_INVALID;
+    uint32_t width = 0, height = 0;
+};
+
 static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views, const float view_proj[16], const float cam_pos[3],
-                            uint32_t camera_layers, uint32_t shadow_pass, uint32_t pass_mask, const rve_pyramid* pyramids) {
+                            uint32_t camera_layers, uint32_t shadow_pass, uint32_t pass_mask, const rve_pyramid* pyramids,
+                            const PyramidSource* build = nullptr) {
     rve_ctx* ctx = w->ctx;
     const uint32_t copies = nviews ? nviews : 1;
     // :1223-1229
@@ -38,7 +45,8 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     }
     w->lastNumCubos = globalCubo.numCubos;
     w->lastTotalEntities = totalEntities;
-    if (globalCubo.numCubos == 0) return 0;  // :1245-1247
+    if (globalCubo.numCubos == 0)  // :1245-1247 (the pyramid of the fused encode is still built)
+        return build ? rve_depth_pyramid_build(ctx, pyramids[0], build->depth, build->width, build->height) : 0;
 
     // :1249-1251 cuboBuffer + staging (entries past the written ones are zero here; stale in the reference)
     int rc = realloc_buffer(w, &w->cuboBuffer, &w->cuboBytes, globalCubo.numCubos, sizeof(RveCullingUBOinstance));
@@ -146,6 +154,14 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     }
     // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
     const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));
+    if (build) {
+        // upload -> pyramid build -> pyramid upper -> cull: the build is a plain launch (it starts once the tables are
+        // complete), the cull a programmatic dependent of the pyramid kernels that needs them only for its Hi-Z batches
+        rc = rve_depth_pyramid_build(ctx, pyramids[0], build->depth, build->width, build->height);
+        if (rc) return rc;
+        static const bool late = [] { const char* e = getenv("RVE_CULL_LATE_WAIT"); return !e || atoi(e) != 0; }();
+        if ((cullFlags & kCullTablesPrepared) && late) cullFlags |= kCullLateWait;
+    }
     if (!nviews) return cull_launch(ctx, &globalCubo, 0, &pyramids[0], nullptr, w->cuboBuffer, w->model, w->layers, w->flagsBuf, groups, cullFlags);
     std::vector<RveCullingUBO> ubos(nviews, globalCubo);
     for (uint32_t v = 0; v < nviews; ++v) {
@@ -164,6 +180,13 @@ int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos
                     uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid) {
     if (!w || !view_proj || !cam_pos) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
     return cull_static_impl(w, 0, nullptr, view_proj, cam_pos, camera_layers, shadow_pass, pass_mask, &pyramid);
+}
+
+int rvs_cull_static_with_pyramid(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers, uint32_t shadow_pass,
+                                 uint32_t pass_mask, rve_pyramid pyramid, rve_buffer depth, uint32_t depth_width, uint32_t depth_height) {
+    if (!w || !view_proj || !cam_pos) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    const PyramidSource src{depth, depth_width, depth_height};
+    return cull_static_impl(w, 0, nullptr, view_proj, cam_pos, camera_layers, shadow_pass, pass_mask, &pyramid, &src);
 }
 
 int rvs_cull_static_views(rvs_world* w, uint32_t num_views, const rvs_view* views, const rve_pyramid* pyramids, uint32_t pass_mask) {

@@ -29,6 +29,10 @@ struct PyramidRec {
     rve_buffer footmin = RVE_BUFFER_INVALID;
     bool footmin_valid = true;  // both buffers start zeroed, which is consistent
     bool live = false;
+    // TMA path of rve_depth_pyramid_build: tensor map of the last depth image built from, and the tile geometry for it
+    alignas(64) unsigned char depthMap[128] = {};
+    const void* mapBase = nullptr;
+    uint32_t mapW = 0, mapH = 0, boxW = 0, boxH = 0;
 };
 
 // Programmatic dependent launch: the kernel may become resident while its predecessor on the stream is still running;
@@ -95,6 +99,7 @@ struct rve_ctx {
     void* d_view_stride = nullptr;  // per-CUBO output strides of a view-batched cull
     size_t d_view_stride_cap = 0;
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
+    size_t pyramid_smem_opt_in = 48 * 1024;  // dynamic shared memory pyramid_build_tma_kernel has been opted in for
     bool views_attr_set = false;  // cull_views_kernel's dynamic shared memory opt-in (per device, hence per context)
     uint32_t* d_gather_ticket = nullptr;  // rve_gather_ids_p2p: CTAs-done counter
     // scratch: view-space light records for rve_cluster_assign
@@ -135,9 +140,13 @@ struct HostCuboStaging {
 int cull_host_tables(rve_ctx* ctx, const RveCullingUBOinstance* cubos, uint32_t n, const float* const* lodDistHost, HostCuboStaging* keep,
                      std::vector<RawSegment>* segs);
 constexpr uint32_t kCullTablesPrepared = 1u;  // cull_launch flag: the scratch tables of this CUBO array are already uploaded
+constexpr uint32_t kCullLateWait = 2u;        // ... and were complete before the grids directly ahead of the cull (a pyramid build) started:
+                                              // the cull waits for those only before its first Hi-Z batch
 int cull_launch(rve_ctx* ctx, const RveCullingUBO* ubo, uint32_t num_views, const rve_pyramid* pyramids, const RveViewStride* strides,
                 rve_buffer cubos, rve_buffer model_matrices, rve_buffer render_layers, rve_buffer per_object_flags, uint32_t num_groups_x,
                 uint32_t flags);
+// cull.cu: CUtensorMap (128 bytes, 64-byte aligned, passed as void*) of a row-major f32 image, boxes of boxRows x boxCols
+int make_image_map(const void* base, uint64_t cols, uint64_t rows, uint32_t boxCols, uint32_t boxRows, void* out);
 // (re)derives the footprint-min chain of a pyramid from its texels when they changed since the last derivation
 int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel = 0);
 // marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)

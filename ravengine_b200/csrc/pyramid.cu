@@ -11,6 +11,10 @@
 //
 // Sampler model = oracle.cpp sample_min(): min over the clamped 2x2 bilinear footprint
 // floor(u*W-0.5)+{0,1} (src/RenderEngine.cpp:323-331, reduction mode Minimum).
+#include <cmath>
+
+#include <cuda.h>  // CUtensorMap (type only)
+
 #include "internal.h"
 
 namespace rve {
@@ -60,33 +64,11 @@ __device__ __forceinline__ void reduce_level(const float* lv, uint32_t n_in, flo
     }
 }
 
-__global__ void __launch_bounds__(kPyrThreads)
-pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
-                     uint32_t dim, uint32_t levels, uint32_t tile) {
-    // mip 0 of the tile plus one halo column / row ((tile+1)^2, stride tile+1), then the in-tile levels 1.. back to back
-    __shared__ float s_lv[(kPyrTile + 1) * (kPyrTile + 1) + (kPyrTile * kPyrTile) / 3 + 2];
-
-    // let pyramid_upper_kernel's blocks become resident as this grid's CTAs retire (they wait in griddepcontrol.wait)
-    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    const uint32_t tiles_per_row = dim / tile;
-    const uint32_t tx0 = (blockIdx.x % tiles_per_row) * tile;
-    const uint32_t ty0 = (blockIdx.x / tiles_per_row) * tile;
-
-    // mip 0 — depthpyramidcopy.fsh: texcoord = gl_FragCoord.xy / targetDim (pixel centres). The tile is sampled with
-    // one extra column and row (clamped at the image edge) so that level 0 of the footprint-min chain - 3/4 of it -
-    // is produced here, from shared memory, instead of by a second pass over the texels.
+// Everything a tile does after its (tile+1)^2 mip-0 samples sit in s_lv: level 0 of the footprint-min chain and the
+// in-tile mips 1..log2(tile), each written to the chain and reduced further from shared memory (depthpyramid.csh).
+__device__ __forceinline__ void tile_levels(float* s_lv, float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels,
+                                            uint32_t tile, uint32_t tx0, uint32_t ty0) {
     const uint32_t S = tile + 1;
-    for (uint32_t i = threadIdx.x; i < S * S; i += blockDim.x) {
-        const uint32_t lx = i % S, ly = i / S;
-        uint32_t x = tx0 + lx, y = ty0 + ly;
-        x = x < dim ? x : dim - 1;
-        y = y < dim ? y : dim - 1;
-        const float u = (float(x) + 0.5f) / float(dim);
-        const float v = (float(y) + 0.5f) / float(dim);
-        const float m = sample_min_src(depth, w, h, u, v);
-        s_lv[i] = m;
-        if (lx < tile && ly < tile) pyr[uint64_t(y) * dim + x] = m;
-    }
     __syncthreads();
     {   // footprint-min level 0: F[fy][fx] = min of texels {fx-1,fx} x {fy-1,fy} (clamped), (dim+1)^2 entries
         const uint32_t n1 = dim + 1;
@@ -115,7 +97,129 @@ pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, fl
         n_stride = n_out;
         ++level;
     }
+}
+
+__global__ void __launch_bounds__(kPyrThreads)
+pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
+                     uint32_t dim, uint32_t levels, uint32_t tile) {
+    // mip 0 of the tile plus one halo column / row ((tile+1)^2, stride tile+1), then the in-tile levels 1.. back to back
+    __shared__ float s_lv[(kPyrTile + 1) * (kPyrTile + 1) + (kPyrTile * kPyrTile) / 3 + 2];
+
+    // let pyramid_upper_kernel's blocks become resident as this grid's CTAs retire (they wait in griddepcontrol.wait)
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    const uint32_t tiles_per_row = dim / tile;
+    const uint32_t tx0 = (blockIdx.x % tiles_per_row) * tile;
+    const uint32_t ty0 = (blockIdx.x / tiles_per_row) * tile;
+
+    // mip 0 — depthpyramidcopy.fsh: texcoord = gl_FragCoord.xy / targetDim (pixel centres). The tile is sampled with
+    // one extra column and row (clamped at the image edge) so that level 0 of the footprint-min chain - 3/4 of it -
+    // is produced here, from shared memory, instead of by a second pass over the texels.
+    const uint32_t S = tile + 1;
+    for (uint32_t i = threadIdx.x; i < S * S; i += blockDim.x) {
+        const uint32_t lx = i % S, ly = i / S;
+        uint32_t x = tx0 + lx, y = ty0 + ly;
+        x = x < dim ? x : dim - 1;
+        y = y < dim ? y : dim - 1;
+        const float u = (float(x) + 0.5f) / float(dim);
+        const float v = (float(y) + 0.5f) / float(dim);
+        const float m = sample_min_src(depth, w, h, u, v);
+        s_lv[i] = m;
+        if (lx < tile && ly < tile) pyr[uint64_t(y) * dim + x] = m;
+    }
+    tile_levels(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
     // levels above log2(tile) and the footprint-min levels >= 1: pyramid_upper_kernel
+}
+
+
+namespace pyr {
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return uint32_t(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* b, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "PYR_WAIT:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra PYR_DONE;\n"
+        "bra PYR_WAIT;\n"
+        "PYR_DONE:\n"
+        "}\n" ::"r"(smem_u32(b)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void tma_load_box(void* dst, const void* map, int32_t x, int32_t y, uint64_t* b) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(smem_u32(dst)),
+                 "l"(map), "r"(x), "r"(y), "r"(smem_u32(b))
+                 : "memory");
+}
+}  // namespace pyr
+
+// first texel of the clamped 2x2 footprint of mip-0 sample `t` along an axis of n source texels (sample_min_src's
+// arithmetic); host and device evaluate the same IEEE operations, so the host can size the source box exactly
+__host__ __device__ inline uint32_t footprint_start(uint32_t t, uint32_t dim, uint32_t n) {
+    const float u = (float(t) + 0.5f) / float(dim);
+#ifdef __CUDA_ARCH__
+    const float fx = floorf(__fmaf_rn(u, float(n), -0.5f));
+#else
+    const float fx = floorf(fmaf(u, float(n), -0.5f));
+#endif
+    if (!(fx >= 0.0f)) return 0;
+    if (fx >= float(n - 1)) return n - 1;
+    return uint32_t(fx);
+}
+
+// The same tile work fed by ONE TMA tensor copy per CTA: the source rectangle that the tile's 33 x 33 samples touch
+// (124 x 71 texels for 3840x2160 -> 1024^2) lands in shared memory asynchronously, in full lines, with the copy of every
+// resident CTA in flight at once; CTAs then finish at different times, so the sampling / reduction of one overlaps the
+// DRAM traffic of the others (the LSU-fed kernel moved through load -> five barrier-separated reductions in lock step).
+// The box must start at a 16-byte aligned global address (x a multiple of 4 texels): anything else raises "illegal
+// instruction" on sm_100a (tools/tma_probe.cu); boxes up to 256 x 128 texels in one copy are fine.
+__global__ void __launch_bounds__(kPyrThreads)
+pyramid_build_tma_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
+                         uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH) {
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    __shared__ uint64_t s_bar;
+    float* s_src = reinterpret_cast<float*>(s_dyn);
+    float* s_lv = s_src + boxW * boxH;
+    constexpr uint32_t tile = kPyrTile, S = kPyrTile + 1;
+    const uint32_t tiles_per_row = dim / tile;
+    const uint32_t tx0 = (blockIdx.x % tiles_per_row) * tile;
+    const uint32_t ty0 = (blockIdx.x / tiles_per_row) * tile;
+    // TMA needs a 16-byte aligned global start address: the box begins at the 4-texel boundary at or left of the first footprint
+    const uint32_t sx0 = footprint_start(tx0, dim, w) & ~3u, sy0 = footprint_start(ty0, dim, h);
+    if (threadIdx.x == 0) {
+        pyr::mbar_init(&s_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        pyr::mbar_expect_tx(&s_bar, boxW * boxH * 4u);
+        pyr::tma_load_box(s_src, &depthMap, int32_t(sx0), int32_t(sy0), &s_bar);
+    }
+    __syncthreads();  // the barrier is initialised for everybody
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    pyr::mbar_wait(&s_bar, 0);
+
+    for (uint32_t i = threadIdx.x; i < S * S; i += blockDim.x) {
+        const uint32_t lx = i % S, ly = i / S;
+        uint32_t x = tx0 + lx, y = ty0 + ly;
+        x = x < dim ? x : dim - 1;
+        y = y < dim ? y : dim - 1;
+        const float u = (float(x) + 0.5f) / float(dim);
+        const float v = (float(y) + 0.5f) / float(dim);
+        uint32_t x0, x1, y0, y1;
+        footprint(__fmaf_rn(u, float(w), -0.5f), w, x0, x1);
+        footprint(__fmaf_rn(v, float(h), -0.5f), h, y0, y1);
+        x0 -= sx0, x1 -= sx0, y0 -= sy0, y1 -= sy0;  // box-local (the host sized the box so that these fit)
+        const float a = s_src[y0 * boxW + x0], b = s_src[y0 * boxW + x1];
+        const float c = s_src[y1 * boxW + x0], d = s_src[y1 * boxW + x1];
+        const float m = gmin(gmin(a, b), gmin(c, d));
+        s_lv[i] = m;
+        if (lx < tile && ly < tile) pyr[uint64_t(y) * dim + x] = m;
+    }
+    tile_levels(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
 }
 
 __device__ __forceinline__ float footmin_entry(const float* img, uint32_t n, uint32_t fx, uint32_t fy) {
@@ -129,8 +233,13 @@ __device__ __forceinline__ float footmin_entry(const float* img, uint32_t n, uin
 // one thread per entry. Launched with programmatic stream serialization: everything before griddepcontrol.wait
 // overlaps the tail of pyramid_build_kernel.
 __global__ void __launch_bounds__(kPyrThreads)
-pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels, uint32_t topLevel) {
+pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels, uint32_t topLevel, uint32_t earlyTrigger) {
     __shared__ float s_lv[kPyrTile * kPyrTile + (kPyrTile * kPyrTile) / 3 + 2];
+    // earlyTrigger (RVE_UPPER_TRIGGER=1, off by default): a cull enqueued behind the build becomes resident now and waits for
+    // this grid before its first Hi-Z batch. Measured on B200 (profiles/r02_fused_variants.txt): the persistent cull then
+    // takes 64 us LONGER - its CTAs are placed while pyramid CTAs still hold SM resources and the late ones carry a full
+    // static share - so by default the cull launches when this grid has drained.
+    if (earlyTrigger) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (blockIdx.x == 0) {
         if (topLevel >= levels) return;
         const uint32_t r = dim >> (topLevel - 1);  // <= 32
@@ -302,8 +411,43 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     float* fmPtr = static_cast<float*>(f->ptr);
     {
         ProfScope prof(ctx, RVE_PROF_PYRAMID);
-        pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height, pyrPtr, fmPtr, p->dim,
-                                                                      p->levels, tile);
+        // TMA-fed tiles when the image qualifies (16-byte aligned rows, full 32-texel tiles, a source box that fits)
+        bool tma = false;
+        if (tile == uint32_t(kPyrTile) && (width & 3u) == 0 && (reinterpret_cast<uintptr_t>(d->ptr) & 15) == 0 && !getenv("RVE_PYRAMID_NO_TMA")) {
+            if (p->mapBase != d->ptr || p->mapW != width || p->mapH != height) {
+                // exact extent of the source rectangle a tile's 33 x 33 samples touch, over all tiles (same float math as the kernel)
+                uint32_t bw = 0, bh = 0;
+                for (uint32_t t0 = 0; t0 < p->dim; t0 += tile) {
+                    const uint32_t last = t0 + tile < p->dim ? t0 + tile : p->dim - 1;
+                    const uint32_t ex = footprint_start(last, p->dim, width) + 1, ey = footprint_start(last, p->dim, height) + 1;
+                    const uint32_t x1 = ex < width ? ex : width - 1, y1 = ey < height ? ey : height - 1;
+                    bw = std::max(bw, x1 - (footprint_start(t0, p->dim, width) & ~3u) + 1);  // from the aligned box start
+                    bh = std::max(bh, y1 - footprint_start(t0, p->dim, height) + 1);
+                }
+                bw = (bw + 3u) & ~3u;  // rows of whole 16-byte units
+                if ((bw & 31u) == 0) bw += 4;  // a row pitch of 32 banks would put a footprint's two rows on the same banks
+                p->mapBase = nullptr;
+                if (bw <= 256 && bh <= 256) {
+                    const int rc = make_image_map(d->ptr, width, height, bw, bh, p->depthMap);
+                    if (rc) return rc;
+                    p->mapBase = d->ptr;
+                    p->mapW = width, p->mapH = height, p->boxW = bw, p->boxH = bh;
+                }
+            }
+            const size_t smem = size_t(p->boxW) * p->boxH * 4 + sizeof(float) * ((kPyrTile + 1) * (kPyrTile + 1) + (kPyrTile * kPyrTile) / 3 + 2);
+            if (p->mapBase == d->ptr && smem <= 96 * 1024) {
+                if (smem > ctx->pyramid_smem_opt_in) {
+                    RVE_CUDA(cudaFuncSetAttribute(pyramid_build_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+                    ctx->pyramid_smem_opt_in = smem;
+                }
+                pyramid_build_tma_kernel<<<blocks, kPyrThreads, smem, ctx->stream>>>(*reinterpret_cast<const CUtensorMap*>(p->depthMap), width, height,
+                                                                                   pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH);
+                tma = true;
+            }
+        }
+        if (!tma)
+            pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height, pyrPtr, fmPtr, p->dim,
+                                                                          p->levels, tile);
         ctx->launches++;
         RVE_CUDA(cudaGetLastError());
         if (p->levels > 1) {
@@ -318,7 +462,8 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
             attr.val.programmaticStreamSerializationAllowed = 1;
             cfg.attrs = &attr;
             cfg.numAttrs = 1;
-            RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel));
+            static const uint32_t early = [] { const char* e = getenv("RVE_UPPER_TRIGGER"); return (e && atoi(e) != 0) ? 1u : 0u; }();
+            RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel, early));
             ctx->launches++;
         }
     }

@@ -69,6 +69,14 @@ class World:
         k2, cp = _fp(cam_pos)
         _check(self.lib, self.lib.rvs_cull_static(self.h, vp, cp, layers, 1 if shadow else 0, mask, pyramid.handle))
 
+    def cull_static_with_pyramid(self, view_proj, cam_pos, pyramid: Pyramid, depth: Buffer, width: int, height: int, layers=0xFFFFFFFF,
+                                 shadow=False, mask=MAT_ALL):
+        """rvs_cull_static_with_pyramid: pyramid build + cull as one encode (tables first, cull overlapping the pyramid's tail)."""
+        k1, vp = _fp(view_proj)
+        k2, cp = _fp(cam_pos)
+        _check(self.lib, self.lib.rvs_cull_static_with_pyramid(self.h, vp, cp, layers, 1 if shadow else 0, mask, pyramid.handle, depth.handle,
+                                                               width, height))
+
     def cull_static_views(self, views, pyramids, mask=MAT_ALL):
         """views: list of (view_proj_cm[16], cam_pos[3], camera_layers, shadow) - all of them in ONE launch
         (rvs_cull_static_views); outputs hold len(views) consecutive copies of the single-view layout."""

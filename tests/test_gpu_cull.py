@@ -225,3 +225,30 @@ def test_dynamic_tail_rounds_mixed_paths(ctx, n):
     t, ref = _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=360, nthreads=oracle.default_workers())
     if n == 1_000_003:  # and with the dispatch cut short (defaultcull.csh:166-171 bounds by the dispatch as well)
         _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=360, groups=(n - 70_000) // 64, nthreads=oracle.default_workers())
+
+
+@pytest.mark.parametrize("size", [(3840, 2160), (1920, 1080), (1280, 720), (2560, 1440), (7680, 4320), (1024, 1024), (1028, 4000), (36, 32)])
+def test_pyramid_tma_tiles_equal_the_lsu_tiles_and_the_oracle(ctx, size):
+    """The TMA-fed build (one tensor copy of the tile's source rectangle per CTA) against the LSU-fed kernel and the oracle,
+    at sizes with different source / pyramid ratios (1x .. 7.5x) and edge clamping on both axes."""
+    import os
+
+    w, h = size
+    rng = np.random.default_rng(w + 3 * h)
+    depth = rng.random((h, w), dtype=np.float32)
+    ref, dim, levels = oracle.pyramid_build(depth)
+    d = ctx.buffer_from_numpy(depth)
+    out = []
+    for no_tma in ("", "1"):
+        if no_tma:
+            os.environ["RVE_PYRAMID_NO_TMA"] = "1"
+        else:
+            os.environ.pop("RVE_PYRAMID_NO_TMA", None)
+        pyr = ctx.create_pyramid(min(w, h))
+        for _ in range(2):
+            ctx.build_pyramid(pyr, d, w, h)
+        ctx.synchronize()
+        out.append(pyr.texels.download(np.float32))
+    os.environ.pop("RVE_PYRAMID_NO_TMA", None)
+    np.testing.assert_array_equal(ref, out[0])
+    np.testing.assert_array_equal(ref, out[1])

@@ -364,3 +364,28 @@ def test_frame_encode_equals_the_reference_pass_schedule(ctx):
     assert frame_launches <= 4 + 4 + 2 * 4, frame_launches
     w1.destroy()
     w2.destroy()
+
+
+@pytest.mark.parametrize("n,size", [(6000, (512, 288)), (300_000, (3840, 2160)), (600, (100, 37))])
+def test_fused_pyramid_and_cull_encode_matches_oracle(ctx, n, size):
+    """rvs_cull_static_with_pyramid (tables -> pyramid kernels -> cull overlapping the pyramid's tail, its programmatic
+    dependency wait moved to the first Hi-Z batch) gives the oracle's pyramid and the oracle's cull, frame after frame
+    with a depth buffer that changes between frames."""
+    model, layers, flags, mats = _static_scene(seed=11, n=n)
+    cam = scenes.default_camera(z_far=500.0)
+    wd, hd = size
+    w, mat_ids, keep = _world_from(ctx, model, layers, flags, mats)
+    pyr = ctx.create_pyramid(min(size))
+    t = host_tables.build_static_tables(mats)
+    ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos)
+    for frame in range(3):
+        depth = scenes.synth_depth(wd, hd, cam, n_occluders=30, seed=frame + 1)
+        pyr_h, dim, levels = oracle.pyramid_build(depth, min(size))
+        ref = oracle_cull(t, ubo, model, layers, flags, pyr_h, dim, levels, nthreads=4)
+        d = ctx.buffer_from_numpy(depth)
+        w.cull_static_with_pyramid(cam.view_proj_cm, cam.pos, pyr, d, wd, hd)
+        ctx.synchronize()
+        np.testing.assert_array_equal(pyr_h, pyr.texels.download(np.float32))
+        _compare_static(ctx, w, mat_ids, mats, t, ref)
+        d.destroy()
+    w.destroy()
