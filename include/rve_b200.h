@@ -234,6 +234,9 @@ RVE_API const char* rve_last_error_string(void);
 RVE_API const char* rve_version(void);
 /* number of SMs of the context's device (grid sizing information) */
 RVE_API int rve_ctx_sm_count(rve_ctx* ctx);
+/* CUBO entries dropped by rve_cull since the context was created because a bindless handle did not name a live buffer
+ * (the reference would fault in defaultcull.csh:56-59); synchronises the stream */
+RVE_API uint32_t rve_ctx_bad_cubo_handles(rve_ctx* ctx);
 /* how many kernels this context has launched so far (bench.py "gpu_launches") */
 RVE_API uint64_t rve_ctx_launch_count(rve_ctx* ctx);
 
@@ -333,7 +336,11 @@ RVE_API int rve_depth_pyramid_texels_changed(rve_ctx* ctx, rve_pyramid pyr);
  * DispatchCompute(num_groups_x,1,1, 64,1,1): num_groups_x*64 invocations, those
  * past sum(cubo.numObjects) exit (defaultcull.csh:150-164).
  * Indirect buffers must have been initialised by the caller (instanceCount=0),
- * as the reference does with CopyBufferToBuffer from its staging table. */
+ * as the reference does with CopyBufferToBuffer from its staging table.
+ * The CUBO array may be passed as the reference builds it: `numCubos` counts LODs while one entry per command is written
+ * (src/RenderEngine_Draw.cpp:1238), so its tail is stale staging memory. Entries that cannot be selected (numObjects 0, or
+ * starting past the dispatch) are never resolved; a selectable entry whose handles do not name live buffers is dropped
+ * (treated as numObjects 0) and counted - rve_ctx_bad_cubo_handles() - instead of being followed. */
 RVE_API int rve_cull(rve_ctx* ctx, const RveCullingUBO* ubo, rve_buffer cubos,
                      rve_buffer model_matrices, rve_buffer render_layers,
                      rve_buffer per_object_flags, rve_pyramid pyramid,

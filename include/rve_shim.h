@@ -61,8 +61,9 @@ RVE_API int rvs_cull_static(rvs_world* w, const float view_proj[16], const float
                             uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid);
 /* generatePyramid for the camera's target (src/RenderEngine_Draw.cpp:2475-2514) and cullTheRenderData for that camera
  * (:1221-1407) as ONE encode: the pass tables go up first, then the pyramid kernels, then the cull as a programmatic
- * dependent launch whose table look-ups, tile loads and frustum phase overlap the pyramid's tail (only its Hi-Z batches
- * wait for the pyramid). Same results as rve_depth_pyramid_build followed by rvs_cull_static. */
+ * dependent launch that needs the pyramid only for its Hi-Z batches. (Letting the cull become resident before the pyramid
+ * grids drain is possible - RVE_UPPER_TRIGGER=1 - but measured slower on B200, so by default it launches as they drain.)
+ * Same results as rve_depth_pyramid_build followed by rvs_cull_static. */
 RVE_API int rvs_cull_static_with_pyramid(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
                                          uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid, rve_buffer depth,
                                          uint32_t depth_width, uint32_t depth_height);
@@ -70,7 +71,9 @@ RVE_API int rvs_cull_static_with_pyramid(rvs_world* w, const float view_proj[16]
  * shadow cascades, spot / point shadow faces (src/RenderEngine_Draw.cpp:1769-1866, 1875-1987) - re-walking the scene
  * each time and reusing the material buffers between culls. Here the tables are built once and rve_cull_views tests
  * every instance against all views in one launch; each material's cullingBuffer / indirectBuffer then hold num_views
- * consecutive copies of the single-view layout (view v at v * numEntities*numLODs ids / v * numLODs commands). */
+ * consecutive copies of the single-view layout (view v at v * numEntities*numLODs ids / v * numLODs commands).
+ * Batches of fewer than 8 views run pass by pass (one rve_cull per view, CUBO offsets displaced per view) into the same
+ * layout: below that the batched kernel's fixed cost loses to separate launches (profiles/r01r_views.jsonl). */
 typedef struct rvs_view {
     float view_proj[16];
     float cam_pos[3];

@@ -90,6 +90,7 @@ PROTOTYPES = {
     "rve_version": (C.c_char_p, []),
     "rve_ctx_sm_count": (C.c_int, [VP]),
     "rve_ctx_launch_count": (u64, [VP]),
+    "rve_ctx_bad_cubo_handles": (u32, [VP]),
     "rve_ctx_bind_host_to_device": (C.c_int, [VP, u32, VP]),
     "rve_ctx_set_profiling": (C.c_int, [VP, C.c_int]),
     "rve_ctx_profile_read": (C.c_int, [VP, C.c_int, C.POINTER(C.c_double), C.POINTER(u32)]),

@@ -177,8 +177,8 @@ int rve_ctx_create(int device_ordinal, void* cuda_stream, rve_ctx** out_ctx) {
     }
     ctx->sm_count = prop.multiProcessorCount;
     ctx->l2_bytes = size_t(prop.l2CacheSize);
-    rc = check_cuda(cudaMalloc(reinterpret_cast<void**>(&ctx->d_gather_ticket), sizeof(uint32_t)), "cudaMalloc");
-    if (rc == 0) rc = check_cuda(cudaMemset(ctx->d_gather_ticket, 0, sizeof(uint32_t)), "cudaMemset");
+    rc = check_cuda(cudaMalloc(reinterpret_cast<void**>(&ctx->d_gather_ticket), 2 * sizeof(uint32_t)), "cudaMalloc");
+    if (rc == 0) rc = check_cuda(cudaMemset(ctx->d_gather_ticket, 0, 2 * sizeof(uint32_t)), "cudaMemset");
     if (rc == 0) rc = p2p_preload();
     if (rc) {
         delete ctx;
@@ -293,6 +293,15 @@ int rve_ctx_bind_host_to_device(rve_ctx* ctx, uint32_t flags, rve_host_affinity*
     }
     if (out) *out = info;
     return 0;
+}
+
+uint32_t rve_ctx_bad_cubo_handles(rve_ctx* ctx) {
+    if (!ctx) return 0;
+    DeviceGuard g(ctx->device);
+    uint32_t v = 0;
+    if (cudaMemcpyAsync(&v, ctx->d_gather_ticket + 1, sizeof(v), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess) return 0;
+    cudaStreamSynchronize(ctx->stream);
+    return v;
 }
 
 void* rve_ctx_stream(rve_ctx* ctx) { return ctx ? ctx->stream : nullptr; }

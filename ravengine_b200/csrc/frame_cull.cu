@@ -123,37 +123,65 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
             cubo.cullingBufferOffset += lodsForThisMesh * c.count;
         }
     }
-    // :1367-1375 copy to the cubo buffer
-    uploads.push_back({w->cuboBuffer, 0, cuboStaging.data(), cuboStaging.size() * sizeof(RveCullingUBOinstance)});
-    // The CUBO table was built right here, so the tables the cull derives from it (prefix sums, resolved handles, squared
-    // LOD thresholds: cubo_prepare_kernel) are built on the host too and ride in the same parameter-block upload - one
-    // launch and one dependent kernel less per pass. Entries past the written ones (numCubos counts LODs) are zero:
-    // numObjects 0, never selected. Falls back to the plain path when the block would not fit.
-    uint32_t cullFlags = 0;
-    {
-        std::vector<RawSegment> raw;
-        HostCuboStaging hostTables;
-        bool ok = true;
-        for (const rve_upload_segment& u : uploads) {
-            char* base = static_cast<char*>(rve_buffer_device_ptr(ctx, u.dst));
-            if (!base || u.dst_offset + u.bytes > rve_buffer_size(ctx, u.dst)) ok = false;
-            raw.push_back(RawSegment{base + u.dst_offset, u.src, u.bytes});
-        }
-        static const float kNoLods[4] = {0.f, 0.f, 0.f, 0.f};
-        for (auto& lp : lodHost)
-            if (!lp) lp = kNoLods;
-        if (ok && cull_host_tables(ctx, cuboStaging.data(), globalCubo.numCubos, lodHost.data(), &hostTables, &raw) == 0) {
-            rc = upload_batch_raw(ctx, raw.data(), uint32_t(raw.size()));
-            if (rc == 0) cullFlags = kCullTablesPrepared;
-            else if (rc != RVE_ERR_UNSUPPORTED) return rc;
-        }
-    }
-    if (!cullFlags) {
-        rc = rve_buffer_upload_batch(ctx, uploads.data(), uint32_t(uploads.size()));
-        if (rc) return rc;
-    }
-    // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
+    // Below the measured crossover the view-batched kernel loses to one launch per view (profiles/r01r_views.jsonl: 4 views
+    // 0.65x, 16 views 1.21x; its fixed cost is ~0.3-0.5 ms): small batches run pass by pass - the reference's own schedule -
+    // into the same per-view layout, each view with its CUBO offsets displaced by its copy of the output buffers.
+    const char* batchEnv = getenv("RVS_VIEW_BATCH_MIN");  // development / tests: force either path
+    const uint32_t kBatchMin = batchEnv ? uint32_t(atoi(batchEnv)) : 8u;
+    const bool passByPass = nviews != 0 && nviews < kBatchMin;
     const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));
+    const uint32_t passes = passByPass ? nviews : 1u;
+    uint32_t cullFlags = 0;
+    for (uint32_t pass = 0; pass < passes; ++pass) {
+        std::vector<RveCullingUBOinstance> cuboPass = cuboStaging;
+        if (passByPass)
+            for (uint32_t c = 0; c < cuboIdx; ++c) {
+                cuboPass[c].indirectBufferOffset += pass * strides[c].indirect_stride;
+                cuboPass[c].cullingBufferOffset += pass * strides[c].culling_stride;
+            }
+        std::vector<rve_upload_segment> ups;
+        if (pass == 0) ups = uploads;  // the indirect-init tables (all views' copies) go up once
+        // :1367-1375 copy to the cubo buffer
+        ups.push_back({w->cuboBuffer, 0, cuboPass.data(), cuboPass.size() * sizeof(RveCullingUBOinstance)});
+        // The CUBO table was built right here, so the tables the cull derives from it (prefix sums, resolved handles, squared
+        // LOD thresholds: cubo_prepare_kernel) are built on the host too and ride in the same parameter-block upload - one
+        // launch and one dependent kernel less per pass. Entries past the written ones (numCubos counts LODs) are zero:
+        // numObjects 0, never selected. Falls back to the plain path when the block would not fit.
+        cullFlags = 0;
+        {
+            std::vector<RawSegment> raw;
+            HostCuboStaging hostTables;
+            bool ok = true;
+            for (const rve_upload_segment& u : ups) {
+                char* base = static_cast<char*>(rve_buffer_device_ptr(ctx, u.dst));
+                if (!base || u.dst_offset + u.bytes > rve_buffer_size(ctx, u.dst)) ok = false;
+                raw.push_back(RawSegment{base + u.dst_offset, u.src, u.bytes});
+            }
+            static const float kNoLods[4] = {0.f, 0.f, 0.f, 0.f};
+            for (auto& lp : lodHost)
+                if (!lp) lp = kNoLods;
+            if (ok && cull_host_tables(ctx, cuboPass.data(), globalCubo.numCubos, lodHost.data(), &hostTables, &raw) == 0) {
+                rc = upload_batch_raw(ctx, raw.data(), uint32_t(raw.size()));
+                if (rc == 0) cullFlags = kCullTablesPrepared;
+                else if (rc != RVE_ERR_UNSUPPORTED) return rc;
+            }
+        }
+        if (!cullFlags) {
+            rc = rve_buffer_upload_batch(ctx, ups.data(), uint32_t(ups.size()));
+            if (rc) return rc;
+        }
+        if (passByPass) {
+            RveCullingUBO u = globalCubo;
+            std::memcpy(u.viewProj, views[pass].view_proj, 64);
+            std::memcpy(u.camPos, views[pass].cam_pos, 12);
+            u.cameraRenderLayers = views[pass].camera_layers;
+            u.singleInstanceModeAndShadowMode = views[pass].shadow_pass ? RVE_CULL_SHADOW_MODE : 0u;
+            rc = cull_launch(ctx, &u, 0, &pyramids[pass], nullptr, w->cuboBuffer, w->model, w->layers, w->flagsBuf, groups, cullFlags);
+            if (rc) return rc;
+        }
+    }
+    if (passByPass) return 0;
+    // :1377-1403 bind + DispatchCompute(ceil(totalEntities / 64), 1, 1, 64, 1, 1)
     if (build) {
         // upload -> pyramid build -> pyramid upper -> cull: the build is a plain launch (it starts once the tables are
         // complete), the cull a programmatic dependent of the pyramid kernels that needs them only for its Hi-Z batches

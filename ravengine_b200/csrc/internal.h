@@ -101,7 +101,7 @@ struct rve_ctx {
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
     size_t pyramid_smem_opt_in = 48 * 1024;  // dynamic shared memory pyramid_build_tma_kernel has been opted in for
     bool views_attr_set = false;  // cull_views_kernel's dynamic shared memory opt-in (per device, hence per context)
-    uint32_t* d_gather_ticket = nullptr;  // rve_gather_ids_p2p: CTAs-done counter
+    uint32_t* d_gather_ticket = nullptr;  // [0] rve_gather_ids_p2p: CTAs-done counter; [1] CUBO entries with bad handles (cubo_prepare_kernel)
     // scratch: view-space light records for rve_cluster_assign
     float4* d_lights = nullptr;
     size_t d_lights_cap = 0;

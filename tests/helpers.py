@@ -32,7 +32,8 @@ def device_cull(ctx, tables, ubo, model, layers, flags, depth=None, pyr_width=10
     cubos = tables.cubos.copy()
     for f in ("idOutputBufferBindlessHandle", "entityIDInputBufferBindlessHandle", "indirectOutputBufferBindlessHandle",
               "lodDistanceBufferBindlessHandle"):
-        cubos[f] = np.array([dev[int(h)].bindless for h in tables.cubos[f]], dtype=np.uint32)
+        # oracle handle -> device handle; values that name no oracle buffer (a dirty table tail) are passed through as they are
+        cubos[f] = np.array([dev[int(h)].bindless if int(h) < len(dev) else int(h) for h in tables.cubos[f]], dtype=np.uint32)
     d_cubos = ctx.buffer_from_numpy(cubos.view(np.uint8))
     d_model, d_layers, d_flags = ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(layers), ctx.buffer_from_numpy(flags)
     pyr = ctx.create_pyramid(pyr_width)

@@ -252,3 +252,42 @@ def test_pyramid_tma_tiles_equal_the_lsu_tiles_and_the_oracle(ctx, size):
     os.environ.pop("RVE_PYRAMID_NO_TMA", None)
     np.testing.assert_array_equal(ref, out[0])
     np.testing.assert_array_equal(ref, out[1])
+
+
+def test_garbage_in_the_unwritten_cubo_tail_is_never_followed(ctx):
+    """The reference writes one CUBO per command but sets numCubos to the LOD count (src/RenderEngine_Draw.cpp:1238): the
+    tail of its cuboBuffer is recycled staging memory. rve_cull must give the same result with garbage there - stale
+    handles past the table, handles of destroyed buffers, huge numObjects past the dispatch - and must drop (and count) a
+    selectable entry whose handles are dead instead of following them."""
+    model, layers, flags, mats = _scene(30_080, 3, n_mats=2, lods=(0.0, 40.0, 120.0))  # a multiple of 64: the dispatch ends where the entities end
+    cam = scenes.default_camera()
+    t = host_tables.build_static_tables(mats)
+    assert t.num_cubos == 6 and len(t.cubos) == 6  # 2 written entries, 4 zero tail entries in the oracle's table
+    ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos)
+    depth = scenes.synth_depth(320, 180, cam, n_occluders=10)
+    pyr, dim, levels = oracle.pyramid_build(depth, 180)
+    ref = oracle_cull(t, ubo, model, layers, flags, pyr, dim, levels, nthreads=2)
+    import dataclasses
+
+    dirty = t.cubos.copy()
+    rng = np.random.default_rng(0)
+    for i in range(2, 6):  # never selectable: empty, or starting past the dispatch (= total entities)
+        dirty[i]["numObjects"] = 0 if i == 2 else int(rng.integers(1, 1 << 30))
+        dirty[i]["numLODs"] = int(rng.integers(2, 5))
+        dirty[i]["radius"] = float(rng.random())
+        for j, f in enumerate(("idOutputBufferBindlessHandle", "entityIDInputBufferBindlessHandle", "indirectOutputBufferBindlessHandle",
+                               "lodDistanceBufferBindlessHandle")):
+            dirty[i][f] = [0xFFFFFFF0, 123456, 0x00FFFFFF, 0x7FFFFFFF][(i + j) % 4]
+    before = ctx.lib.rve_ctx_bad_cubo_handles(ctx.h)
+    got, _ = device_cull(ctx, dataclasses.replace(t, cubos=dirty), ubo, model, layers, flags, depth=depth, pyr_width=180)
+    compare_cull_outputs(t, mats, ref, got)
+    assert ctx.lib.rve_ctx_bad_cubo_handles(ctx.h) == before  # nothing selectable was dropped
+    # a SELECTABLE entry with a dead handle: dropped and counted; the other command's result is unchanged
+    broken = t.cubos.copy()
+    broken[1]["lodDistanceBufferBindlessHandle"] = 0xFFFFFF00
+    got3, _ = device_cull(ctx, dataclasses.replace(t, cubos=broken), ubo, model, layers, flags, depth=depth, pyr_width=180)
+    assert ctx.lib.rve_ctx_bad_cubo_handles(ctx.h) == before + 1
+    h0 = int(t.cubos[0]["indirectOutputBufferBindlessHandle"])
+    np.testing.assert_array_equal(got3[h0], ref[h0])
+    h1 = int(t.cubos[1]["indirectOutputBufferBindlessHandle"])
+    assert not got3[h1][:, 1].any()  # the broken command drew nothing

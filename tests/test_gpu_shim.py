@@ -247,9 +247,12 @@ def test_bin_lights_matches_oracle(ctx):
     w.destroy()
 
 
-def test_cull_static_views_matches_per_view_culls(ctx):
-    """rvs_cull_static_views: all views of a frame (main camera + shadow passes) in one launch == the reference's
-    one cullTheRenderData per view; view v occupies the v-th copy of every material's output layout."""
+@pytest.mark.parametrize("batch_min", ["1", "100"])
+def test_cull_static_views_matches_per_view_culls(ctx, batch_min, monkeypatch):
+    """rvs_cull_static_views: all views of a frame (main camera + shadow passes) == the reference's one cullTheRenderData
+    per view; view v occupies the v-th copy of every material's output layout. Both schedules: one view-batched launch
+    (RVS_VIEW_BATCH_MIN=1) and the pass-by-pass fallback small batches take by default (forced with 100)."""
+    monkeypatch.setenv("RVS_VIEW_BATCH_MIN", batch_min)
     model, layers, flags, mats = _static_scene(seed=9)
     t = host_tables.build_static_tables(mats)
     cams = [scenes.default_camera(z_far=500.0), scenes.default_camera(z_far=500.0, eye=(80, 20, 60), target=(0, 0, 0)),
@@ -267,9 +270,11 @@ def test_cull_static_views_matches_per_view_culls(ctx):
         pyrs.append(p)
         views.append((cam.view_proj_cm, cam.pos, 0xFFFFFFFF, sh))
     w, mat_ids, keep = _world_from(ctx, model, layers, flags, mats)
+    launches = ctx.launch_count
     for _ in range(2):
         w.cull_static_views(views, pyrs)
     ctx.synchronize()
+    assert ctx.launch_count - launches == (2 * 2 if batch_min == "1" else 2 * 2 * len(views))  # upload + cull, per batch or per view
     ci = 0
     for mat, m in zip(mat_ids, mats):
         cull_b, ind_b, lods, ents = w.material_outputs(mat)
@@ -360,13 +365,15 @@ def test_frame_encode_equals_the_reference_pass_schedule(ctx):
         assert ref[:, 6].max() > 0 and ref[:, 7].max() > 0
         live = np.concatenate([np.arange(16)[None, :] < ref[:, 6:7], np.arange(16)[None, :] < ref[:, 7:8]], axis=1)
         np.testing.assert_array_equal(got[:, 8:][live], ref[:, 8:][live])
-    # 2 pyramid builds x 2 launches + (table upload + prepare + cull) + 2 x (cluster build + assign prepare/assign)
-    assert frame_launches <= 4 + 4 + 2 * 4, frame_launches
+    # 2 pyramid builds x 2 launches + the culls + 2 x (cluster build + assign prepare/assign); the culls are one (table upload,
+    # cull) pair per view below 8 views (pass-by-pass fallback), one view-batched launch + upload from 8 views on
+    nv = len(views_all)
+    assert frame_launches <= 4 + (2 * nv if nv < 8 else 4) + 2 * 4, frame_launches
     w1.destroy()
     w2.destroy()
 
 
-@pytest.mark.parametrize("n,size", [(6000, (512, 288)), (300_000, (3840, 2160)), (600, (100, 37))])
+@pytest.mark.parametrize("n,size", [(6000, (512, 288)), (300_000, (3840, 2160)), (6000, (100, 37))])
 def test_fused_pyramid_and_cull_encode_matches_oracle(ctx, n, size):
     """rvs_cull_static_with_pyramid (tables -> pyramid kernels -> cull overlapping the pyramid's tail, its programmatic
     dependency wait moved to the first Hi-Z batch) gives the oracle's pyramid and the oracle's cull, frame after frame
