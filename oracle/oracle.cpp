@@ -75,16 +75,37 @@ inline vec3 operator-(vec3 a, vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}
 inline vec3 operator*(vec3 a, float s) { return {a.x * s, a.y * s, a.z * s}; }
 inline vec4 operator*(vec4 a, float s) { return {a.x * s, a.y * s, a.z * s, a.w * s}; }
 inline vec4 operator+(vec4 a, vec4 b) { return {a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w}; }
+// ORC_VARIANT_* build the OTHER evaluations GLSL allows (tools/contract_sensitivity.py counts how many decisions of a
+// scene depend on the choice; the product is only ever compared with the default build):
+//   ORC_VARIANT_NO_FMA        a*b+c rounded twice everywhere        ORC_VARIANT_DOT_REVERSED  dot accumulates from the last component
+//   ORC_VARIANT_TRUE_DIV      vector / scalar divides each component (no reciprocal-multiply)
+#if defined(ORC_VARIANT_NO_FMA)
+inline float fma_(float a, float b, float c) {
+    volatile float p = a * b;  // rounded product
+    return p + c;
+}
+#else
 inline float fma_(float a, float b, float c) { return __builtin_fmaf(a, b, c); }
+#endif
 inline float rcp_(float s) { return 1.0f / s; }
+#if defined(ORC_VARIANT_DOT_REVERSED)
+inline float dot(vec3 a, vec3 b) { return fma_(a.x, b.x, fma_(a.y, b.y, a.z * b.z)); }
+inline float dot(vec4 a, vec4 b) { return fma_(a.x, b.x, fma_(a.y, b.y, fma_(a.z, b.z, a.w * b.w))); }
+#else
 inline float dot(vec3 a, vec3 b) { return fma_(a.z, b.z, fma_(a.y, b.y, a.x * b.x)); }
 inline float dot(vec4 a, vec4 b) { return fma_(a.w, b.w, fma_(a.z, b.z, fma_(a.y, b.y, a.x * b.x))); }
+#endif
 inline float length(vec3 v) { return std::sqrt(dot(v, v)); }
 inline vec3 fma3(vec3 a, float s, vec3 c) { return {fma_(a.x, s, c.x), fma_(a.y, s, c.y), fma_(a.z, s, c.z)}; }
 inline vec4 fma4(vec4 a, float s, vec4 c) { return {fma_(a.x, s, c.x), fma_(a.y, s, c.y), fma_(a.z, s, c.z), fma_(a.w, s, c.w)}; }
 // vector / scalar = vector * (1/scalar)
+#if defined(ORC_VARIANT_TRUE_DIV)
+inline vec3 vdiv(vec3 v, float s) { return {v.x / s, v.y / s, v.z / s}; }
+inline vec4 vdiv(vec4 v, float s) { return {v.x / s, v.y / s, v.z / s, v.w / s}; }
+#else
 inline vec3 vdiv(vec3 v, float s) { return v * rcp_(s); }
 inline vec4 vdiv(vec4 v, float s) { return v * rcp_(s); }
+#endif
 inline vec3 vmin(vec3 a, vec3 b) { return {gmin(a.x, b.x), gmin(a.y, b.y), gmin(a.z, b.z)}; }
 inline vec3 vmax(vec3 a, vec3 b) { return {gmax(a.x, b.x), gmax(a.y, b.y), gmax(a.z, b.z)}; }
 
