@@ -228,6 +228,7 @@ int rvs_cull_static_views(rvs_world* w, uint32_t num_views, const rvs_view* view
 static int bin_lights_into(rvs_world* w, rve_buffer* buf, size_t* bytes, const float inv_proj[16], const float view_mat[16],
                            const uint32_t grid_size[3], const uint32_t screen_dim[2], float z_near, float z_far, rve_buffer point_lights,
                            uint32_t point_light_count, rve_buffer spot_lights, uint32_t spot_light_count) {
+    RVE_PROFILE_FN_N("RenderFromPerspective: cluster lights");
     const uint64_t n = uint64_t(grid_size[0]) * grid_size[1] * grid_size[2];
     RVE_REQUIRE(n > 0 && n < 0x7FFFFFFFull, "bad cluster grid");
     // lightClusterBuffer: numClusters * sizeof(Cluster) (src/RenderEngine.cpp:839-845)
@@ -277,6 +278,7 @@ int rvs_bin_lights(rvs_world* w, const float inv_proj[16], const float view_mat[
 // lights are binned once per camera into that camera's own cluster buffer.
 int rvs_frame_encode(rvs_world* w, const rvs_frame_desc* f) {
     if (!w || !f) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_PROFILE_FN_N("RenderEngine::Draw");
     RVE_REQUIRE(f->num_cameras == 0 || f->cameras, "cameras is null");
     RVE_REQUIRE(f->num_shadow_views == 0 || (f->shadow_views && f->shadow_pyramids), "shadow views / pyramids are null");
     const uint32_t nviews = f->num_cameras + f->num_shadow_views;

@@ -159,6 +159,7 @@ int rvs_prepare_skeletal_culling_buffer(rvs_world* w) {
 
 int rvs_cull_skeletal(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
                       uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid) {
+    RVE_PROFILE_FN_N("Cull Skeletal Meshes");
     if (!w || !view_proj || !cam_pos) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
     rve_ctx* ctx = w->ctx;
     // :1069-1123 reset the indirect buffers from a host staging table

@@ -1,6 +1,7 @@
 // internal.h — shared by the translation units of librve_b200.so (not part of the ABI)
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>  // header-only NVTX 3: a no-op unless a profiler is attached
 
 #include <cstdint>
 #include <mutex>
@@ -169,6 +170,18 @@ struct ProfScope {
         if (b) cudaEventRecord(b, ctx->stream);
     }
 };
+
+// Host-side profiler zone around an encode block, named like the reference's Tracy zones for the same block
+// (RVE_PROFILE_FN_N, include/RavEngine/Profile.hpp:5-30; zones at src/RenderEngine_Draw.cpp:100,578,911,1068,1222,2477).
+struct ProfileZone {
+    explicit ProfileZone(const char* name) { nvtxRangePushA(name); }
+    ~ProfileZone() { nvtxRangePop(); }
+    ProfileZone(const ProfileZone&) = delete;
+    ProfileZone& operator=(const ProfileZone&) = delete;
+};
+#define RVE_ZONE_CAT2(a, b) a##b
+#define RVE_ZONE_CAT(a, b) RVE_ZONE_CAT2(a, b)
+#define RVE_PROFILE_FN_N(name) rve::ProfileZone RVE_ZONE_CAT(rve_zone_, __LINE__)(name)
 
 struct DeviceGuard {
     int prev = -1;

@@ -393,6 +393,7 @@ int rve_depth_pyramid_info(rve_ctx* ctx, rve_pyramid pyr, uint32_t* dim, uint32_
 
 int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height) {
     if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    RVE_PROFILE_FN_N("generatePyramid");
     DeviceGuard g(ctx->device);
     PyramidRec* p = get_pyramid(ctx, pyr);
     if (!p) return RVE_ERR_BAD_HANDLE;

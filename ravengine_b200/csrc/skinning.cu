@@ -30,6 +30,7 @@ struct SkinParams {
     const float* __restrict__ inUV;
     const float4* __restrict__ pose;  // mat4 = 4 x float4 columns
     const RveVertexJointBinding* __restrict__ weights;
+    uint32_t groupBase;     // first object group of this launch (grid.y is capped at 65535 groups per launch)
     uint32_t group;         // objects per CTA
     uint32_t vertsPerCta;   // multiple of kSkinThreads
 };
@@ -60,7 +61,7 @@ __device__ __forceinline__ float4 fma4(float4 acc, float w, float4 m) {
 template <bool kSharedPalette>
 __global__ void __launch_bounds__(kSkinThreads) skin_kernel(const SkinParams p) {
     extern __shared__ float4 s_pal[];  // [group][numBones][3] row blocks
-    const uint32_t obj0 = blockIdx.y * p.group;
+    const uint32_t obj0 = (p.groupBase + blockIdx.y) * p.group;
     const uint32_t nObj = min(p.group, p.u.numObjects - obj0);
     const uint32_t v0 = blockIdx.x * p.vertsPerCta;
 
@@ -159,6 +160,7 @@ extern "C" {
 int rve_skin(rve_ctx* ctx, const RveSkinningUBO* ubo, const rve_buffer out_streams[5], const rve_buffer in_streams[5],
              rve_buffer pose, rve_buffer weights) {
     if (!ctx || !ubo || !out_streams || !in_streams) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_PROFILE_FN_N("Enc Pose Skinned Meshes");
     DeviceGuard g(ctx->device);
     if (ubo->numObjects == 0 || ubo->numVertices == 0) return 0;
     BufferRec* o[5];
@@ -210,19 +212,18 @@ int rve_skin(rve_ctx* ctx, const RveSkinningUBO* ubo, const rve_buffer out_strea
     // vertices per CTA: enough CTAs to fill the machine, few enough to amortise the palette staging
     uint32_t vertsPerCta = kSkinThreads * 4;
     p.vertsPerCta = vertsPerCta;
-    dim3 grid((ubo->numVertices + vertsPerCta - 1) / vertsPerCta, (ubo->numObjects + group - 1) / group);
-    RVE_REQUIRE(grid.y <= 65535, "too many object groups for one dispatch (numObjects/8 > 65535)");
+    const uint32_t groups = (ubo->numObjects + group - 1) / group;
     ProfScope prof(ctx, RVE_PROF_SKIN);
-    if (shared) {
-        const size_t smem = palBytes * group;
-        if (smem > 48 * 1024)
-            RVE_CUDA(cudaFuncSetAttribute(skin_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-        skin_kernel<true><<<grid, kSkinThreads, smem, ctx->stream>>>(p);
-    } else {
-        skin_kernel<false><<<grid, kSkinThreads, 0, ctx->stream>>>(p);
+    const size_t smem = shared ? palBytes * group : 0;
+    if (smem > 48 * 1024) RVE_CUDA(cudaFuncSetAttribute(skin_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    for (uint32_t g0 = 0; g0 < groups; g0 += 65535u) {  // grid.y holds 65535 groups: more objects take further launches
+        p.groupBase = g0;
+        const dim3 grid((ubo->numVertices + vertsPerCta - 1) / vertsPerCta, groups - g0 < 65535u ? groups - g0 : 65535u);
+        if (shared) skin_kernel<true><<<grid, kSkinThreads, smem, ctx->stream>>>(p);
+        else skin_kernel<false><<<grid, kSkinThreads, 0, ctx->stream>>>(p);
+        ctx->launches++;
+        RVE_CUDA(cudaGetLastError());
     }
-    ctx->launches++;
-    RVE_CUDA(cudaGetLastError());
     return 0;
 }
 

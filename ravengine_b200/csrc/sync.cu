@@ -591,6 +591,7 @@ static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st) {
 // BufferedVRAMStructureBase::EncodeSync (src/BufferedVRAMVector.cpp:27-144)
 int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_rows, rvs_sync_stats* stats) {
     if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
+    RVE_PROFILE_FN_N("EncodeSync");
     RVE_REQUIRE(mode <= RVS_SYNC_FULL_PULL, "unknown sync mode");
     rve_ctx* ctx = v->ctx;
     DeviceGuard g(ctx->device);

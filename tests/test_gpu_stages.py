@@ -49,6 +49,15 @@ def test_skinning_matches_oracle(ctx, shape):
         assert np.abs(g[sl] - r64[sl]).max() / scale <= 1e-5
 
 
+def test_skinning_more_object_groups_than_one_grid_holds(ctx):
+    """600 000 objects x 1 bone = 75 000 groups of 8: past grid.y's 65 535, so rve_skin takes a second launch."""
+    launches = ctx.launch_count
+    ubo, ins, pose, w, ref, got = _skin_case(ctx, 3, 600_000, 1, seed=2)
+    assert ctx.launch_count - launches == 2
+    for r, g in zip(ref, got):
+        np.testing.assert_array_equal(r, g)
+
+
 def test_skinning_identity_palette_is_exact_copy(ctx):
     ubo, ins, pose, w, ref, got = _skin_case(ctx, 500, 4, 16, seed=5, identity=True)
     for o in range(4):
