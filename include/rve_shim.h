@@ -208,6 +208,31 @@ RVE_API uint64_t rvs_vector_pulled_rows(rvs_vector* v);
 /* (begin, end) pairs of the last sync, for inspection; returns their number */
 RVE_API uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max_pairs);
 
+/* ---- entity lists: BufferedVRAMSparseSet<entity_id_t, entity_id_t> (include/RavEngine/World.hpp:342,355: MDIICommand::command::
+ * entities; include/RavEngine/SparseSet.hpp:6-104; include/RavEngine/BufferedVRAMVector.hpp:129-170). The dense array is what the
+ * cull reads (entityIDInputBufferBindlessHandle); erase is a swap-remove, so a live engine's lists are dense runs with
+ * out-of-order entries wherever something was removed. ---- */
+typedef struct rvs_sparse_set rvs_sparse_set;
+RVE_API int rvs_sparse_set_create(rve_ctx* ctx, rvs_sparse_set** out);
+RVE_API int rvs_sparse_set_destroy(rvs_sparse_set* s);
+/* Emplace(sparse_index, value): no-op when the index has a record; the new dense element is flagged modified */
+RVE_API int rvs_sparse_set_emplace(rvs_sparse_set* s, uint32_t sparse_index, uint32_t value);
+/* EraseAtSparseIndex: the last dense element moves into the hole (flagged modified there); an unknown index is an error
+ * (the reference asserts) */
+RVE_API int rvs_sparse_set_erase(rvs_sparse_set* s, uint32_t sparse_index);
+RVE_API int rvs_sparse_set_emplace_many(rvs_sparse_set* s, const uint32_t* sparse_indices, const uint32_t* values, uint32_t n);
+RVE_API int rvs_sparse_set_erase_many(rvs_sparse_set* s, const uint32_t* sparse_indices, uint32_t n);
+RVE_API int rvs_sparse_set_has(rvs_sparse_set* s, uint32_t sparse_index);
+RVE_API uint32_t rvs_sparse_set_dense_size(rvs_sparse_set* s);
+/* GetDenseData() / GetReverseMap(): host views, valid until the next mutation */
+RVE_API const uint32_t* rvs_sparse_set_dense(rvs_sparse_set* s);
+RVE_API const uint32_t* rvs_sparse_set_reverse_map(rvs_sparse_set* s);
+/* the dense array as a BufferedVRAMVector stand-in (rvs_vector_encode_sync / rvs_vector_private_buffer) */
+RVE_API rvs_vector* rvs_sparse_set_vector(rvs_sparse_set* s);
+/* MDIICommand::command with its entities held in a sparse set: every cull over the world first syncs the set (EncodeSync,
+ * packed mode) and reads its private buffer and DenseSize() - rvs_material_add_command with a live list */
+RVE_API int rvs_material_add_command_set(rvs_world* w, uint32_t material, uint32_t mesh, rvs_sparse_set* entities);
+
 /* ---- shared vertex arena + .rvem container: the data formats on the input side of skinning ---- */
 /* RenderEngine's shared mesh buffers (src/RenderEngine_Allocate.cpp:168-177): positions, normals, tangents, bitangents
  * (12 B), uv0, lightmapUV (8 B), u32 indices; offsets and sizes are ELEMENTS (include/RavEngine/MeshAllocation.hpp:27-52). */

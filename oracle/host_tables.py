@@ -198,3 +198,47 @@ def sync_ranges(tracking: np.ndarray, max_gap: int = 5) -> np.ndarray:
     if gap != 0:
         out.append((begin, n))
     return np.array(out, np.uint32).reshape(-1, 2)
+
+
+class SparseSetRef:
+    """Restatement of UnorderedSparseSetGenericContainer + BufferedVRAMSparseSet's flag writes
+    (include/RavEngine/SparseSet.hpp:22-47, include/RavEngine/BufferedVRAMVector.hpp:132-163) for index = value = u32:
+    dense array with swap-remove erase, sparse -> dense map, reverse map, one modification flag per dense element."""
+
+    INVALID = 0xFFFFFFFF
+
+    def __init__(self):
+        self.dense: list[int] = []
+        self.sparse: list[int] = [self.INVALID]  # sparse_set{ default_index }
+        self.reverse: list[int] = []
+        self.flags: list[bool] = []  # syncTrackingBuffer
+
+    def has(self, i: int) -> bool:
+        return i < len(self.sparse) and self.sparse[i] != self.INVALID
+
+    def emplace(self, i: int, value: int) -> None:
+        if self.has(i):
+            return
+        self.dense.append(value)
+        self.reverse.append(i)
+        if i >= len(self.sparse):
+            want = (i + 1 + 1) // 2 * 2  # closest_multiple_of<int>(i + 1, 2)
+            self.sparse += [self.INVALID] * (want - len(self.sparse))
+        self.sparse[i] = len(self.dense) - 1
+        if len(self.dense) > len(self.flags):  # ResizeIfNeeded: new flags start true
+            self.flags += [True] * (len(self.dense) - len(self.flags))
+        self.flags[self.sparse[i]] = True
+
+    def erase(self, i: int) -> None:
+        assert self.has(i)
+        d = self.sparse[i]
+        self.flags[d] = True
+        last = len(self.dense) - 1
+        self.dense[d] = self.dense[last]  # unordered_vector::erase: swap with the last element, pop
+        self.dense.pop()
+        if d < len(self.dense):
+            owner = self.reverse[-1]
+            self.sparse[owner] = d
+            self.reverse[d] = self.reverse[-1]
+        self.reverse.pop()
+        self.sparse[i] = self.INVALID

@@ -213,6 +213,21 @@ PROTOTYPES.update({
     "rvs_vector_last_ranges": (u32, [VP, UP, u32]),
 })
 
+PROTOTYPES.update({
+    "rvs_sparse_set_create": (C.c_int, [VP, C.POINTER(VP)]),
+    "rvs_sparse_set_destroy": (C.c_int, [VP]),
+    "rvs_sparse_set_emplace": (C.c_int, [VP, u32, u32]),
+    "rvs_sparse_set_erase": (C.c_int, [VP, u32]),
+    "rvs_sparse_set_emplace_many": (C.c_int, [VP, VP, VP, u32]),
+    "rvs_sparse_set_erase_many": (C.c_int, [VP, VP, u32]),
+    "rvs_sparse_set_has": (C.c_int, [VP, u32]),
+    "rvs_sparse_set_dense_size": (u32, [VP]),
+    "rvs_sparse_set_dense": (VP, [VP]),
+    "rvs_sparse_set_reverse_map": (VP, [VP]),
+    "rvs_sparse_set_vector": (VP, [VP]),
+    "rvs_material_add_command_set": (C.c_int, [VP, u32, u32, VP]),
+})
+
 _lib = None
 
 

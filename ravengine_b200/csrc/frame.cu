@@ -109,6 +109,15 @@ int rvs_material_add_command(rvs_world* w, uint32_t material, uint32_t mesh, rve
     return 0;
 }
 
+int rvs_material_add_command_set(rvs_world* w, uint32_t material, uint32_t mesh, rvs_sparse_set* entities) {
+    if (!w || !entities) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(material < w->materials.size() && mesh < w->meshes.size(), "bad material / mesh index");
+    Command c{mesh, RVE_BUFFER_INVALID, 0};
+    c.set = entities;
+    w->materials[material].commands.push_back(c);
+    return 0;
+}
+
 int rvs_material_set_command_entities(rvs_world* w, uint32_t material, uint32_t command_index, rve_buffer entity_ids,
                                       uint32_t entity_count) {
     if (!w) return set_error(RVE_ERR_INVALID_ARGUMENT, "world is null");

@@ -34,6 +34,17 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     globalCubo.cameraRenderLayers = nviews ? views[0].camera_layers : camera_layers;
     globalCubo.singleInstanceModeAndShadowMode = (nviews ? views[0].shadow_pass : shadow_pass) ? RVE_CULL_SHADOW_MODE : 0u;
 
+    // entity lists held in sparse sets: EncodeSync first (the reference syncs its BufferedVRAM structures ahead of the encode),
+    // then the command reads the set's private buffer and DenseSize()
+    for (auto& m : w->materials)
+        for (auto& c : m.commands)
+            if (c.set) {
+                rvs_vector* v = rvs_sparse_set_vector(c.set);
+                const int src = rvs_vector_encode_sync(v, RVS_SYNC_PACKED, 256, nullptr);
+                if (src) return src;
+                c.entityIds = rvs_vector_private_buffer(v);
+                c.count = rvs_sparse_set_dense_size(c.set);
+            }
     // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch
     uint32_t totalEntities = 0;
     for (auto& m : w->materials) {

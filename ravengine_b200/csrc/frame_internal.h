@@ -25,6 +25,7 @@ struct Command {
     uint32_t mesh;
     rve_buffer entityIds;
     uint32_t count;
+    rvs_sparse_set* set = nullptr;  // when set: entityIds / count follow the set (synced before every cull)
 };
 
 // MDICommandBase + MDIICommand (World.hpp:334-349)

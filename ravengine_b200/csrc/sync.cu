@@ -777,3 +777,105 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// BufferedVRAMSparseSet<entity_id_t, entity_id_t> stand-in: the per-command entity lists the cull walks
+// (include/RavEngine/World.hpp:342,355; include/RavEngine/SparseSet.hpp:6-104; include/RavEngine/BufferedVRAMVector.hpp:129-170).
+// Dense array = an rvs_vector of u32 (pinned host block + flags + private buffer), sparse -> dense map and reverse map
+// on the host. Erase is a swap-remove: the last dense element moves into the hole, which is the only flag it sets.
+// ---------------------------------------------------------------------------------------------------------
+struct rvs_sparse_set {
+    rvs_vector* dense = nullptr;
+    std::vector<uint32_t> sparse{0xFFFFFFFFu};  // sparse_set{ default_index } (SparseSet.hpp:15)
+    std::vector<uint32_t> reverse;              // reverse_map: dense index -> sparse index
+};
+
+extern "C" {
+
+int rvs_sparse_set_create(rve_ctx* ctx, rvs_sparse_set** out) {
+    if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    auto* s = new rvs_sparse_set();
+    const int rc = rvs_vector_create(ctx, 4, 0, &s->dense);
+    if (rc) {
+        delete s;
+        return rc;
+    }
+    *out = s;
+    return 0;
+}
+
+int rvs_sparse_set_destroy(rvs_sparse_set* s) {
+    if (!s) return 0;
+    rvs_vector_destroy(s->dense);
+    delete s;
+    return 0;
+}
+
+uint32_t rvs_sparse_set_dense_size(rvs_sparse_set* s) { return s ? rvs_vector_size(s->dense) : 0; }
+
+int rvs_sparse_set_has(rvs_sparse_set* s, uint32_t sparse_index) {
+    return s && sparse_index < s->sparse.size() && s->sparse[sparse_index] != 0xFFFFFFFFu;  // HasForSparseIndex (SparseSet.hpp:58-60)
+}
+
+// Emplace (SparseSet.hpp:22-32 + BufferedVRAMVector.hpp:153-158): no-op when the index already has a record
+int rvs_sparse_set_emplace(rvs_sparse_set* s, uint32_t sparse_index, uint32_t value) {
+    if (!s) return set_error(RVE_ERR_INVALID_ARGUMENT, "null set");
+    RVE_REQUIRE(sparse_index != 0xFFFFFFFFu, "0xFFFFFFFF is the invalid index");
+    if (rvs_sparse_set_has(s, sparse_index)) return 0;
+    const uint32_t n = rvs_vector_size(s->dense);
+    int rc = rvs_vector_resize(s->dense, n + 1);  // the new element starts out modified
+    if (rc) return rc;
+    rc = rvs_vector_set(s->dense, n, &value);
+    if (rc) return rc;
+    s->reverse.push_back(sparse_index);
+    if (sparse_index >= s->sparse.size()) {
+        const size_t want = (size_t(sparse_index) + 1 + 1) / 2 * 2;  // closest_multiple_of<int>(sparse_index + 1, 2)
+        s->sparse.resize(want, 0xFFFFFFFFu);
+    }
+    s->sparse[sparse_index] = n;
+    return 0;
+}
+
+// EraseAtSparseIndex (BufferedVRAMVector.hpp:160-163 + SparseSet.hpp:34-47): swap-remove
+int rvs_sparse_set_erase(rvs_sparse_set* s, uint32_t sparse_index) {
+    if (!s) return set_error(RVE_ERR_INVALID_ARGUMENT, "null set");
+    RVE_REQUIRE(rvs_sparse_set_has(s, sparse_index), "no record for this sparse index");  // the reference asserts
+    const uint32_t denseidx = s->sparse[sparse_index];
+    const uint32_t last = rvs_vector_size(s->dense) - 1;
+    auto* host = static_cast<uint32_t*>(rvs_vector_host(s->dense));
+    if (denseidx < last) {  // a move happens: the last element lands in the hole
+        const uint32_t moved = host[last];
+        const int rc = rvs_vector_set(s->dense, denseidx, &moved);  // marks the dense index modified
+        if (rc) return rc;
+        const uint32_t ownerOfMoved = s->reverse.back();
+        s->sparse[ownerOfMoved] = denseidx;
+        s->reverse[denseidx] = ownerOfMoved;
+    }
+    s->reverse.pop_back();
+    s->sparse[sparse_index] = 0xFFFFFFFFu;
+    return rvs_vector_resize(s->dense, last);
+}
+
+int rvs_sparse_set_emplace_many(rvs_sparse_set* s, const uint32_t* sparse_indices, const uint32_t* values, uint32_t n) {
+    if (!s || (n && (!sparse_indices || !values))) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    for (uint32_t i = 0; i < n; ++i) {
+        const int rc = rvs_sparse_set_emplace(s, sparse_indices[i], values[i]);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+int rvs_sparse_set_erase_many(rvs_sparse_set* s, const uint32_t* sparse_indices, uint32_t n) {
+    if (!s || (n && !sparse_indices)) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    for (uint32_t i = 0; i < n; ++i) {
+        const int rc = rvs_sparse_set_erase(s, sparse_indices[i]);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+const uint32_t* rvs_sparse_set_dense(rvs_sparse_set* s) { return s ? static_cast<const uint32_t*>(rvs_vector_host(s->dense)) : nullptr; }
+const uint32_t* rvs_sparse_set_reverse_map(rvs_sparse_set* s) { return s && !s->reverse.empty() ? s->reverse.data() : nullptr; }
+rvs_vector* rvs_sparse_set_vector(rvs_sparse_set* s) { return s ? s->dense : nullptr; }
+
+}  // extern "C"

@@ -77,3 +77,62 @@ class BufferedVRAMVector:
         if self.h:
             self.ctx.lib.rvs_vector_destroy(self.h)
             self.h = None
+
+
+class SparseSet:
+    """BufferedVRAMSparseSet<entity_id_t, entity_id_t> mirror (include/RavEngine/SparseSet.hpp:6-104,
+    include/RavEngine/BufferedVRAMVector.hpp:129-170): a command's entity list. Marshalling only (csrc/sync.cu)."""
+
+    def __init__(self, ctx: Context):
+        self.ctx = ctx
+        h = C.c_void_p()
+        _check(ctx.lib, ctx.lib.rvs_sparse_set_create(ctx.h, C.byref(h)))
+        self.h = h
+
+    def __len__(self) -> int:
+        return self.ctx.lib.rvs_sparse_set_dense_size(self.h)
+
+    def emplace(self, sparse_index: int, value: int | None = None) -> None:
+        _check(self.ctx.lib, self.ctx.lib.rvs_sparse_set_emplace(self.h, sparse_index, sparse_index if value is None else value))
+
+    def erase(self, sparse_index: int) -> None:
+        _check(self.ctx.lib, self.ctx.lib.rvs_sparse_set_erase(self.h, sparse_index))
+
+    def emplace_many(self, sparse_indices: np.ndarray, values: np.ndarray | None = None) -> None:
+        idx = np.ascontiguousarray(sparse_indices, dtype=np.uint32)
+        val = idx if values is None else np.ascontiguousarray(values, dtype=np.uint32)
+        _check(self.ctx.lib, self.ctx.lib.rvs_sparse_set_emplace_many(self.h, idx.ctypes.data, val.ctypes.data, len(idx)))
+
+    def erase_many(self, sparse_indices: np.ndarray) -> None:
+        idx = np.ascontiguousarray(sparse_indices, dtype=np.uint32)
+        _check(self.ctx.lib, self.ctx.lib.rvs_sparse_set_erase_many(self.h, idx.ctypes.data, len(idx)))
+
+    def has(self, sparse_index: int) -> bool:
+        return bool(self.ctx.lib.rvs_sparse_set_has(self.h, sparse_index))
+
+    def dense(self) -> np.ndarray:
+        n = len(self)
+        if n == 0:
+            return np.empty(0, np.uint32)
+        return np.ctypeslib.as_array((C.c_uint32 * n).from_address(self.ctx.lib.rvs_sparse_set_dense(self.h))).copy()
+
+    def reverse_map(self) -> np.ndarray:
+        n = len(self)
+        if n == 0:
+            return np.empty(0, np.uint32)
+        return np.ctypeslib.as_array((C.c_uint32 * n).from_address(self.ctx.lib.rvs_sparse_set_reverse_map(self.h))).copy()
+
+    def encode_sync(self, mode: int = SYNC_PACKED, direct_min_rows: int = 256) -> _abi.SyncStats:
+        st = _abi.SyncStats()
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_encode_sync(self.ctx.lib.rvs_sparse_set_vector(self.h), mode, direct_min_rows, C.byref(st)))
+        return st
+
+    @property
+    def private_buffer(self) -> Buffer:
+        h = self.ctx.lib.rvs_vector_private_buffer(self.ctx.lib.rvs_sparse_set_vector(self.h))
+        return Buffer(self.ctx, h, self.ctx.lib.rve_buffer_size(self.ctx.h, h))
+
+    def destroy(self) -> None:
+        if self.h:
+            self.ctx.lib.rvs_sparse_set_destroy(self.h)
+            self.h = None

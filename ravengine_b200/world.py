@@ -61,6 +61,11 @@ class World:
     def add_command(self, material: int, mesh: int, entity_ids: Buffer, count: int):
         _check(self.lib, self.lib.rvs_material_add_command(self.h, material, mesh, entity_ids.handle, count))
 
+    def add_command_set(self, material: int, mesh: int, entities) -> None:
+        """rvs_material_add_command_set: the command's entity list is a vram_vector.SparseSet, synced before every cull"""
+        _check(self.lib, self.lib.rvs_material_add_command_set(self.h, material, mesh, entities.h))
+        self._keep.append(entities)
+
     def set_command_entities(self, material: int, command: int, entity_ids: Buffer, count: int):
         _check(self.lib, self.lib.rvs_material_set_command_entities(self.h, material, command, entity_ids.handle, count))
 

@@ -1,0 +1,108 @@
+"""Entity lists as the engine mutates them: the shim's BufferedVRAMSparseSet stand-in against a restatement
+of the reference containers over random emplace / erase sequences, its private buffer after every sync, and a cull over a
+churned list against the oracle."""
+import math
+
+import numpy as np
+import pytest
+
+import oracle
+from oracle import host_tables
+from oracle.host_tables import SparseSetRef
+from ravengine_b200 import scenes
+from ravengine_b200.vram_vector import SYNC_PACKED, SYNC_PULL, SYNC_RANGES, SparseSet
+from ravengine_b200.world import World
+from tests.helpers import make_ubo, oracle_cull
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("mode", [SYNC_RANGES, SYNC_PACKED, SYNC_PULL])
+def test_sparse_set_matches_the_restated_reference_containers(ctx, mode):
+    rng = np.random.default_rng(mode + 10)
+    s, ref = SparseSet(ctx), SparseSetRef()
+    universe = 5000
+    for step in range(30):
+        alive = np.array([i for i in range(universe) if ref.has(i)], np.uint32)
+        n_erase = int(rng.integers(0, max(len(alive) // 3, 1) + 1)) if len(alive) else 0
+        erase = rng.choice(alive, size=n_erase, replace=False) if n_erase else np.empty(0, np.uint32)
+        add = rng.choice(universe, size=int(rng.integers(1, 400)), replace=False).astype(np.uint32)
+        for i in erase:
+            ref.erase(int(i))
+        for i in add:  # emplace of an existing index is a no-op on both sides
+            ref.emplace(int(i), int(i) ^ 0x5A5A)
+        if step % 2:
+            s.erase_many(erase)
+            s.emplace_many(add, add ^ 0x5A5A)
+        else:
+            for i in erase:
+                s.erase(int(i))
+            for i in add:
+                s.emplace(int(i), int(i) ^ 0x5A5A)
+        assert len(s) == len(ref.dense)
+        assert np.array_equal(s.dense(), np.array(ref.dense, np.uint32))
+        assert np.array_equal(s.reverse_map(), np.array(ref.reverse, np.uint32))
+        for probe in rng.integers(0, universe + 50, size=20):
+            assert s.has(int(probe)) == ref.has(int(probe))
+        s.encode_sync(mode, 16)
+        ctx.synchronize()
+        got = s.private_buffer.download(np.uint32)[: len(s)]
+        assert np.array_equal(got, np.array(ref.dense, np.uint32))
+    with pytest.raises(Exception):
+        s.erase(universe + 7)  # the reference asserts
+    s.destroy()
+
+
+def test_cull_over_churned_entity_lists_matches_oracle(ctx):
+    """Two commands whose entity lists went through swap-remove churn (10 % erased, re-inserted at the end): the cull walks
+    the sets' private buffers; compared with the oracle over the same dense arrays, twice (a second churn between frames)."""
+    rng = np.random.default_rng(4)
+    n = 40_000
+    model = scenes.random_transforms(rng, n, 200.0, 60.0)
+    layers = np.full(n, 0xFFFFFFFF, np.uint32)
+    flags = np.full(n, 0xFFFF, np.uint16)
+    cam = scenes.default_camera(z_far=500.0)
+    depth = scenes.synth_depth(512, 288, cam, n_occluders=30)
+    pyr_h, dim, levels = oracle.pyramid_build(depth, 288)
+    w = World(ctx)
+    keep = [ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(layers), ctx.buffer_from_numpy(flags)]
+    w.set_entity_buffers(*keep)
+    meshes = [scenes.simple_mesh(1.5, (0.0, 30.0, 90.0)), scenes.simple_mesh(2.5, (math.inf,), base=7000)]
+    sets, mats = [], []
+    for k, mesh in enumerate(meshes):
+        s = SparseSet(ctx)
+        s.emplace_many(np.arange(k * n // 2, (k + 1) * n // 2, dtype=np.uint32))
+        sets.append(s)
+        mat = w.material()
+        mid = w.mesh_collection(mesh.radius, mesh.lod_distances, [l.index_count for l in mesh.lods], [l.index_start for l in mesh.lods],
+                                [l.base_vertex for l in mesh.lods])
+        w.add_command_set(mat, mid, s)
+        mats.append(mat)
+    pyr = ctx.create_pyramid(288)
+    ctx.build_pyramid(pyr, ctx.buffer_from_numpy(depth), 512, 288)
+    for frame in range(2):
+        for k, s in enumerate(sets):  # churn: erase 10 % at random, re-insert them (they land at the end, out of order)
+            alive = s.dense()
+            gone = rng.choice(alive, size=len(alive) // 10, replace=False)
+            s.erase_many(gone)
+            s.emplace_many(rng.permutation(gone))
+        lists = [s.dense() for s in sets]
+        assert not np.array_equal(lists[0], np.sort(lists[0]))
+        omats = [scenes.MaterialDraws([scenes.DrawCommand(mesh, l)]) for mesh, l in zip(meshes, lists)]
+        t = host_tables.build_static_tables(omats)
+        ref = oracle_cull(t, make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos), model, layers, flags, pyr_h, dim, levels, nthreads=4)
+        w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+        ctx.synchronize()
+        ci = 0
+        for mat, m in zip(mats, omats):
+            cull_b, ind_b, lods, ents = w.material_outputs(mat)
+            cb = t.cubos[ci]
+            r_ind, r_ids = ref[int(cb["indirectOutputBufferBindlessHandle"])], ref[int(cb["idOutputBufferBindlessHandle"])]
+            g_ind, g_ids = ind_b.download(np.uint32).reshape(-1, 5)[:lods], cull_b.download(np.uint32)[: lods * ents]
+            np.testing.assert_array_equal(g_ind, r_ind)
+            for x, y in zip(host_tables.sorted_slices(r_ind, r_ids, t.cubos, range(ci, ci + 1)), host_tables.sorted_slices(g_ind, g_ids, t.cubos, range(ci, ci + 1))):
+                np.testing.assert_array_equal(x, y)
+            ci += 1
+    w.destroy()
+    for s in sets:
+        s.destroy()

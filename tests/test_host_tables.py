@@ -132,3 +132,26 @@ def test_gen_instances_is_pure_function_of_index():
     assert np.all(m[:, 15] == 1.0) and np.all(np.abs(m[:, 12]) <= 500.0) and np.all(np.abs(m[:, 13]) <= 50.0)
     s = np.linalg.norm(m[:, 0:3], axis=1)
     assert s.min() >= 0.49 and s.max() <= 2.01
+
+
+def test_restated_sparse_set_known_answers():
+    """SparseSetRef (the checker of tests/test_gpu_sparse_set.py) on a hand-worked sequence: swap-remove moves the last
+    dense element into the hole, reverse map and sparse map follow, flags mark the touched dense slots
+    (include/RavEngine/SparseSet.hpp:22-47, include/RavEngine/BufferedVRAMVector.hpp:153-163)."""
+    from oracle.host_tables import SparseSetRef
+
+    s = SparseSetRef()
+    for i in (5, 2, 9, 7):
+        s.emplace(i, i * 10)
+    assert s.dense == [50, 20, 90, 70] and s.reverse == [5, 2, 9, 7]
+    assert len(s.sparse) == 10 and s.sparse[5] == 0 and s.sparse[7] == 3 and s.sparse[0] == SparseSetRef.INVALID
+    s.flags = [False] * 4
+    s.erase(2)  # dense slot 1 <- last element (70, owner 7)
+    assert s.dense == [50, 70, 90] and s.reverse == [5, 7, 9] and s.sparse[7] == 1 and not s.has(2)
+    assert s.flags == [False, True, False, False]
+    s.erase(9)  # the last element itself: no move
+    assert s.dense == [50, 70] and s.reverse == [5, 7] and s.flags[2]
+    s.emplace(5, 123)  # already present: no-op
+    assert s.dense == [50, 70]
+    s.emplace(2, 21)
+    assert s.dense == [50, 70, 21] and s.sparse[2] == 2 and s.flags[2]

@@ -59,7 +59,7 @@ def line(stage, workload, ms_med, ms_best, algo_bytes, bound, extra=None):
     return d
 
 
-def _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats, reps=3):
+def _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats, reps=3, ids_override=None):
     """the same cull on the host cores: oracle (CPU restatement, TEST INFRASTRUCTURE) with the engine's worker count"""
     import oracle
     from oracle import host_tables
@@ -74,7 +74,9 @@ def _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats, reps=3):
                          model, layers, flags, ids)
     if not occlusion:
         flags[:] = 0xFFFD
-    if shuffle:
+    if ids_override is not None:
+        ids = ids_override
+    elif shuffle:
         ids = np.random.default_rng(1).permutation(n).astype(np.uint32)
     bounds = [n * i // n_mats for i in range(n_mats + 1)]
     mats = []
@@ -123,8 +125,26 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu
     n_mats = 4 if occlusion else 2
     bounds = [n * i // n_mats for i in range(n_mats + 1)]
     keep = []
-    if shuffle:
-        perm = torch.from_numpy(np.random.default_rng(1).permutation(n).astype(np.int32)).to(dev)
+    host_ids = None
+    if shuffle == "churn":
+        # every material's list goes through the engine's own mutation: 10 % of its entities erased at random (swap-remove)
+        # and inserted again - BufferedVRAMSparseSet semantics through the shim (csrc/sync.cu)
+        from ravengine_b200.vram_vector import SparseSet
+
+        rng = np.random.default_rng(1)
+        host_ids = np.arange(n, dtype=np.uint32)
+        for i in range(n_mats):
+            ss = SparseSet(ctx)
+            ss.emplace_many(host_ids[bounds[i]:bounds[i + 1]])
+            gone = rng.choice(host_ids[bounds[i]:bounds[i + 1]], size=(bounds[i + 1] - bounds[i]) // 10, replace=False)
+            ss.erase_many(gone)
+            ss.emplace_many(rng.permutation(gone))
+            host_ids[bounds[i]:bounds[i + 1]] = ss.dense()
+            ss.destroy()
+    elif shuffle:
+        host_ids = np.random.default_rng(1).permutation(n).astype(np.uint32)
+    if host_ids is not None:
+        perm = torch.from_numpy(host_ids.view(np.int32)).to(dev)
         with torch.cuda.stream(st):
             t_ids.copy_(perm)
         torch.cuda.synchronize()
@@ -156,8 +176,11 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu
     k_ms = ms / cnt
     extra = {"instances": n, "visible": vis, "ginst_per_s": n / (k_ms * 1e-3) / 1e9,
              "l2": "flushed between launches" if flush is not None else "inputs exceed L2"}
+    if host_ids is not None:
+        runs = np.flatnonzero(np.diff(host_ids.astype(np.int64)) != 1).size + 1
+        extra["id_runs"] = int(runs)  # maximal runs of consecutive ids in the lists (1 per material when untouched)
     if cpu:
-        extra["cpu"] = _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats)
+        extra["cpu"] = _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats, ids_override=host_ids)
     w.destroy()
     return line("cull", name, k_ms, k_ms, algo, "hbm", extra)
 
@@ -176,6 +199,10 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
     if want("c2s"):
         yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, True, (3840, 2160), reps,
                         "C2 variant: 10M instances, shuffled ids (cp.async gather path)", None, cpu)
+
+    if want("c2churn"):
+        yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, "churn", (3840, 2160), reps,
+                        "C2 variant: 10M instances after 10 % erase / re-insert churn of every entity list (swap-remove)", None, cpu)
 
     if want("pyramid"):
         cam = scenes.default_camera(z_far=1000.0)
