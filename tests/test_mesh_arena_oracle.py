@@ -115,3 +115,51 @@ def test_rvem_rejects_what_the_reference_rejects():
     short = bytes(head) + s[0].tobytes() + idx.tobytes()
     info = parse_rvem(short)
     assert info.off_normals == 2 ** 64 - 1 and info.off_indices == 16 + 60 and oma.parse_rvem(short)["normals"] is None
+
+
+@pytest.mark.parametrize("name", ["static", "lightmap", "skinned"])
+def test_rvem_bytes_pinned_by_the_reference_writer(name):
+    """PINNED: tests/golden/rvem.npz holds the bytes the reference mesh compiler's own SerializeMeshPart
+    (tools/rvemc/rvemc.cpp:233-292, compiled unchanged into oracle/_ref/libref_rvem.so) wrote for three assets. The Python
+    writer must produce the same bytes, and rvs_rvem_parse (C-ABI) / the oracle parser must read the reference's file."""
+    from pathlib import Path
+
+    g = np.load(Path(__file__).parent / "golden" / "rvem.npz")
+    blob = g[f"{name}_bytes"].tobytes()
+    streams = [g[f"{name}_{k}"] for k in ("positions", "normals", "tangents", "bitangents", "uv0")]
+    idx = g[f"{name}_indices"]
+    lm = g[f"{name}_lightmap"] if f"{name}_lightmap" in g else None
+    wts = g[f"{name}_weights"].view(WEIGHT).reshape(-1, 4) if f"{name}_weights" in g else None
+    assert write_rvem(*streams, idx, lightmap_uvs=lm, weights=wts) == blob
+    ref = oma.parse_rvem(blob)
+    info = parse_rvem(blob)
+    nv, ni = len(streams[0]), len(idx)
+    assert (info.num_vertices, info.num_indices) == (nv, ni) == (ref["num_vertices"], ref["num_indices"])
+    raw = np.frombuffer(blob, np.uint8)
+    for k, (off, arr) in enumerate(zip((info.off_positions, info.off_normals, info.off_tangents, info.off_bitangents, info.off_uv0), streams)):
+        assert np.array_equal(raw[off:off + arr.nbytes].view(np.float32).reshape(arr.shape), arr)
+        assert np.array_equal(ref[oma.ORDER[k]], arr)
+    assert np.array_equal(raw[info.off_indices:info.off_indices + 4 * ni].view(np.uint32), idx)
+    assert info.mesh_bytes == info.off_indices + 4 * ni
+    if lm is not None:
+        assert np.array_equal(raw[info.off_lightmap_uv:info.off_lightmap_uv + lm.nbytes].view(np.float32).reshape(lm.shape), lm)
+    else:
+        assert info.off_lightmap_uv == 2 ** 64 - 1
+    if wts is not None:
+        assert info.off_weights == info.mesh_bytes and info.weights_bytes == 32 * nv == len(blob) - info.mesh_bytes
+        assert np.array_equal(raw[info.off_weights:].view(np.uint32), wts.view(np.uint32).reshape(-1))
+    else:
+        assert info.off_weights == 2 ** 64 - 1 and len(blob) == info.mesh_bytes
+
+
+def test_rvem_live_reference_writer_when_built():
+    """where oracle/_ref/libref_rvem.so exists (this container), the committed fixture is what it writes today"""
+    from pathlib import Path
+
+    from tests.golden import make_golden_rvem as mg
+
+    if not (Path(mg.ROOT) / "oracle" / "_ref" / "libref_rvem.so").exists():
+        pytest.skip("reference writer not built here")
+    g = np.load(Path(__file__).parent / "golden" / "rvem.npz")
+    for name, (seed, nv, ni, lm, sk) in mg.CASES.items():
+        assert mg.run_ref(mg.make_inputs(seed, nv, ni, lm, sk)) == g[f"{name}_bytes"].tobytes()
