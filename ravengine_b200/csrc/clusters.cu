@@ -95,11 +95,30 @@ __global__ void light_prepare_kernel(const unsigned char* __restrict__ lights, u
     out[i] = r;
 }
 
-// one warp per cluster; kinds processed one after the other (points, then spots)
+// One warp per cluster, eight clusters per CTA (x-neighbours of one y / z-slice: clusters are indexed x fastest); kinds
+// processed one after the other (points, then spots). Per tile of kLightTile lights the CTA first rejects, all threads
+// together, every light whose sphere misses the UNION of its eight AABBs - one y band and one depth slice of the grid,
+// so the large majority - and compacts the rest IN INDEX ORDER (ballot / popc, a 32-entry scan) into shared memory;
+// the warps then run the shader's exact test (cluster_assign_lights.csh:28-35) over the survivors only and append the
+// first 16 in index order (:60-67). The union test uses the same arithmetic and is conservative in floating point
+// (clamp is exact, rounding is monotonic: the distance to a superset box never rounds above the distance to the box),
+// so the result is the shader's, bit for bit.
+__device__ __forceinline__ bool sphere_hits_box(const float4 L, const float (&mn)[3], const float (&mx)[3]) {
+    const float qx = gmin(gmax(L.x, mn[0]), mx[0]) - L.x;
+    const float qy = gmin(gmax(L.y, mn[1]), mx[1]) - L.y;
+    const float qz = gmin(gmax(L.z, mn[2]), mx[2]) - L.z;
+    return dot3(qx, qy, qz, qx, qy, qz) <= L.w;
+}
+
 __global__ void __launch_bounds__(kAssignThreads)
 cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, const float4* __restrict__ pointRec,
                       uint32_t pointCount, const float4* __restrict__ spotRec, uint32_t spotCount) {
-    __shared__ float4 s_tile[kLightTile];
+    __shared__ float4 s_surv[kLightTile];      // lights of the tile that touch the CTA's union box, in index order
+    __shared__ uint32_t s_survIdx[kLightTile];
+    __shared__ float s_box[kAssignWarps][6];
+    __shared__ uint32_t s_off[kAssignWarps * 4 + 1];
+    constexpr uint32_t kSteps = kLightTile / (kAssignWarps * 32);  // prefilter steps per warp and tile
+    static_assert(kSteps == 4, "s_off is sized for four prefilter steps per warp");
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t index = blockIdx.x * kAssignWarps + warp;
     const bool have = index < numClusters;
@@ -111,6 +130,25 @@ cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, c
             mx[k] = clusters[index].maxPoint[k];
         }
     }
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            s_box[warp][k] = have ? mn[k] : __int_as_float(0x7f800000);       // +inf: ignored by the min
+            s_box[warp][3 + k] = have ? mx[k] : -__int_as_float(0x7f800000);  // -inf
+        }
+    }
+    __syncthreads();
+    float umn[3], umx[3];  // union of the CTA's boxes
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        umn[k] = s_box[0][k];
+        umx[k] = s_box[0][3 + k];
+#pragma unroll
+        for (int w = 1; w < kAssignWarps; ++w) {
+            umn[k] = fminf(umn[k], s_box[w][k]);
+            umx[k] = fmaxf(umx[k], s_box[w][3 + k]);
+        }
+    }
     for (int kind = 0; kind < 2; ++kind) {
         const float4* rec = kind ? spotRec : pointRec;
         const uint32_t count = kind ? spotCount : pointCount;
@@ -118,26 +156,52 @@ cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, c
         uint32_t* outIdx = have ? (kind ? clusters[index].spotLightIndices : clusters[index].pointLightIndices) : nullptr;
         uint32_t found = 0;  // warp-uniform
         for (uint32_t base = 0; base < count; base += kLightTile) {
-            // stop when every cluster of the CTA is full
+            // stop when every cluster of the CTA is full (also: the survivor list of the previous tile is free again)
             if (__syncthreads_and(!have || found >= cap)) break;
-            const uint32_t n = min(uint32_t(kLightTile), count - base);
-            for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) s_tile[i] = __ldg(rec + base + i);
+            // ---- prefilter: warp w owns lights [base + 128 w, base + 128 (w + 1)) of the tile, 32 per step ----
+            float4 L[kSteps];
+            uint32_t ballots[kSteps];
+#pragma unroll
+            for (uint32_t st = 0; st < kSteps; ++st) {
+                const uint32_t i = base + (warp * kSteps + st) * 32 + lane;
+                bool hit = false;
+                if (i < count) {
+                    L[st] = __ldg(rec + i);
+                    hit = sphere_hits_box(L[st], umn, umx);
+                }
+                ballots[st] = __ballot_sync(0xffffffffu, hit);
+                if (lane == 0) s_off[warp * kSteps + st] = __popc(ballots[st]);
+            }
             __syncthreads();
+            if (warp == 0) {  // exclusive scan of the 32 (warp, step) counts
+                const uint32_t v = s_off[lane];
+                uint32_t x = v;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) {
+                    const uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
+                    if (lane >= uint32_t(o)) x += y;
+                }
+                s_off[lane] = x - v;
+                if (lane == 31) s_off[32] = x;
+            }
+            __syncthreads();
+#pragma unroll
+            for (uint32_t st = 0; st < kSteps; ++st)
+                if ((ballots[st] >> lane) & 1u) {
+                    const uint32_t pos = s_off[warp * kSteps + st] + __popc(ballots[st] & ((1u << lane) - 1u));
+                    s_surv[pos] = L[st];
+                    s_survIdx[pos] = base + (warp * kSteps + st) * 32 + lane;
+                }
+            __syncthreads();
+            // ---- exact test over the survivors, in index order ----
+            const uint32_t n = s_off[32];
             if (have) {
                 for (uint32_t j = 0; j < n && found < cap; j += 32) {
-                    bool hit = false;
-                    if (j + lane < n) {
-                        const float4 L = s_tile[j + lane];
-                        // sphereAABBIntersection (cluster_assign_lights.csh:28-35)
-                        const float qx = gmin(gmax(L.x, mn[0]), mx[0]) - L.x;
-                        const float qy = gmin(gmax(L.y, mn[1]), mx[1]) - L.y;
-                        const float qz = gmin(gmax(L.z, mn[2]), mx[2]) - L.z;
-                        hit = dot3(qx, qy, qz, qx, qy, qz) <= L.w;
-                    }
+                    const bool hit = (j + lane < n) && sphere_hits_box(s_surv[j + lane], mn, mx);
                     const uint32_t ballot = __ballot_sync(0xffffffffu, hit);
                     if (hit) {
                         const uint32_t pos = found + __popc(ballot & ((1u << lane) - 1u));
-                        if (pos < cap) outIdx[pos] = base + j + lane;
+                        if (pos < cap) outIdx[pos] = s_survIdx[j + lane];
                     }
                     found = min(cap, found + uint32_t(__popc(ballot)));
                 }
