@@ -346,6 +346,15 @@ RVE_API int rve_cull(rve_ctx* ctx, const RveCullingUBO* ubo, rve_buffer cubos,
                      rve_buffer per_object_flags, rve_pyramid pyramid,
                      uint32_t num_groups_x);
 
+/* List maintenance for rve_cull: writes the ids of `entity_ids[0..count)` to `sorted_out` in ascending order. The cull maps
+ * invocation -> list position -> entity id (shaders/defaultcull.csh:150-170) and appends in arrival order, so - outside
+ * single-instance mode, where the position is the output slot - its result does not depend on the order of a command's
+ * list; the engine's lists are swap-remove dense arrays (include/RavEngine/SparseSet.hpp:34-47) and lose their runs as
+ * entities come and go. A CUBO may name the sorted copy as its entityIDInputBufferBindlessHandle; rebuild it when the list
+ * changed. Ids must be unique and < id_limit (the entity id space, e.g. the element count of worldTransforms); ids past
+ * the limit are dropped. Bitmap pass (set bits, block counts, scan, expand): four small launches, no comparison sort. */
+RVE_API int rve_sort_entity_ids(rve_ctx* ctx, rve_buffer entity_ids, uint32_t count, uint32_t id_limit, rve_buffer sorted_out);
+
 /* View-batched cull (SURVEY 8e partition B, 8f-2): the reference runs cullTheRenderData once per view of a frame
  * (main camera, every shadow cascade / spot / point face: src/RenderEngine_Draw.cpp:1769-1866, 1875-1987), each
  * pass re-reading every transform. Here one launch reads each instance ONCE and tests it against all `num_views`

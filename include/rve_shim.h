@@ -30,6 +30,11 @@ typedef struct rvs_world rvs_world;
                                         src/RenderEngine_Draw.cpp:1314 (collides when a material holds several
                                         multi-LOD collections); default: running LOD offset = what the shader reads */
 
+#define RVS_SORT_ENTITY_LISTS 0x2u   /* static culls read an ascending device copy of every command's entity list
+                                        (rve_sort_entity_ids), rebuilt when the list changed: a list bound with
+                                        rvs_material_add_command_set after a sync that uploaded something, a caller-owned
+                                        buffer after rvs_material_set_command_entities. Results are identical (compared as
+                                        sets per slice); skinned (single-instance) culls never use it */
 RVE_API int rvs_world_create(rve_ctx* ctx, uint32_t flags, rvs_world** out);
 RVE_API int rvs_world_destroy(rvs_world* w);
 

@@ -156,6 +156,10 @@ class Context:
         _check(self.lib, self.lib.rve_cull(self.h, C.byref(ubo), cubos.handle, model.handle, layers.handle, flags.handle,
                                            pyr.handle, num_groups_x))
 
+    def sort_entity_ids(self, ids: Buffer, count: int, id_limit: int, out: Buffer) -> None:
+        """rve_sort_entity_ids: ascending copy of an entity-id list (the cull's result does not depend on list order)"""
+        _check(self.lib, self.lib.rve_sort_entity_ids(self.h, ids.handle, count, id_limit, out.handle))
+
     def skin(self, ubo: SkinningUBO, outs: list[Buffer], ins: list[Buffer], pose: Buffer, weights: Buffer) -> None:
         o = (C.c_uint32 * 5)(*[b.handle for b in outs])
         i = (C.c_uint32 * 5)(*[b.handle for b in ins])

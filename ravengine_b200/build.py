@@ -10,7 +10,7 @@ from pathlib import Path
 HERE = Path(__file__).resolve().parent
 CSRC = HERE / "csrc"
 LIB = HERE / "librve_b200.so"
-SOURCES = ["ctx.cu", "pyramid.cu", "cull.cu", "skinning.cu", "clusters.cu", "scenegen.cu", "frame.cu", "frame_cull.cu", "frame_skinned.cu", "sync.cu", "p2p.cu", "csm.cu", "mesh_arena.cu"]
+SOURCES = ["ctx.cu", "pyramid.cu", "cull.cu", "skinning.cu", "clusters.cu", "scenegen.cu", "frame.cu", "frame_cull.cu", "frame_skinned.cu", "sync.cu", "p2p.cu", "csm.cu", "mesh_arena.cu", "sort_ids.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -50,6 +50,7 @@ int rvs_world_destroy(rvs_world* w) {
     for (auto& m : w->materials) {
         kill(m.cullingBuffer);
         kill(m.indirectBuffer);
+        for (auto& c : m.commands) kill(c.sortedIds);
     }
     for (auto& m : w->skinnedMaterials) {
         kill(m.cullingBuffer);
@@ -125,6 +126,7 @@ int rvs_material_set_command_entities(rvs_world* w, uint32_t material, uint32_t 
     auto& c = w->materials[material].commands[command_index];
     c.entityIds = entity_ids;
     c.count = entity_count;
+    c.sortedValid = false;  // also the way to say "the list's contents changed" for a caller-owned buffer
     return 0;
 }
 

@@ -1,5 +1,6 @@
 // frame_cull.cu — cullTheRenderData (src/RenderEngine_Draw.cpp:1221-1407) and the clustered-light
 // prologue of renderFromPerspective (:928-974), restated over the rve_* C-ABI. Host C++ only.
+#include <algorithm>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -40,11 +41,30 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
         for (auto& c : m.commands)
             if (c.set) {
                 rvs_vector* v = rvs_sparse_set_vector(c.set);
-                const int src = rvs_vector_encode_sync(v, RVS_SYNC_PACKED, 256, nullptr);
+                rvs_sync_stats st{};
+                const int src = rvs_vector_encode_sync(v, RVS_SYNC_PACKED, 256, &st);
                 if (src) return src;
+                if (st.ranges) c.sortedValid = false;  // the list changed
                 c.entityIds = rvs_vector_private_buffer(v);
                 c.count = rvs_sparse_set_dense_size(c.set);
             }
+    // RVS_SORT_ENTITY_LISTS: the cull reads an ascending copy of every list (its result does not depend on list order;
+    // a list shuffled by swap-remove erases costs the cull its tile path), rebuilt only when the list changed
+    if (w->flags & RVS_SORT_ENTITY_LISTS) {
+        const uint64_t idLimit = rve_buffer_size(w->ctx, w->model) / 64;
+        for (auto& m : w->materials)
+            for (auto& c : m.commands) {
+                if (!c.count) continue;
+                if (c.sortedValid && c.sortedOf == c.entityIds && c.sortedCount == c.count) continue;
+                int src = realloc_buffer(w, &c.sortedIds, &c.sortedBytes, c.count, sizeof(uint32_t));
+                if (src) return src;
+                src = rve_sort_entity_ids(w->ctx, c.entityIds, c.count, uint32_t(std::min<uint64_t>(idLimit, 0xFFFFFFFFull)), c.sortedIds);
+                if (src) return src;
+                c.sortedOf = c.entityIds;
+                c.sortedCount = c.count;
+                c.sortedValid = true;
+            }
+    }
     // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch
     uint32_t totalEntities = 0;
     for (auto& m : w->materials) {
@@ -126,7 +146,8 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
             cubo.idOutputBufferBindlessHandle = rve_buffer_bindless_index(ctx, m.cullingBuffer);
             cubo.indirectOutputBufferBindlessHandle = rve_buffer_bindless_index(ctx, m.indirectBuffer);
             cubo.lodDistanceBufferBindlessHandle = rve_buffer_bindless_index(ctx, mesh.lodDistances);
-            cubo.entityIDInputBufferBindlessHandle = rve_buffer_bindless_index(ctx, c.entityIds);
+            cubo.entityIDInputBufferBindlessHandle =
+                rve_buffer_bindless_index(ctx, ((w->flags & RVS_SORT_ENTITY_LISTS) && c.sortedValid && c.count) ? c.sortedIds : c.entityIds);
             strides[cuboIdx] = RveViewStride{numLODs, uint32_t(cullingbufferTotalSlots)};
             lodHost[cuboIdx] = mesh.lodDistancesHost.data();
             cuboStaging[cuboIdx++] = cubo;

@@ -26,6 +26,12 @@ struct Command {
     rve_buffer entityIds;
     uint32_t count;
     rvs_sparse_set* set = nullptr;  // when set: entityIds / count follow the set (synced before every cull)
+    // RVS_SORT_ENTITY_LISTS: ascending device copy of the list, rebuilt when the list changed; the cull reads it instead
+    rve_buffer sortedIds = RVE_BUFFER_INVALID;
+    size_t sortedBytes = 0;
+    rve_buffer sortedOf = RVE_BUFFER_INVALID;
+    uint32_t sortedCount = 0;
+    bool sortedValid = false;
 };
 
 // MDICommandBase + MDIICommand (World.hpp:334-349)

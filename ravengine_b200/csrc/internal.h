@@ -99,6 +99,8 @@ struct rve_ctx {
     size_t d_views_cap = 0;
     void* d_view_stride = nullptr;  // per-CUBO output strides of a view-batched cull
     size_t d_view_stride_cap = 0;
+    void* d_sort = nullptr;  // rve_sort_entity_ids: bitmap + block sums
+    size_t d_sort_cap = 0;
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
     size_t pyramid_smem_opt_in = 48 * 1024;  // dynamic shared memory pyramid_build_tma_kernel has been opted in for
     bool views_attr_set = false;  // cull_views_kernel's dynamic shared memory opt-in (per device, hence per context)

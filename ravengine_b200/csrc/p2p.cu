@@ -132,7 +132,17 @@ __global__ void __launch_bounds__(256) gather_ids_kernel(const GatherParams p) {
             for (uint32_t q = 0; q < world; ++q) {
                 if (!((p.consumers >> q) & 1u)) continue;
                 uint32_t* dst = p.dst[q][b] + p.dstStart[s] + off;
-                for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) dst[i] = __ldg(src + i) + p.idBase;
+                // four independent loads in flight per thread (the loop is latency-bound: NVLink stores are fire-and-forget)
+                const uint32_t stride = gridDim.x * blockDim.x;
+                uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+                for (; i + 3 * stride < n; i += 4 * stride) {
+                    const uint32_t a = __ldg(src + i), b = __ldg(src + i + stride), c = __ldg(src + i + 2 * stride), d = __ldg(src + i + 3 * stride);
+                    dst[i] = a + p.idBase;
+                    dst[i + stride] = b + p.idBase;
+                    dst[i + 2 * stride] = c + p.idBase;
+                    dst[i + 3 * stride] = d + p.idBase;
+                }
+                for (; i < n; i += stride) dst[i] = __ldg(src + i) + p.idBase;
             }
         }
     }

@@ -11,6 +11,7 @@ from .api import Buffer, Context, Pyramid, _check
 
 MAT_LIT_OPAQUE, MAT_UNLIT_OPAQUE, MAT_LIT_TRANSPARENT, MAT_UNLIT_TRANSPARENT, MAT_ALL = 1, 2, 4, 8, 0xF
 QUIRK_INDIRECT_SLOT = 1
+SORT_ENTITY_LISTS = 2
 
 
 def _fp(a):

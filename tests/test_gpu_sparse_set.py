@@ -106,3 +106,93 @@ def test_cull_over_churned_entity_lists_matches_oracle(ctx):
     w.destroy()
     for s in sets:
         s.destroy()
+
+
+@pytest.mark.parametrize("count,id_limit", [(1, 1), (1, 70_000), (33, 64), (5000, 5000), (100_000, 3_000_000), (1_000_003, 33_554_433)])
+def test_sort_entity_ids_is_numpy_sort(ctx, count, id_limit):
+    """rve_sort_entity_ids (bitmap pass: set bits, block counts, scan, expand) against np.sort, over id spaces from one
+    bitmap word to several scan blocks; twice on the same context (the scratch is re-zeroed)."""
+    rng = np.random.default_rng(count)
+    for _ in range(2):
+        ids = rng.choice(id_limit, size=count, replace=False).astype(np.uint32)
+        src, dst = ctx.buffer_from_numpy(ids), ctx.create_buffer(4 * count)
+        ctx.sort_entity_ids(src, count, id_limit, dst)
+        ctx.synchronize()
+        assert np.array_equal(dst.download(np.uint32)[:count], np.sort(ids))
+        src.destroy()
+        dst.destroy()
+
+
+def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
+    """RVS_SORT_ENTITY_LISTS: the cull reads an ascending copy of every list. Same oracle result as the unsorted world over
+    churned lists, the copy is rebuilt exactly when a list changes (launch counts), for set-backed and buffer-backed
+    commands."""
+    from ravengine_b200.world import SORT_ENTITY_LISTS
+
+    rng = np.random.default_rng(8)
+    n = 30_000
+    model = scenes.random_transforms(rng, n, 200.0, 60.0)
+    layers = np.full(n, 0xFFFFFFFF, np.uint32)
+    flags = np.full(n, 0xFFFF, np.uint16)
+    cam = scenes.default_camera(z_far=500.0)
+    depth = scenes.synth_depth(512, 288, cam, n_occluders=30)
+    pyr_h, dim, levels = oracle.pyramid_build(depth, 288)
+    w = World(ctx, SORT_ENTITY_LISTS)
+    keep = [ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(layers), ctx.buffer_from_numpy(flags)]
+    w.set_entity_buffers(*keep)
+    meshes = [scenes.simple_mesh(1.5, (0.0, 30.0, 90.0)), scenes.simple_mesh(2.5, (math.inf,), base=7000)]
+    mids = [w.mesh_collection(m.radius, m.lod_distances, [l.index_count for l in m.lods], [l.index_start for l in m.lods],
+                              [l.base_vertex for l in m.lods]) for m in meshes]
+    s = SparseSet(ctx)
+    s.emplace_many(rng.permutation(np.arange(0, n // 2, dtype=np.uint32)))
+    raw_ids = rng.permutation(np.arange(n // 2, n, dtype=np.uint32))
+    raw_buf = ctx.buffer_from_numpy(raw_ids)
+    mats = [w.material(), w.material()]
+    w.add_command_set(mats[0], mids[0], s)
+    w.add_command(mats[1], mids[1], raw_buf, len(raw_ids))
+    pyr = ctx.create_pyramid(288)
+    ctx.build_pyramid(pyr, ctx.buffer_from_numpy(depth), 512, 288)
+
+    def check():
+        lists = [s.dense(), raw_ids]
+        omats = [scenes.MaterialDraws([scenes.DrawCommand(mesh, l)]) for mesh, l in zip(meshes, lists)]
+        t = host_tables.build_static_tables(omats)
+        ref = oracle_cull(t, make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos), model, layers, flags, pyr_h, dim, levels, nthreads=4)
+        for ci, mat in enumerate(mats):
+            cull_b, ind_b, lods, ents = w.material_outputs(mat)
+            cb = t.cubos[ci]
+            r_ind, r_ids = ref[int(cb["indirectOutputBufferBindlessHandle"])], ref[int(cb["idOutputBufferBindlessHandle"])]
+            g_ind, g_ids = ind_b.download(np.uint32).reshape(-1, 5)[:lods], cull_b.download(np.uint32)[: lods * ents]
+            np.testing.assert_array_equal(g_ind, r_ind)
+            for x, y in zip(host_tables.sorted_slices(r_ind, r_ids, t.cubos, range(ci, ci + 1)), host_tables.sorted_slices(g_ind, g_ids, t.cubos, range(ci, ci + 1))):
+                np.testing.assert_array_equal(x, y)
+
+    l0 = ctx.launch_count
+    w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+    ctx.synchronize()
+    first = ctx.launch_count - l0
+    check()
+    l0 = ctx.launch_count
+    w.cull_static(cam.view_proj_cm, cam.pos, pyr)  # nothing changed: no re-sort, no list upload
+    ctx.synchronize()
+    steady = ctx.launch_count - l0
+    assert steady == 2 and first == steady + 2 * 4 + 1  # upload + cull; first frame: + two sorts (4 launches each) + the set's scatter
+    check()
+    gone = rng.choice(s.dense(), size=1500, replace=False)  # the set changes: only its copy is rebuilt
+    s.erase_many(gone)
+    s.emplace_many(rng.permutation(gone)[:700])
+    l0 = ctx.launch_count
+    w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+    ctx.synchronize()
+    assert 2 + 4 <= ctx.launch_count - l0 <= 2 + 4 + 2
+    check()
+    raw_ids = rng.permutation(raw_ids)[:-300]  # the caller-owned list changes: set_command_entities announces it
+    raw_buf2 = ctx.buffer_from_numpy(raw_ids)
+    w.set_command_entities(mats[1], 0, raw_buf2, len(raw_ids))
+    l0 = ctx.launch_count
+    w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+    ctx.synchronize()
+    assert ctx.launch_count - l0 == 2 + 4
+    check()
+    w.destroy()
+    s.destroy()

@@ -103,7 +103,7 @@ def _cpu_cull(n, lods, occlusion, shuffle, depth, cam, n_mats, reps=3, ids_overr
             "sample": f"{n} instances (the full stage), median of {reps}"}
 
 
-def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu=True):
+def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu=True, world_flags=0):
     dev = torch.device("cuda", ctx.device)
     st = torch.cuda.ExternalStream(ctx.stream)
     with torch.cuda.stream(st):
@@ -120,7 +120,7 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu
         with torch.cuda.stream(st):
             t_flags.fill_(-3)  # 0xFFFD: occlusion bit cleared (C1 is frustum + LOD only)
     cam = scenes.default_camera(z_near=0.1, z_far=far)
-    w = World(ctx)
+    w = World(ctx, world_flags)
     w.set_entity_buffers(model, layers, flags)
     n_mats = 4 if occlusion else 2
     bounds = [n * i // n_mats for i in range(n_mats + 1)]
@@ -203,6 +203,15 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
     if want("c2churn"):
         yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, "churn", (3840, 2160), reps,
                         "C2 variant: 10M instances after 10 % erase / re-insert churn of every entity list (swap-remove)", None, cpu)
+
+    if want("c2sorted"):
+        from ravengine_b200.world import SORT_ENTITY_LISTS
+
+        yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, "churn", (3840, 2160), reps,
+                        "C2 variant: the churned lists, culled through their ascending device copies (RVS_SORT_ENTITY_LISTS; "
+                        "the copy is rebuilt only when a list changes - not in these launches)", None, False, SORT_ENTITY_LISTS)
+        yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, True, (3840, 2160), reps,
+                        "C2 variant: fully shuffled lists through their ascending device copies", None, False, SORT_ENTITY_LISTS)
 
     if want("pyramid"):
         cam = scenes.default_camera(z_far=1000.0)
