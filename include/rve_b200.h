@@ -240,6 +240,20 @@ RVE_API uint32_t rve_ctx_bad_cubo_handles(rve_ctx* ctx);
 /* how many kernels this context has launched so far (bench.py "gpu_launches") */
 RVE_API uint64_t rve_ctx_launch_count(rve_ctx* ctx);
 
+/* One frame = one submission. The reference records its whole frame into one command buffer and commits it once
+ * (src/App_priv.hpp:475-483); every rve_* / rvs_* call here is an enqueue on the context's stream, so a frame's calls can be
+ * recorded into a CUDA graph and replayed with a single launch - what a small scene needs, whose step is bound by launch
+ * latency rather than bandwidth (C1: 100 k instances). Between _begin and _end nothing executes; host tables passed to the
+ * calls are copied into pinned blocks owned by the graph. Capture a frame after it has run once normally (buffers and
+ * scratch sized, bindless table uploaded); replaying is valid while the scene's buffers, counts and views are the ones
+ * recorded - per-entity data (transforms, layers, attributes, depth) may change freely, it is read at replay time. Calls that
+ * synchronise (rve_buffer_download, rve_ctx_synchronize, profile reads) and the profiling events are not capturable. */
+typedef struct rve_graph rve_graph;
+RVE_API int rve_ctx_capture_begin(rve_ctx* ctx);
+RVE_API int rve_ctx_capture_end(rve_ctx* ctx, rve_graph** out);
+RVE_API int rve_graph_launch(rve_ctx* ctx, rve_graph* graph);
+RVE_API int rve_graph_destroy(rve_graph* graph);
+
 /* Host placement for the upload path that feeds this one (the reference's per-frame EncodeSync of the host-shared
  * worldTransforms / renderLayers / perObjectAttributes arrays, src/BufferedVRAMVector.cpp:27-144, from Shared-access
  * RGL buffers, deps/RGL/include/RGL/Buffer.hpp:25-35): binds the CALLING thread (threads it spawns inherit) to the CPUs

@@ -91,6 +91,10 @@ PROTOTYPES = {
     "rve_ctx_sm_count": (C.c_int, [VP]),
     "rve_ctx_launch_count": (u64, [VP]),
     "rve_ctx_bad_cubo_handles": (u32, [VP]),
+    "rve_ctx_capture_begin": (C.c_int, [VP]),
+    "rve_ctx_capture_end": (C.c_int, [VP, C.POINTER(VP)]),
+    "rve_graph_launch": (C.c_int, [VP, VP]),
+    "rve_graph_destroy": (C.c_int, [VP]),
     "rve_ctx_bind_host_to_device": (C.c_int, [VP, u32, VP]),
     "rve_ctx_set_profiling": (C.c_int, [VP, C.c_int]),
     "rve_ctx_profile_read": (C.c_int, [VP, C.c_int, C.POINTER(C.c_double), C.POINTER(u32)]),

@@ -65,6 +65,21 @@ class Buffer:
         self._keepalive = None
 
 
+class Graph:
+    """A captured frame (rve_graph): one launch replays every enqueue recorded by Context.capture."""
+
+    def __init__(self, ctx: "Context", h):
+        self.ctx, self.h = ctx, h
+
+    def launch(self) -> None:
+        _check(self.ctx.lib, self.ctx.lib.rve_graph_launch(self.ctx.h, self.h))
+
+    def destroy(self) -> None:
+        if self.h:
+            self.ctx.lib.rve_graph_destroy(self.h)
+            self.h = None
+
+
 class Context:
     """One device + one in-order stream (the reference's device/queue pair)."""
 
@@ -101,6 +116,17 @@ class Context:
     @property
     def launch_count(self) -> int:
         return int(self.lib.rve_ctx_launch_count(self.h))
+
+    def capture(self, record) -> "Graph":
+        """Records the enqueues `record()` makes into a CUDA graph (rve_ctx_capture_begin / _end); replay with Graph.launch()."""
+        _check(self.lib, self.lib.rve_ctx_capture_begin(self.h))
+        try:
+            record()
+        finally:
+            g = C.c_void_p()
+            rc = self.lib.rve_ctx_capture_end(self.h, C.byref(g))
+        _check(self.lib, rc)
+        return Graph(self, g)
 
     def bind_host_to_device(self, cpus: bool = True, memory: bool = True) -> dict:
         """rve_ctx_bind_host_to_device: this thread onto the GPU's local CPUs, its next (pinned) allocations onto the GPU's NUMA node."""

@@ -155,6 +155,14 @@ cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, c
         const uint32_t cap = kind ? RVE_CLUSTER_MAX_SPOTS : RVE_CLUSTER_MAX_POINTS;
         uint32_t* outIdx = have ? (kind ? clusters[index].spotLightIndices : clusters[index].pointLightIndices) : nullptr;
         uint32_t found = 0;  // warp-uniform
+        // the next tile's records are requested one tile ahead: at three CTAs per SM the tile loop is otherwise bound by the
+        // latency of these loads (a view whose clusters never fill scans all 64 tiles)
+        float4 Lnext[kSteps];
+#pragma unroll
+        for (uint32_t st = 0; st < kSteps; ++st) {
+            const uint32_t i = (warp * kSteps + st) * 32 + lane;
+            Lnext[st] = i < count ? __ldg(rec + i) : make_float4(0.f, 0.f, 0.f, -1.f);
+        }
         for (uint32_t base = 0; base < count; base += kLightTile) {
             // stop when every cluster of the CTA is full (also: the survivor list of the previous tile is free again)
             if (__syncthreads_and(!have || found >= cap)) break;
@@ -162,13 +170,16 @@ cluster_assign_kernel(RveCluster* __restrict__ clusters, uint32_t numClusters, c
             float4 L[kSteps];
             uint32_t ballots[kSteps];
 #pragma unroll
+            for (uint32_t st = 0; st < kSteps; ++st) L[st] = Lnext[st];
+#pragma unroll
+            for (uint32_t st = 0; st < kSteps; ++st) {
+                const uint32_t i = base + kLightTile + (warp * kSteps + st) * 32 + lane;
+                Lnext[st] = i < count ? __ldg(rec + i) : make_float4(0.f, 0.f, 0.f, -1.f);
+            }
+#pragma unroll
             for (uint32_t st = 0; st < kSteps; ++st) {
                 const uint32_t i = base + (warp * kSteps + st) * 32 + lane;
-                bool hit = false;
-                if (i < count) {
-                    L[st] = __ldg(rec + i);
-                    hit = sphere_hits_box(L[st], umn, umx);
-                }
+                const bool hit = i < count && sphere_hits_box(L[st], umn, umx);
                 ballots[st] = __ballot_sync(0xffffffffu, hit);
                 if (lane == 0) s_off[warp * kSteps + st] = __popc(ballots[st]);
             }
@@ -237,7 +248,8 @@ int rve_cluster_build(rve_ctx* ctx, const RveGridBuildUBO* ubo, rve_buffer clust
     for (uint32_t k = 0; k <= gz; ++k) slices[k] = ubo->zFar * std::pow(ubo->zNear / ubo->zFar, float(k) / float(gz));
     int rc = ensure_scratch(ctx, reinterpret_cast<void**>(&ctx->d_slices), &ctx->d_slices_cap, slices.size() * sizeof(float));
     if (rc) return rc;
-    RVE_CUDA(cudaMemcpyAsync(ctx->d_slices, slices.data(), slices.size() * sizeof(float), cudaMemcpyHostToDevice, ctx->stream));
+    rc = staged_h2d(ctx, ctx->d_slices, slices.data(), slices.size() * sizeof(float));
+    if (rc) return rc;
     const uint32_t n = uint32_t(n64), threads = 128;
     cluster_build_kernel<<<(n + threads - 1) / threads, threads, 0, ctx->stream>>>(*ubo, ctx->d_slices,
                                                                                  static_cast<RveCluster*>(b->ptr), n);

@@ -60,6 +60,19 @@ int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes) {
     return 0;
 }
 
+int staged_h2d(rve_ctx* ctx, void* dst, const void* src, size_t bytes) {
+    if (!bytes) return 0;
+    if (ctx->capture) {
+        void* pin = nullptr;
+        RVE_CUDA(cudaHostAlloc(&pin, bytes, cudaHostAllocDefault));
+        memcpy(pin, src, bytes);
+        ctx->capture->pinned.push_back(pin);
+        src = pin;
+    }
+    RVE_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return 0;
+}
+
 int sync_table(rve_ctx* ctx) {
     if (!ctx->table_dirty) return 0;
     const size_t n = ctx->buffers.size();
@@ -76,7 +89,8 @@ int sync_table(rve_ctx* ctx) {
         std::vector<void*> host(n);
         for (size_t i = 0; i < n; ++i) host[i] = ctx->buffers[i].live ? ctx->buffers[i].ptr : nullptr;
         // pageable source: the runtime stages it before returning, so `host` may die afterwards
-        RVE_CUDA(cudaMemcpyAsync(ctx->d_table, host.data(), n * sizeof(void*), cudaMemcpyHostToDevice, ctx->stream));
+        const int rc = staged_h2d(ctx, ctx->d_table, host.data(), n * sizeof(void*));
+        if (rc) return rc;
     }
     ctx->table_dirty = false;
     return 0;
@@ -305,6 +319,58 @@ uint32_t rve_ctx_bad_cubo_handles(rve_ctx* ctx) {
     return v;
 }
 
+// ---- one frame = one submission: the reference records its whole frame into one command buffer and commits it once
+// (src/App_priv.hpp:475-483). Here: capture the rve_* / rvs_* enqueues of a frame into a CUDA graph, replay it with one launch.
+int rve_ctx_capture_begin(rve_ctx* ctx) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    RVE_REQUIRE(!ctx->capture, "a capture is already in progress on this context");
+    DeviceGuard g(ctx->device);
+    auto* gr = new rve_graph();
+    gr->device = ctx->device;
+    // relaxed mode: the library may allocate (pinned staging, scratch growth) while the stream records
+    const int rc = check_cuda(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeRelaxed), "cudaStreamBeginCapture");
+    if (rc) {
+        delete gr;
+        return rc;
+    }
+    ctx->capture = gr;
+    return 0;
+}
+
+int rve_ctx_capture_end(rve_ctx* ctx, rve_graph** out) {
+    if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(ctx->capture, "no capture in progress");
+    DeviceGuard g(ctx->device);
+    rve_graph* gr = ctx->capture;
+    ctx->capture = nullptr;
+    int rc = check_cuda(cudaStreamEndCapture(ctx->stream, &gr->graph), "cudaStreamEndCapture");
+    if (rc == 0) rc = check_cuda(cudaGraphInstantiate(&gr->exec, gr->graph, 0), "cudaGraphInstantiate");
+    if (rc) {
+        rve_graph_destroy(gr);
+        return rc;
+    }
+    *out = gr;
+    return 0;
+}
+
+int rve_graph_launch(rve_ctx* ctx, rve_graph* graph) {
+    if (!ctx || !graph || !graph->exec) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(ctx->device == graph->device, "graph captured on another device");
+    DeviceGuard g(ctx->device);
+    RVE_CUDA(cudaGraphLaunch(graph->exec, ctx->stream));
+    return 0;
+}
+
+int rve_graph_destroy(rve_graph* graph) {
+    if (!graph) return 0;
+    DeviceGuard g(graph->device);
+    if (graph->exec) cudaGraphExecDestroy(graph->exec);
+    if (graph->graph) cudaGraphDestroy(graph->graph);
+    for (void* p : graph->pinned) cudaFreeHost(p);
+    delete graph;
+    return 0;
+}
+
 void* rve_ctx_stream(rve_ctx* ctx) { return ctx ? ctx->stream : nullptr; }
 int rve_ctx_sm_count(rve_ctx* ctx) { return ctx ? ctx->sm_count : 0; }
 uint64_t rve_ctx_launch_count(rve_ctx* ctx) { return ctx ? ctx->launches : 0; }
@@ -356,7 +422,8 @@ int rve_buffer_upload(rve_ctx* ctx, rve_buffer buf, size_t dst_offset, const voi
     if (!b) return RVE_ERR_BAD_HANDLE;
     if (dst_offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "upload out of range");
     if (!bytes) return 0;
-    RVE_CUDA(cudaMemcpyAsync(static_cast<char*>(b->ptr) + dst_offset, host_src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    const int rc = staged_h2d(ctx, static_cast<char*>(b->ptr) + dst_offset, host_src, bytes);
+    if (rc) return rc;
     pyramid_note_buffer_write(ctx, buf);
     return 0;
 }

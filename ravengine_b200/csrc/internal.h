@@ -60,8 +60,18 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 
 }  // namespace rve
 
+// A captured frame (rve_ctx_capture_begin / _end): the CUDA graph, its executable instance and the pinned blocks that hold
+// the host data its copy nodes read at every replay.
+struct rve_graph {
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    std::vector<void*> pinned;
+    int device = 0;
+};
+
 struct rve_ctx {
     int device = 0;
+    rve_graph* capture = nullptr;  // non-null between rve_ctx_capture_begin and rve_ctx_capture_end
     cudaStream_t stream = nullptr;
     bool owns_stream = false;
     int sm_count = 0;
@@ -124,6 +134,10 @@ PyramidRec* get_pyramid(rve_ctx* ctx, rve_pyramid h);
 // makes sure the device pointer table reflects the host table (enqueued on the stream)
 int sync_table(rve_ctx* ctx);
 int ensure_scratch(rve_ctx* ctx, void** ptr, size_t* cap, size_t bytes);
+// host -> device copy of a small table on the context's stream. Outside a capture: a plain (pageable, runtime-staged) copy.
+// While a frame is being captured the bytes are first copied into a pinned block owned by the graph, so that the copy
+// node has something to read at every replay.
+int staged_h2d(rve_ctx* ctx, void* dst, const void* src, size_t bytes);
 // Small host tables written by ONE kernel whose payload travels as kernel parameters (ctx.cu). Raw destinations; returns
 // RVE_ERR_UNSUPPORTED (nothing enqueued) when the segments do not fit one launch.
 struct RawSegment {

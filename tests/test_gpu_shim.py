@@ -396,3 +396,64 @@ def test_fused_pyramid_and_cull_encode_matches_oracle(ctx, n, size):
         _compare_static(ctx, w, mat_ids, mats, t, ref)
         d.destroy()
     w.destroy()
+
+
+def test_captured_frame_replays_with_new_per_entity_data(ctx):
+    """rve_ctx_capture_begin / _end: a frame (tables -> pyramid -> cull, then an 8-view batch and the light binning of
+    rvs_frame_encode) recorded once and replayed with ONE launch per frame gives the oracle's result for the data that is
+    in the buffers AT REPLAY TIME: transforms and the depth image change between replays."""
+    model, layers, flags, mats = _static_scene(seed=21)
+    cam = scenes.default_camera(z_far=500.0)
+    t = host_tables.build_static_tables(mats)
+    ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos)
+    w, mat_ids, keep = _world_from(ctx, model, layers, flags, mats)
+    pyr = ctx.create_pyramid(288)
+    depth = scenes.synth_depth(512, 288, cam, n_occluders=30, seed=1)
+    d_depth = ctx.buffer_from_numpy(depth)
+    w.cull_static_with_pyramid(cam.view_proj_cm, cam.pos, pyr, d_depth, 512, 288)  # warm-up: buffers, scratch, bindless table
+    ctx.synchronize()
+    launches = ctx.launch_count
+    graph = ctx.capture(lambda: w.cull_static_with_pyramid(cam.view_proj_cm, cam.pos, pyr, d_depth, 512, 288))
+    recorded = ctx.launch_count - launches
+    assert recorded == 4  # upload, pyramid build, pyramid upper, cull - recorded, not executed
+    rng = np.random.default_rng(3)
+    for frame in range(3):
+        model2 = scenes.random_transforms(rng, len(model), 120.0, 60.0)
+        depth2 = scenes.synth_depth(512, 288, cam, n_occluders=30, seed=10 + frame)
+        keep[0].upload(model2)
+        d_depth.upload(depth2)
+        graph.launch()
+        ctx.synchronize()
+        pyr_h, dim, levels = oracle.pyramid_build(depth2, 288)
+        np.testing.assert_array_equal(pyr_h, pyr.texels.download(np.float32))
+        ref = oracle_cull(t, ubo, model2, layers, flags, pyr_h, dim, levels, nthreads=4)
+        _compare_static(ctx, w, mat_ids, mats, t, ref)
+    graph.destroy()
+    # a view batch (host view table, strides: staged into pinned blocks owned by the graph)
+    cams = [scenes.default_camera(z_far=500.0, eye=(10.0 * i, 5.0, 40.0 - 9.0 * i), target=(0.0, 0.0, -20.0)) for i in range(9)]
+    views = [(c.view_proj_cm, c.pos, 0xFFFFFFFF, i % 3 == 1) for i, c in enumerate(cams)]
+    w.cull_static_views(views, [pyr] * 9)
+    ctx.synchronize()
+    graph = ctx.capture(lambda: w.cull_static_views(views, [pyr] * 9))
+    model3 = scenes.random_transforms(rng, len(model), 120.0, 60.0)
+    keep[0].upload(model3)
+    graph.launch()
+    ctx.synchronize()
+    pyr_h = pyr.texels.download(np.float32)
+    dim, levels = oracle.pyramid_dims(288)
+    ci = 0
+    for mat, m in zip(mat_ids, mats):
+        cull_b, ind_b, lods, ents = w.material_outputs(mat)
+        all_ind, all_ids = ind_b.download(np.uint32).reshape(-1, 5), cull_b.download(np.uint32)
+        cb = t.cubos[ci]
+        rng_c = range(ci, ci + len(m.commands))
+        for v, (c, (_, _, _, sh)) in enumerate(zip(cams, views)):
+            ref = oracle_cull(t, make_ubo(c.view_proj_cm, c.pos, t.num_cubos, shadow=sh), model3, layers, flags, pyr_h, dim, levels, nthreads=4)
+            r_ind, r_ids = ref[int(cb["indirectOutputBufferBindlessHandle"])], ref[int(cb["idOutputBufferBindlessHandle"])]
+            g_ind, g_ids = all_ind[v * lods:(v + 1) * lods], all_ids[v * lods * ents:(v + 1) * lods * ents]
+            np.testing.assert_array_equal(g_ind, r_ind)
+            for x, y in zip(host_tables.sorted_slices(r_ind, r_ids, t.cubos, rng_c), host_tables.sorted_slices(g_ind, g_ids, t.cubos, rng_c)):
+                np.testing.assert_array_equal(x, y)
+        ci += len(m.commands)
+    graph.destroy()
+    w.destroy()

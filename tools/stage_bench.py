@@ -170,12 +170,23 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu
         w.cull_static(cam.view_proj_cm, cam.pos, pyr)
     ms, cnt = ctx.profile_read(0)
     ctx.set_profiling(False)
+    step_ms = None
+    if n <= 1_000_000:  # small scenes are launch-bound: the whole step (upload + cull), enqueued call by call and as one captured graph
+        def one():
+            w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+        direct, _ = timed(ctx, one, reps, flush)
+        graph = ctx.capture(one)
+        replay, _ = timed(ctx, graph.launch, reps, flush)
+        graph.destroy()
+        step_ms = {"step_ms_call_by_call": direct, "step_ms_captured_graph": replay}
     counts = [w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:len(lods), 1] for m in keep if isinstance(m, int)]
     vis = int(sum(int(c.sum()) for c in counts))
     algo = n * 74 + vis * 4 + 36 * n_mats + 20 * n_mats * len(lods) + (4 * (4 * pyr.dim ** 2 - 1) // 3 if depth_wh else 0)
     k_ms = ms / cnt
     extra = {"instances": n, "visible": vis, "ginst_per_s": n / (k_ms * 1e-3) / 1e9,
              "l2": "flushed between launches" if flush is not None else "inputs exceed L2"}
+    if step_ms:
+        extra.update(step_ms)
     if host_ids is not None:
         runs = np.flatnonzero(np.diff(host_ids.astype(np.int64)) != 1).size + 1
         extra["id_runs"] = int(runs)  # maximal runs of consecutive ids in the lists (1 per material when untouched)
@@ -298,13 +309,28 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
             med, best = timed(ctx, lambda: ctx.cluster_build(u, cl), reps)
             yield line("cluster_build", f"C4 grid {grid}", med, best, n * 24, "launch latency")
 
+            ubos = []
+            for v in views:
+                a_v = GridAssignUBO()
+                a_v.viewMat[:] = [float(x) for x in scenes.colmajor(v)]
+                a_v.pointLightCount, a_v.spotLightCount = nl, 0
+                ubos.append(a_v)
+
             def five_views():
-                for v in views:
-                    a.viewMat[:] = [float(x) for x in scenes.colmajor(v)]
-                    ctx.cluster_assign(a, cl, pts, None, n)
+                for a_v in ubos:
+                    ctx.cluster_assign(a_v, cl, pts, None, n)
             med, best = timed(ctx, five_views, reps)
+            ctx.set_profiling(True)  # the assign kernel alone (events inside the library), without the light prepare pass and launch gaps
+            for _ in range(3):
+                five_views()
+            k_ms, k_n = ctx.profile_read(3)
+            ctx.set_profiling(False)
             tests = 5 * n * nl
-            extra = {"sphere_aabb_tests": tests, "gtests_per_s": tests / (med * 1e-3) / 1e9, "ms_per_view": med / 5}
+            extra = {"sphere_aabb_tests": tests, "gtests_per_s": tests / (med * 1e-3) / 1e9, "ms_per_view": med / 5,
+                     "assign_kernel_ms_per_view": k_ms / max(k_n, 1),
+                     "note": "ms_per_view = light prepare + assign as enqueued from Python (two launches per view; at ~20 us of GPU work per "
+                             "view the loop is partly host-bound); sphere_aabb_tests counts every (cluster, light) pair, most of which the "
+                             "per-CTA union-box prefilter rejects eight clusters at a time"}
             if cpu and grid == (16, 9, 24):
                 import oracle
 
