@@ -191,6 +191,10 @@ RVE_API int rvs_vector_create(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count,
  * of the private buffer is unchanged and 25 % fewer bytes cross PCIe. Every sync mode works; byte-identical to a 64-B
  * vector holding the same matrices. */
 #define RVS_VECTOR_AFFINE_ROWS 0x1u
+/* The host block is a memfd mapping (pinned with cudaHostRegister) instead of a cudaHostAlloc block, so that ANOTHER rank
+ * of the same box can map and pin it too (rvs_vector_share / rve_host_import) and carry part of this rank's upload over
+ * its own PCIe link (rvs_forward_rows). The block is allocated once: such a vector cannot grow past its first size. */
+#define RVS_VECTOR_SHARED_HOST 0x2u
 RVE_API int rvs_vector_create_ex(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, uint32_t flags, rvs_vector** out);
 RVE_API int rvs_vector_destroy(rvs_vector* v);
 /* Resize: new elements are zero and start out modified (BufferedVRAMVector.hpp:64-69) */
@@ -206,6 +210,29 @@ RVE_API int rvs_vector_set(rvs_vector* v, uint32_t index, const void* value);
 RVE_API int rvs_vector_mark(rvs_vector* v, uint32_t begin, uint32_t end);
 /* EncodeSync: enqueues the copies on the context's stream; afterwards the private buffer equals the host buffer */
 RVE_API int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_rows, rvs_sync_stats* stats);
+/* RVS_SYNC_FULL / RVS_SYNC_FULL_PULL restricted to rows [row_begin, row_end): the owner's share of a forwarded upload */
+RVE_API int rvs_vector_encode_sync_rows(rvs_vector* v, uint32_t mode, uint32_t row_begin, uint32_t row_end, rvs_sync_stats* stats);
+/* (pid, fd, mapped bytes) of a RVS_VECTOR_SHARED_HOST vector's host block: what a peer passes to rve_host_import */
+RVE_API int rvs_vector_share(rvs_vector* v, int32_t* pid, int32_t* fd, uint64_t* bytes);
+
+/* ---- upload forwarding between ranks of one box. The reference has one GPU: its EncodeSync
+ * copies (src/BufferedVRAMVector.cpp:87-104) all cross that GPU's PCIe link. With
+ * one process per GPU the links are not equal (on the pool's 8-GPU boxes four GPUs share one path to host memory), and a
+ * rank on a fast link can carry the tail of a slow rank's rows: it maps the owner's host block, reads the rows over its
+ * own link with one kernel and writes them - expanded to 64-B rows when `affine` - straight into the owner's private
+ * buffer over NVLink peer memory. ---- */
+/* maps and pins the host block (pid, fd) of another process (or this one); *out_ptr is usable by kernels of ctx's device */
+RVE_API int rve_host_import(rve_ctx* ctx, int32_t pid, int32_t fd, uint64_t bytes, void** out_ptr);
+RVE_API int rve_host_release(rve_ctx* ctx, void* ptr, uint64_t bytes);
+/* flag words (u32) in a buffer both ranks have mapped (rve_ipc_export / rve_ipc_import): signal = release-store of `value`
+ * behind everything enqueued so far; wait = spin until the word reaches `value` (wrap-safe), ~2 s timeout -> *status |= 1 */
+RVE_API int rve_flag_signal(rve_ctx* ctx, rve_buffer flags, uint32_t word, uint32_t value);
+RVE_API int rve_flag_wait(rve_ctx* ctx, rve_buffer flags, uint32_t word, uint32_t value, rve_buffer status);
+/* rows [first_row, first_row + rows) of the imported host block (row_bytes each; affine != 0: 48-B rows expanded to 64-B
+ * rows) -> the same rows of `dst` (the owner's private buffer, imported), on ctx's stream */
+RVE_API int rvs_forward_rows(rve_ctx* ctx, const void* host_rows, uint32_t row_bytes, uint32_t affine, uint64_t first_row, uint64_t rows,
+                             rve_buffer dst);
+
 /* GetPrivateBuffer(): may change at every rvs_vector_encode_sync after a growth, like the reference's */
 RVE_API rve_buffer rvs_vector_private_buffer(rvs_vector* v);
 /* rows copied by RVS_SYNC_PULL syncs since creation (reads a device counter: synchronises the stream) */

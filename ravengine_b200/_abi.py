@@ -202,6 +202,7 @@ class SyncStats(C.Structure):
 
 SYNC_RANGES, SYNC_PACKED, SYNC_PULL, SYNC_FULL, SYNC_FULL_PULL = 0, 1, 2, 3, 4
 VECTOR_AFFINE_ROWS = 1
+VECTOR_SHARED_HOST = 2
 PROTOTYPES.update({
     "rvs_vector_create": (C.c_int, [VP, u32, u32, C.POINTER(VP)]),
     "rvs_vector_create_ex": (C.c_int, [VP, u32, u32, u32, C.POINTER(VP)]),
@@ -214,6 +215,13 @@ PROTOTYPES.update({
     "rvs_vector_mark": (C.c_int, [VP, u32, u32]),
     "rvs_vector_encode_sync": (C.c_int, [VP, u32, u32, C.POINTER(SyncStats)]),
     "rvs_vector_private_buffer": (u32, [VP]),
+    "rvs_vector_encode_sync_rows": (C.c_int, [VP, u32, u32, u32, C.POINTER(SyncStats)]),
+    "rvs_vector_share": (C.c_int, [VP, C.POINTER(i32), C.POINTER(i32), C.POINTER(u64)]),
+    "rve_host_import": (C.c_int, [VP, i32, i32, u64, C.POINTER(VP)]),
+    "rve_host_release": (C.c_int, [VP, VP, u64]),
+    "rve_flag_signal": (C.c_int, [VP, u32, u32, u32]),
+    "rve_flag_wait": (C.c_int, [VP, u32, u32, u32, u32]),
+    "rvs_forward_rows": (C.c_int, [VP, VP, u32, u32, u64, u64, u32]),
     "rvs_vector_pulled_rows": (u64, [VP]),
     "rvs_vector_last_ranges": (u32, [VP, UP, u32]),
 })

@@ -258,6 +258,26 @@ class Context:
         _check(self.lib, self.lib.rve_gather_ids_p2p(self.h, sh, nb, sb, ss, ds, ns, dh, consumers, id_base, offsets.handle, totals.handle, m,
                                                      rank, world, epoch, status.handle))
 
+    # ---- upload forwarding between ranks (csrc/sync.cu) ----
+    def host_import(self, pid: int, fd: int, nbytes: int) -> int:
+        """rve_host_import: maps and pins another rank's shared host block; returns the host pointer"""
+        p = C.c_void_p()
+        _check(self.lib, self.lib.rve_host_import(self.h, pid, fd, nbytes, C.byref(p)))
+        return p.value
+
+    def host_release(self, ptr: int, nbytes: int) -> None:
+        _check(self.lib, self.lib.rve_host_release(self.h, C.c_void_p(ptr), nbytes))
+
+    def flag_signal(self, flags: Buffer, word: int, value: int) -> None:
+        _check(self.lib, self.lib.rve_flag_signal(self.h, flags.handle, word, value & 0xFFFFFFFF))
+
+    def flag_wait(self, flags: Buffer, word: int, value: int, status: Buffer) -> None:
+        _check(self.lib, self.lib.rve_flag_wait(self.h, flags.handle, word, value & 0xFFFFFFFF, status.handle))
+
+    def forward_rows(self, host_ptr: int, row_bytes: int, affine: bool, first_row: int, rows: int, dst: Buffer) -> None:
+        """rvs_forward_rows: rows of an imported host block -> the same rows of `dst` (a peer's private buffer)"""
+        _check(self.lib, self.lib.rvs_forward_rows(self.h, C.c_void_p(host_ptr), row_bytes, 1 if affine else 0, first_row, rows, dst.handle))
+
     def wrap_pointer(self, ptr: int, nbytes: int, keepalive=None) -> Buffer:
         """Register device memory owned elsewhere (another context of the same device) as a buffer of this context."""
         out = C.c_uint32()

@@ -194,6 +194,7 @@ int rve_ctx_create(int device_ordinal, void* cuda_stream, rve_ctx** out_ctx) {
     rc = check_cuda(cudaMalloc(reinterpret_cast<void**>(&ctx->d_gather_ticket), 2 * sizeof(uint32_t)), "cudaMalloc");
     if (rc == 0) rc = check_cuda(cudaMemset(ctx->d_gather_ticket, 0, 2 * sizeof(uint32_t)), "cudaMemset");
     if (rc == 0) rc = p2p_preload();
+    if (rc == 0) rc = sync_preload();
     if (rc) {
         delete ctx;
         return rc;

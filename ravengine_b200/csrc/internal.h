@@ -126,7 +126,8 @@ struct rve_ctx {
 namespace rve {
 
 int set_error(int code, const char* fmt, ...);
-int p2p_preload();  // p2p.cu: forces the exchange / gather kernels to be loaded
+int p2p_preload();   // p2p.cu: forces the exchange / gather kernels to be loaded
+int sync_preload();  // sync.cu: the same for the flag and row-forwarding kernels
 int check_cuda(cudaError_t e, const char* what);
 // resolves a handle; returns nullptr (and sets the error) when invalid
 BufferRec* get_buffer(rve_ctx* ctx, rve_buffer h, const char* role);

@@ -12,6 +12,10 @@
 // flags at a time. Both modes leave the private buffer byte-identical to the host buffer.
 #include <cstring>
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include "frame_internal.h"
 #include "internal.h"
 
@@ -287,6 +291,9 @@ struct rvs_vector {
     uint32_t elemBytes = 0;     // host row
     uint32_t devElemBytes = 0;  // private-buffer row: elemBytes, or 64 for affine rows (48-B host rows)
     bool affine = false;
+    bool sharedHost = false;  // RVS_VECTOR_SHARED_HOST: the host block is a memfd mapping another rank can map and pin too
+    int hostFd = -1;
+    size_t hostMapBytes = 0;
     bool anyDirty = false;  // some flag may be set (SetValueAt / mark / a caller holding the tracking pointer): a clean vector syncs for free
     uint32_t count = 0, capacity = 0;
     unsigned char* host = nullptr;  // pinned: VRAMVector's host-mapped Shared buffer
@@ -330,7 +337,32 @@ int vec_reserve(rvs_vector* v, uint32_t newCap) {
     if (newCap <= v->capacity) return 0;
     DeviceGuard g(v->ctx->device);
     unsigned char* nh = nullptr;
-    RVE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&nh), size_t(newCap) * v->elemBytes, cudaHostAllocDefault));
+    if (v->sharedHost) {
+        // one allocation for the vector's life: peers hold a mapping of this very block
+        if (v->host) return set_error(RVE_ERR_UNSUPPORTED, "a shared-host vector cannot grow past its first size");
+        const size_t bytes = (size_t(newCap) * v->elemBytes + 4095) & ~size_t(4095);
+        const int fd = memfd_create("rvs_vector", 0);
+        if (fd < 0 || ftruncate(fd, off_t(bytes)) != 0) {
+            if (fd >= 0) close(fd);
+            return set_error(RVE_ERR_OUT_OF_MEMORY, "memfd_create / ftruncate failed for a shared-host vector");
+        }
+        void* m = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+        if (m == MAP_FAILED) {
+            close(fd);
+            return set_error(RVE_ERR_OUT_OF_MEMORY, "mmap failed for a shared-host vector");
+        }
+        const int rc = check_cuda(cudaHostRegister(m, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped), "cudaHostRegister");
+        if (rc) {
+            munmap(m, bytes);
+            close(fd);
+            return rc;
+        }
+        nh = static_cast<unsigned char*>(m);
+        v->hostFd = fd;
+        v->hostMapBytes = bytes;
+    } else {
+        RVE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&nh), size_t(newCap) * v->elemBytes, cudaHostAllocDefault));
+    }
     if (v->host) {
         // copies enqueued from the old block must have been consumed before it is released
         RVE_CUDA(cudaStreamSynchronize(v->ctx->stream));
@@ -402,13 +434,14 @@ int rvs_vector_create(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, rvs_vec
 int rvs_vector_create_ex(rve_ctx* ctx, uint32_t elem_bytes, uint32_t count, uint32_t flags, rvs_vector** out) {
     if (!ctx || !out) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
     RVE_REQUIRE(elem_bytes == 2 || (elem_bytes % 4 == 0 && elem_bytes > 0), "element size must be 2 or a multiple of 4 bytes");
-    RVE_REQUIRE(!(flags & ~RVS_VECTOR_AFFINE_ROWS), "unknown vector flags");
+    RVE_REQUIRE(!(flags & ~(RVS_VECTOR_AFFINE_ROWS | RVS_VECTOR_SHARED_HOST)), "unknown vector flags");
     RVE_REQUIRE(!(flags & RVS_VECTOR_AFFINE_ROWS) || elem_bytes == 48, "affine rows are 48-byte mat4x3 host rows");
     auto* v = new rvs_vector();
     v->ctx = ctx;
     v->elemBytes = elem_bytes;
     v->affine = (flags & RVS_VECTOR_AFFINE_ROWS) != 0;
     v->devElemBytes = v->affine ? 64u : elem_bytes;
+    v->sharedHost = (flags & RVS_VECTOR_SHARED_HOST) != 0;
     {
         DeviceGuard g(ctx->device);
         if (cudaEventCreateWithFlags(&v->stageFree, cudaEventDisableTiming) != cudaSuccess ||
@@ -438,7 +471,13 @@ int rvs_vector_destroy(rvs_vector* v) {
     if (v->evBegin) cudaEventDestroy(v->evBegin);
     if (v->evDone) cudaEventDestroy(v->evDone);
     for (cudaEvent_t e : v->evChunk) cudaEventDestroy(e);
-    if (v->host) cudaFreeHost(v->host);
+    if (v->host && v->sharedHost) {
+        cudaHostUnregister(v->host);
+        munmap(v->host, v->hostMapBytes);
+        close(v->hostFd);
+    } else if (v->host) {
+        cudaFreeHost(v->host);
+    }
     if (v->stageHost) cudaFreeHost(v->stageHost);
     if (v->stageFree) cudaEventDestroy(v->stageFree);
     for (int i = 0; i < 2; ++i) {
@@ -520,19 +559,29 @@ uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max
 }
 
 // RVS_SYNC_FULL / RVS_SYNC_FULL_PULL: every row goes up, flags are not consulted (and cleared when any may be set)
-static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st) {
+static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st, uint32_t rowBegin = 0, uint32_t rowEnd = 0xFFFFFFFFu) {
     rve_ctx* ctx = v->ctx;
-    auto* dev = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
-    if (!dev) return RVE_ERR_BAD_HANDLE;
+    auto* dev0 = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->priv));
+    if (!dev0) return RVE_ERR_BAD_HANDLE;
+    if (rowEnd > v->count) rowEnd = v->count;
+    if (rowBegin >= rowEnd) return 0;
     const size_t eb = v->elemBytes;
-    const size_t bytes = size_t(v->count) * eb;
-    const bool chunked16 = (eb % 16 == 0) && ((reinterpret_cast<uintptr_t>(v->host) | reinterpret_cast<uintptr_t>(dev)) & 15) == 0;
+    // the rows [rowBegin, rowEnd) as a vector of their own
+    struct Sub {
+        unsigned char* host;
+        unsigned char* dev;
+        uint32_t count;
+    } sub{v->host + size_t(rowBegin) * eb, dev0 + size_t(rowBegin) * v->devElemBytes, rowEnd - rowBegin};
+    unsigned char* dev = sub.dev;
+    const size_t bytes = size_t(sub.count) * eb;
+    const bool whole = rowBegin == 0 && rowEnd == v->count;
+    const bool chunked16 = (eb % 16 == 0) && ((reinterpret_cast<uintptr_t>(sub.host) | reinterpret_cast<uintptr_t>(dev)) & 15) == 0;
     if (mode == RVS_SYNC_FULL_PULL && (v->affine || chunked16)) {
         // one kernel reads the pinned host rows over PCIe and writes the private rows: no copy-engine operation, no staging
-        const int rc = launch_full(ctx, ctx->stream, v->host, dev, v->count, v->elemBytes, v->affine);
+        const int rc = launch_full(ctx, ctx->stream, sub.host, dev, sub.count, v->elemBytes, v->affine);
         if (rc) return rc;
     } else if (!v->affine) {
-        RVE_CUDA(cudaMemcpyAsync(dev, v->host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+        RVE_CUDA(cudaMemcpyAsync(dev, sub.host, bytes, cudaMemcpyHostToDevice, ctx->stream));
         st->direct_copies = 1;
     } else {
         // copy engine -> device staging (48-B rows) in chunks on a copy stream; each chunk is expanded into the 64-B
@@ -553,9 +602,9 @@ static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st) {
             if (rc) return rc;
             v->fullStageBytes = want;
         }
-        auto* stage = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->fullStage));
+        auto* stage = static_cast<unsigned char*>(rve_buffer_device_ptr(ctx, v->fullStage)) + size_t(rowBegin) * eb;
         constexpr uint32_t kChunkRows = 1u << 20;  // 48 MB per copy: ~0.9 ms on the link, ~25 us to expand
-        const uint32_t nChunks = (v->count + kChunkRows - 1) / kChunkRows;
+        const uint32_t nChunks = (sub.count + kChunkRows - 1) / kChunkRows;
         while (v->evChunk.size() < nChunks) {
             cudaEvent_t e;
             RVE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -567,8 +616,8 @@ static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st) {
         RVE_CUDA(cudaStreamWaitEvent(v->expandStream, v->evBegin, 0));
         for (uint32_t c = 0; c < nChunks; ++c) {
             const uint32_t r0 = c * kChunkRows;
-            const uint32_t rows = v->count - r0 < kChunkRows ? v->count - r0 : kChunkRows;
-            RVE_CUDA(cudaMemcpyAsync(stage + size_t(r0) * eb, v->host + size_t(r0) * eb, size_t(rows) * eb, cudaMemcpyHostToDevice, v->copyStream));
+            const uint32_t rows = sub.count - r0 < kChunkRows ? sub.count - r0 : kChunkRows;
+            RVE_CUDA(cudaMemcpyAsync(stage + size_t(r0) * eb, sub.host + size_t(r0) * eb, size_t(rows) * eb, cudaMemcpyHostToDevice, v->copyStream));
             RVE_CUDA(cudaEventRecord(v->evChunk[c], v->copyStream));
             RVE_CUDA(cudaStreamWaitEvent(v->expandStream, v->evChunk[c], 0));
             const int rc = launch_full(ctx, v->expandStream, stage + size_t(r0) * eb, dev + size_t(r0) * 64, rows, v->elemBytes, true);
@@ -579,11 +628,11 @@ static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st) {
         st->direct_copies = nChunks;
     }
     st->direct_bytes = bytes;
-    st->rows_in_ranges = v->count;
+    st->rows_in_ranges = sub.count;
     st->ranges = 1;
-    v->ranges.assign({0u, v->count});
-    if (v->anyDirty) std::memset(v->track, 0, v->count);
-    v->anyDirty = false;
+    v->ranges.assign({rowBegin, rowEnd});
+    if (v->anyDirty) std::memset(v->track + rowBegin, 0, sub.count);
+    if (whole) v->anyDirty = false;
     pyramid_note_buffer_write(ctx, v->priv);
     return 0;
 }
@@ -877,5 +926,139 @@ int rvs_sparse_set_erase_many(rvs_sparse_set* s, const uint32_t* sparse_indices,
 const uint32_t* rvs_sparse_set_dense(rvs_sparse_set* s) { return s ? static_cast<const uint32_t*>(rvs_vector_host(s->dense)) : nullptr; }
 const uint32_t* rvs_sparse_set_reverse_map(rvs_sparse_set* s) { return s && !s->reverse.empty() ? s->reverse.data() : nullptr; }
 rvs_vector* rvs_sparse_set_vector(rvs_sparse_set* s) { return s ? s->dense : nullptr; }
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------
+// Upload forwarding between ranks of one box (rve_shim.h): shared host blocks, flags, the forwarding copy
+// ---------------------------------------------------------------------------------------------------------
+namespace rve {
+
+__global__ void flag_signal_kernel(uint32_t* word, uint32_t value) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(word), "r"(value) : "memory");
+}
+
+__global__ void flag_wait_kernel(const uint32_t* word, uint32_t value, uint32_t* status, unsigned long long timeoutCycles) {
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(word) : "memory");
+        if (int32_t(v - value) >= 0) break;
+        if (uint64_t(clock64() - t0) > timeoutCycles) {
+            atomicOr(status, 1u);
+            break;
+        }
+        __nanosleep(200);
+    }
+}
+
+// loaded when the context is created: a first (lazy-loading) launch of one of these while a peer's wait kernel already spins
+// on this device would stall until that wait times out (see p2p_preload)
+int sync_preload() {
+    cudaFuncAttributes a{};
+    RVE_CUDA(cudaFuncGetAttributes(&a, flag_signal_kernel));
+    RVE_CUDA(cudaFuncGetAttributes(&a, flag_wait_kernel));
+    RVE_CUDA(cudaFuncGetAttributes(&a, full_rows_kernel<true>));
+    RVE_CUDA(cudaFuncGetAttributes(&a, full_rows_kernel<false>));
+    return 0;
+}
+
+}  // namespace rve
+
+extern "C" {
+
+int rvs_vector_encode_sync_rows(rvs_vector* v, uint32_t mode, uint32_t row_begin, uint32_t row_end, rvs_sync_stats* stats) {
+    if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
+    RVE_PROFILE_FN_N("EncodeSync");
+    RVE_REQUIRE(mode == RVS_SYNC_FULL || mode == RVS_SYNC_FULL_PULL, "row-range syncs are whole-row uploads (RVS_SYNC_FULL / _FULL_PULL)");
+    RVE_REQUIRE(row_begin <= row_end && row_end <= v->count, "row range out of bounds");
+    RVE_REQUIRE(v->priv != RVE_BUFFER_INVALID && v->privBytes == size_t(v->capacity) * v->devElemBytes,
+                "sync the whole vector once before row-range syncs (the private buffer does not exist yet)");
+    DeviceGuard g(v->ctx->device);
+    rvs_sync_stats st{};
+    const int rc = sync_full(v, mode, &st, row_begin, row_end);
+    if (stats) *stats = st;
+    return rc;
+}
+
+int rvs_vector_share(rvs_vector* v, int32_t* pid, int32_t* fd, uint64_t* bytes) {
+    if (!v || !pid || !fd || !bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_REQUIRE(v->sharedHost && v->host, "not a RVS_VECTOR_SHARED_HOST vector (or still empty)");
+    *pid = int32_t(getpid());
+    *fd = v->hostFd;
+    *bytes = v->hostMapBytes;
+    return 0;
+}
+
+int rve_host_import(rve_ctx* ctx, int32_t pid, int32_t fd, uint64_t bytes, void** out_ptr) {
+    if (!ctx || !out_ptr) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    char path[64];
+    snprintf(path, sizeof(path), "/proc/%d/fd/%d", int(pid), int(fd));
+    const int myfd = open(path, O_RDWR);
+    if (myfd < 0) return set_error(RVE_ERR_INVALID_ARGUMENT, "cannot open %s (the owner's host block)", path);
+    void* m = mmap(nullptr, bytes, PROT_READ | PROT_WRITE, MAP_SHARED, myfd, 0);
+    close(myfd);  // the mapping keeps the memory alive
+    if (m == MAP_FAILED) return set_error(RVE_ERR_OUT_OF_MEMORY, "mmap of the owner's host block failed");
+    const int rc = check_cuda(cudaHostRegister(m, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped), "cudaHostRegister");
+    if (rc) {
+        munmap(m, bytes);
+        return rc;
+    }
+    *out_ptr = m;
+    return 0;
+}
+
+int rve_host_release(rve_ctx* ctx, void* ptr, uint64_t bytes) {
+    if (!ctx || !ptr) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    RVE_CUDA(cudaStreamSynchronize(ctx->stream));
+    cudaHostUnregister(ptr);
+    munmap(ptr, bytes);
+    return 0;
+}
+
+int rve_flag_signal(rve_ctx* ctx, rve_buffer flags, uint32_t word, uint32_t value) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    BufferRec* b = get_buffer(ctx, flags, "flags");
+    if (!b) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE((uint64_t(word) + 1) * 4 <= b->bytes, "flag word outside the buffer");
+    flag_signal_kernel<<<1, 1, 0, ctx->stream>>>(static_cast<uint32_t*>(b->ptr) + word, value);
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int rve_flag_wait(rve_ctx* ctx, rve_buffer flags, uint32_t word, uint32_t value, rve_buffer status) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    BufferRec* b = get_buffer(ctx, flags, "flags");
+    BufferRec* s = get_buffer(ctx, status, "status");
+    if (!b || !s) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE((uint64_t(word) + 1) * 4 <= b->bytes && s->bytes >= 4, "flag word outside the buffer");
+    flag_wait_kernel<<<1, 1, 0, ctx->stream>>>(static_cast<const uint32_t*>(b->ptr) + word, value, static_cast<uint32_t*>(s->ptr), 4000000000ull);
+    ctx->launches++;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+int rvs_forward_rows(rve_ctx* ctx, const void* host_rows, uint32_t row_bytes, uint32_t affine, uint64_t first_row, uint64_t rows, rve_buffer dst) {
+    if (!ctx || !host_rows) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_PROFILE_FN_N("EncodeSync (forwarded rows)");
+    DeviceGuard g(ctx->device);
+    if (!rows) return 0;
+    BufferRec* d = get_buffer(ctx, dst, "forward destination");
+    if (!d) return RVE_ERR_BAD_HANDLE;
+    const uint32_t devRow = affine ? 64u : row_bytes;
+    RVE_REQUIRE(!affine || row_bytes == 48, "affine rows are 48-byte host rows");
+    RVE_REQUIRE(affine || row_bytes % 16 == 0, "forwarded rows are copied in 16-byte chunks");
+    RVE_REQUIRE((first_row + rows) * devRow <= d->bytes, "forwarded rows past the end of the destination");
+    const auto* src = static_cast<const unsigned char*>(host_rows) + first_row * row_bytes;
+    auto* out = static_cast<unsigned char*>(d->ptr) + first_row * devRow;
+    RVE_REQUIRE(((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(out)) & 15) == 0, "forwarded rows must start 16-byte aligned");
+    return launch_full(ctx, ctx->stream, src, out, rows, row_bytes, affine != 0);
+}
 
 }  // extern "C"

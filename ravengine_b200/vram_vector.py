@@ -16,12 +16,26 @@ SYNC_FULL, SYNC_FULL_PULL = _abi.SYNC_FULL, _abi.SYNC_FULL_PULL
 
 
 class BufferedVRAMVector:
-    def __init__(self, ctx: Context, elem_bytes: int, count: int = 0, affine_rows: bool = False):
-        """affine_rows: host rows are 48-B mat4x3 (columns c0..c3, xyz each); the private buffer keeps 64-B mat4 rows."""
+    def __init__(self, ctx: Context, elem_bytes: int, count: int = 0, affine_rows: bool = False, shared_host: bool = False):
+        """affine_rows: host rows are 48-B mat4x3 (columns c0..c3, xyz each); the private buffer keeps 64-B mat4 rows.
+        shared_host: the host block is a memfd mapping another rank can map and pin (share() / Context.host_import)."""
         self.ctx, self.elem_bytes, self.affine_rows = ctx, elem_bytes, affine_rows
         h = C.c_void_p()
-        _check(ctx.lib, ctx.lib.rvs_vector_create_ex(ctx.h, elem_bytes, count, _abi.VECTOR_AFFINE_ROWS if affine_rows else 0, C.byref(h)))
+        flags = (_abi.VECTOR_AFFINE_ROWS if affine_rows else 0) | (_abi.VECTOR_SHARED_HOST if shared_host else 0)
+        _check(ctx.lib, ctx.lib.rvs_vector_create_ex(ctx.h, elem_bytes, count, flags, C.byref(h)))
         self.h = h
+
+    def share(self) -> tuple[int, int, int]:
+        """(pid, fd, mapped bytes) of a shared_host vector's host block"""
+        pid, fd, nb = C.c_int32(), C.c_int32(), C.c_uint64()
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_share(self.h, C.byref(pid), C.byref(fd), C.byref(nb)))
+        return pid.value, fd.value, nb.value
+
+    def encode_sync_rows(self, mode: int, row_begin: int, row_end: int) -> _abi.SyncStats:
+        """whole-row upload (SYNC_FULL / SYNC_FULL_PULL) of rows [row_begin, row_end) only"""
+        st = _abi.SyncStats()
+        _check(self.ctx.lib, self.ctx.lib.rvs_vector_encode_sync_rows(self.h, mode, row_begin, row_end, C.byref(st)))
+        return st
 
     def __len__(self) -> int:
         return self.ctx.lib.rvs_vector_size(self.h)

@@ -191,3 +191,54 @@ def test_full_modes_and_clean_vectors(ctx, elem_bytes, dtype):
         v.encode_sync(SYNC_PACKED)
         assert np.array_equal(v.private_buffer.download(dtype).reshape(-1, per)[:n], h2)
         v.destroy()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("affine", [True, False])
+def test_forwarded_rows_land_in_the_owner_s_private_buffer(ctx, affine):
+    """Upload forwarding (rve_shim.h): the owner uploads rows [0, k) of a shared-host vector itself, a helper context (here:
+    a second stream of the same device, the host block mapped a second time through /proc/self/fd) reads rows [k, n) from
+    the shared block and writes them into the owner's private buffer, ordered by the two flags of the protocol. The
+    private buffer must equal a plain full upload, frame after frame."""
+    import torch
+
+    from ravengine_b200 import Context, scenes
+    from ravengine_b200.vram_vector import SYNC_FULL, BufferedVRAMVector
+
+    n, k = 300_007, 180_000
+    eb, per = (48, 12) if affine else (64, 16)
+    rng = np.random.default_rng(5)
+    v = BufferedVRAMVector(ctx, eb, n, affine_rows=affine, shared_host=True)
+    s2 = torch.cuda.Stream()
+    helper = Context(ctx.device, s2.cuda_stream)
+    pid, fd, nbytes = v.share()
+    host_ptr = helper.host_import(pid, fd, nbytes)
+    flags_owner, flags_helper = ctx.create_buffer(64), ctx.create_buffer(64)  # [0] "free" lives with the helper, [1] "landed" with the owner
+    status = [ctx.create_buffer(16), helper.create_buffer(16)]
+    h = v.host(np.float32).reshape(n, per)
+    m64 = scenes.random_transforms(rng, n, 100.0, 10.0).reshape(n, 16)
+    h[:] = _affine48(m64) if affine else m64
+    v.encode_sync(SYNC_FULL)  # creates the private buffer
+    ctx.synchronize()
+    dst_h = helper.wrap_pointer(v.private_buffer.ptr, v.private_buffer.nbytes)
+    f_helper_view = helper.wrap_pointer(flags_helper.ptr, 64)
+    f_owner_view = helper.wrap_pointer(flags_owner.ptr, 64)
+    for epoch in range(1, 4):
+        m64 = scenes.random_transforms(rng, n, 100.0, 10.0).reshape(n, 16)
+        h[:] = _affine48(m64) if affine else m64
+        # helper first (as a faster rank would be): it must wait for the owner's "free" signal
+        helper.flag_wait(f_helper_view, 0, epoch, status[1])
+        helper.forward_rows(host_ptr, eb, affine, k, n - k, dst_h)
+        helper.flag_signal(f_owner_view, 1, epoch)
+        # owner: "my private buffer is free for this frame", own rows, wait for the forwarded rows
+        ctx.flag_signal(flags_helper, 0, epoch)
+        v.encode_sync_rows(SYNC_FULL, 0, k)
+        ctx.flag_wait(flags_owner, 1, epoch, status[0])
+        ctx.synchronize()
+        helper.synchronize()
+        got = v.private_buffer.download(np.float32).reshape(-1, 16)[:n]
+        assert got.tobytes() == m64.tobytes()
+        assert status[0].download(np.uint32)[0] == 0 and status[1].download(np.uint32)[0] == 0
+    helper.host_release(host_ptr, nbytes)
+    helper.close()
+    v.destroy()
