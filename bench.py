@@ -650,12 +650,12 @@ class HostScene:
     64-B mat4 rows), renderLayers, perObjectAttributes and the entity-id list. Created after the thread was bound to
     the GPU's NUMA node, so the pinned pages are local to the GPU's PCIe root."""
 
-    def __init__(self, sc: DeviceScene, affine: bool):
+    def __init__(self, sc: DeviceScene, affine: bool, shared_host: bool = False):
         from ravengine_b200.vram_vector import SYNC_FULL, BufferedVRAMVector
 
         n, ctx = sc.n, sc.ctx
         self.sc, self.affine = sc, affine
-        self.model = BufferedVRAMVector(ctx, 48 if affine else 64, n, affine_rows=affine)
+        self.model = BufferedVRAMVector(ctx, 48 if affine else 64, n, affine_rows=affine, shared_host=shared_host)
         host = self.model.host(np.float32).reshape(n, 12 if affine else 16)
         for a in range(0, n, 1 << 20):  # device -> pinned host in 1 M-row pieces (no second host copy of the scene)
             rows = sc.t_model[a:a + (1 << 20)]
@@ -784,6 +784,21 @@ def run_e2e(sc: DeviceScene, args, torch, barrier, dist, affinity):
             out["by_dirty_fraction"] = run_e2e_dirty(sc, hs, args, torch, barrier, dist)
         hs.close()
     e2e = dict(out["affine48"])
+    if dist and not args.no_balance:
+        bal = run_e2e_balanced(sc, args, torch, barrier, dist, out["affine48"]["h2d_gbs_upload_alone_by_rank"], out["affine48"]["visible"])
+        if bal is None:
+            e2e["forwarding"] = "not used: every rank's upload rate is within 15 % of every other's"
+        elif bal["verified"] and bal["value"] > e2e["value"]:
+            plain = {k: e2e[k] for k in ("value", "ms_per_step", "ms_per_step_by_rank", "h2d_gbs_achieved", "h2d_gbs_upload_alone_by_rank")}
+            for k in ("value", "ms_per_step", "ms_per_step_by_rank", "steps"):
+                e2e[k] = bal[k]
+            e2e["h2d_gbs_achieved"] = e2e["h2d_bytes_per_step"] / (bal["ms_per_step"] * 1e-3) / 1e9
+            e2e["forwarding"] = {"used": True, "verified": True, "pairs": bal["pairs"], "upload": bal["upload"], "without_forwarding": plain,
+                                 "note": "ranks behind the slower host links upload the head of their rows; their partner on a faster link reads the "
+                                         "tail from the owner's (shared, pinned) host block over its own PCIe link and writes it into the owner's "
+                                         "private buffer over NVLink; same bytes per rank per step"}
+        else:
+            e2e["forwarding"] = {"used": False, "verified": bal["verified"], "balanced_ms_per_step": bal["ms_per_step"], "pairs": bal["pairs"]}
     e2e["dirty_fraction"] = 1.0
     e2e["note"] = ("per step: 100 % of the transforms re-uploaded from pinned host memory as 48-B affine rows (expanded to the reference's "
                    "64-B mat4 layout on the device; exact h2d_bytes_per_step = 48 x instances), renderLayers / perObjectAttributes / entity "
@@ -798,6 +813,114 @@ def run_e2e(sc: DeviceScene, args, torch, barrier, dist, affinity):
         e2e["by_dirty_fraction_note"] = ("same step, only rows flagged since the last frame are uploaded (the reference's EncodeSync policy, "
                                          "GPU-pull variant: one kernel reads the flags and the flagged 48-B rows over PCIe); keys = fraction flagged per step")
     return e2e
+
+
+def pair_ranks(rates: list[float], min_ratio: float = 1.15) -> dict[int, tuple[int, str]]:
+    """Upload forwarding plan from the per-rank upload rates measured with every rank uploading at once: the i-th slowest
+    rank is paired with the i-th fastest while the faster link is at least `min_ratio` x the slower one.
+    Returns {rank: (partner, "owner" | "helper")}; ranks without an entry upload on their own."""
+    order = sorted(range(len(rates)), key=lambda r: (rates[r], r))
+    plan = {}
+    for i in range(len(order) // 2):
+        slow, fast = order[i], order[-1 - i]
+        if rates[slow] > 0 and rates[fast] / rates[slow] >= min_ratio:
+            plan[slow], plan[fast] = (fast, "owner"), (slow, "helper")
+    return plan
+
+
+def run_e2e_balanced(sc: DeviceScene, args, torch, barrier, dist, rates: list[float], want_visible: int):
+    """The headline e2e leg with upload forwarding: ranks behind a slow host link (on the pool's 8-GPU
+    boxes GPUs 0-3 share one path to host memory) upload only the head of their transform rows; a partner rank on a fast link
+    maps the owner's host block, reads the tail over ITS PCIe link and writes it, expanded, into the owner's private buffer
+    over NVLink, concurrently with its own upload. Per step and pair: owner signals "private buffer free", helper forwards
+    and signals "rows landed", owner's cull waits for that flag. Bytes per step per rank are unchanged (48 x instances)."""
+    from ravengine_b200 import Context
+    from ravengine_b200.vram_vector import SYNC_FULL, SYNC_PULL
+
+    rank, ws = dist.get_rank(), dist.get_world_size()
+    n, ctx, lib = sc.n, sc.ctx, sc.ctx.lib
+    if os.environ.get("RVE_BENCH_FAKE_RATES"):  # development: exercise the forwarding path on a box whose links are equal
+        rates = [float(x) for x in os.environ["RVE_BENCH_FAKE_RATES"].split(",")][:ws]
+    plan = pair_ranks(rates)
+    if not plan:
+        return None
+    hs = HostScene(sc, True, shared_host=True)
+    flags, status = ctx.create_buffer(64), ctx.create_buffer(16)
+    flags.zero()
+    status.zero()
+    ctx.synchronize()
+    pid, fd, nbytes = hs.model.share()
+    priv = hs.model.private_buffer
+    mine = {"pid": pid, "fd": fd, "bytes": nbytes, "flags": ctx.ipc_export(flags), "priv": ctx.ipc_export(priv), "priv_bytes": priv.nbytes}
+    everyone = [None] * ws
+    dist.all_gather_object(everyone, mine)
+    role = plan.get(rank)
+    k = n
+    hctx = hstream = host_ptr = peer_priv = peer_flags = my_flags_h = hstatus = None
+    if role:
+        partner, what = role
+        slow, fast = (rank, partner) if what == "owner" else (partner, rank)
+        k = int(2 * n * rates[slow] / (rates[slow] + rates[fast]))  # rows the owner keeps: both links finish together
+        k = max(0, min(n, k // 64 * 64))
+        info = everyone[partner]
+        if what == "owner":
+            peer_flags = ctx.ipc_import(info["flags"], 64)
+        else:
+            hstream = torch.cuda.Stream(device=torch.device("cuda", ctx.device))
+            hctx = Context(ctx.device, hstream.cuda_stream)
+            host_ptr = hctx.host_import(info["pid"], info["fd"], info["bytes"])
+            peer_priv = hctx.ipc_import(info["priv"], info["priv_bytes"])
+            peer_flags = hctx.ipc_import(info["flags"], 64)
+            my_flags_h = hctx.wrap_pointer(flags.ptr, 64)
+            hstatus = hctx.wrap_pointer(status.ptr, 16)
+    outs = [sc.world.material_outputs(m)[1] for m in sc.mats]
+    lods = len(C2["lod_distances"])
+    res = [np.zeros(lods * 5, np.uint32) for _ in outs]
+    epoch = [0]
+
+    def step(_i):
+        epoch[0] += 1
+        e = epoch[0]
+        if role and role[1] == "helper":  # first: the partner's tail rows start crossing this rank's link right away
+            hctx.flag_wait(my_flags_h, 0, e, hstatus)
+            hctx.forward_rows(host_ptr, 48, True, k, n - k, peer_priv)
+            hctx.flag_signal(peer_flags, 1, e)
+        if role and role[1] == "owner":
+            ctx.flag_signal(peer_flags, 0, e)  # behind last frame's cull on this stream: the private buffer is free
+            hs.model.encode_sync_rows(SYNC_FULL, 0, k)
+        else:
+            hs.model.encode_sync(SYNC_FULL)
+        hs.layers.encode_sync(SYNC_PULL)
+        hs.flags.encode_sync(SYNC_PULL)
+        hs.ids.encode_sync(SYNC_PULL)
+        if role and role[1] == "owner":
+            ctx.flag_wait(flags, 1, e, status)  # the forwarded rows have landed
+        sc.step()
+        for ind, r in zip(outs, res):
+            rc = lib.rve_buffer_download(ctx.h, ind.handle, 0, r.ctypes.data, r.nbytes)  # synchronises the stream
+            assert rc == 0
+
+    steps = max(2, min(args.steps, 10))
+    dt, _, by_rank = _timed_host_loop(step, steps, barrier, torch, dist)
+    visible = int(np.concatenate([r.reshape(-1, 5)[:, 1] for r in res]).sum())
+    # checks: same visible set as the unbalanced leg, no timeout, and the forwarded rows are the host rows (sampled)
+    ok = visible == want_visible and int(status.download(np.uint32)[0]) == 0
+    if role and role[1] == "owner" and k < n:
+        got = priv.download(np.float32, offset=64 * (n - 1000), nbytes=64 * 1000).reshape(1000, 16)
+        want = hs.model.host(np.float32).reshape(n, 12)[n - 1000:]
+        ok = ok and np.array_equal(got.reshape(1000, 4, 4)[:, :, :3].reshape(1000, 12), want) and np.all(got[:, 3::4] == np.array([0, 0, 0, 1], np.float32))
+    t_ok = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+    roles = [None] * ws
+    dist.all_gather_object(roles, {"rank": rank, "role": role[1] if role else "alone", "partner": role[0] if role else None, "own_rows": k})
+    barrier()
+    if hctx:
+        hctx.host_release(host_ptr, everyone[role[0]]["bytes"])
+        hctx.close()
+    hs.close()
+    return {"value": n * ws * steps / dt, "unit": "instances/s", "h2d_bytes_per_step": int(48 * n), "d2h_bytes_per_step": int(sum(r.nbytes for r in res)),
+            "ms_per_step": dt / steps * 1e3, "ms_per_step_by_rank": by_rank, "steps": steps, "visible": visible, "verified": bool(int(t_ok.item())),
+            "pairs": roles, "upload": "copy engine for a rank's own rows, one zero-copy kernel (partner's PCIe link -> NVLink) for forwarded rows"}
 
 
 def run_e2e_dirty(sc: DeviceScene, hs: HostScene, args, torch, barrier, dist, fractions=(0.10, 0.01)):
@@ -851,6 +974,7 @@ def main():
                     help="100 %-dirty transform upload: copy engine into staging + expand kernels (RVS_SYNC_FULL) or one zero-copy kernel (RVS_SYNC_FULL_PULL)")
     ap.add_argument("--e2e-headline-only", action="store_true", help="skip the by_layout / by_dirty_fraction e2e variants")
     ap.add_argument("--placement", default="spread", choices=["spread", "packed"], help="rank -> GPU mapping when the box has more GPUs than ranks")
+    ap.add_argument("--no-balance", action="store_true", help="N>1: never forward part of a slow rank's upload through a faster rank's link")
     ap.add_argument("--no-numa-bind", action="store_true", help="leave the process where the launcher put it (diagnostics)")
     ap.add_argument("--no-gather", action="store_true", help="N>1: skip the device-side id gather leg")
     ap.add_argument("--no-c5", action="store_true", help="skip the C5 sub-results (512 views / 1 B instances)")
