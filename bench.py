@@ -165,14 +165,14 @@ class DeviceScene:
     def step(self, before_cull=None):
         """one pass of the hot path for one view: pyramid build + table build/upload + indirect re-init + cull, as one encode
         (rvs_cull_static_with_pyramid); RVE_BENCH_SPLIT_STEP=1 issues the two reference-shaped calls instead"""
-        if os.environ.get("RVE_BENCH_SPLIT_STEP") == "1":
+        if before_cull or os.environ.get("RVE_BENCH_SPLIT_STEP") == "1":
+            # N > 1: the pyramid build does not touch the indirect buffers, so it is enqueued BEFORE the wait for last frame's
+            # count exchange (before_cull) and runs while the slowest peer catches up (the fused order cost 15 us per step at N = 8)
             self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
             if before_cull:
                 before_cull()
             self.world.cull_static(self.vp, self.cam_pos, self.pyr)
             return
-        if before_cull:
-            before_cull()
         self.world.cull_static_with_pyramid(self.vp, self.cam_pos, self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
 
     def visible_counts(self) -> np.ndarray:
