@@ -52,8 +52,9 @@ __device__ __forceinline__ float sample_min_src(const float* __restrict__ img, u
 // reduce `lv` (n x n, shared) into `out` (n/2 x n/2, shared) and global level
 __device__ __forceinline__ void reduce_level(const float* lv, uint32_t n_in, float* out, uint32_t n_out, float* __restrict__ gdst,
                                              uint32_t g_dim_out, uint32_t gx0, uint32_t gy0) {
+    const uint32_t sh = uint32_t(__ffs(int(n_out))) - 1u;  // n_out is a power of two
     for (uint32_t i = threadIdx.x; i < n_out * n_out; i += blockDim.x) {
-        const uint32_t x = i % n_out, y = i / n_out;
+        const uint32_t x = i & (n_out - 1u), y = i >> sh;
         const float a = lv[(2 * y) * n_in + 2 * x];
         const float b = lv[(2 * y) * n_in + 2 * x + 1];
         const float c = lv[(2 * y + 1) * n_in + 2 * x];
@@ -66,8 +67,11 @@ __device__ __forceinline__ void reduce_level(const float* lv, uint32_t n_in, flo
 
 // Everything a tile does after its (tile+1)^2 mip-0 samples sit in s_lv: level 0 of the footprint-min chain and the
 // in-tile mips 1..log2(tile), each written to the chain and reduced further from shared memory (depthpyramid.csh).
+// FULL: the tile is kPyrTile wide (index arithmetic with compile-time constants: the kernel is instruction-bound)
+template <bool FULL>
 __device__ __forceinline__ void tile_levels(float* s_lv, float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels,
-                                            uint32_t tile, uint32_t tx0, uint32_t ty0) {
+                                            uint32_t tileArg, uint32_t tx0, uint32_t ty0) {
+    const uint32_t tile = FULL ? uint32_t(kPyrTile) : tileArg;
     const uint32_t S = tile + 1;
     __syncthreads();
     {   // footprint-min level 0: F[fy][fx] = min of texels {fx-1,fx} x {fy-1,fy} (clamped), (dim+1)^2 entries
@@ -126,7 +130,7 @@ pyramid_build_kernel(const float* __restrict__ depth, uint32_t w, uint32_t h, fl
         s_lv[i] = m;
         if (lx < tile && ly < tile) pyr[uint64_t(y) * dim + x] = m;
     }
-    tile_levels(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
+    tile_levels<false>(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
     // levels above log2(tile) and the footprint-min levels >= 1: pyramid_upper_kernel
 }
 
@@ -198,29 +202,40 @@ pyramid_build_tma_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t 
         pyr::mbar_expect_tx(&s_bar, boxW * boxH * 4u);
         pyr::tma_load_box(s_src, &depthMap, int32_t(sx0), int32_t(sy0), &s_bar);
     }
-    __syncthreads();  // the barrier is initialised for everybody
+    // The footprints are separable: sample (x, y) reads source columns {fx0[x], fx1[x]} and rows {fy0[y], fy1[y]}. The 2 x 33
+    // pairs of the tile are derived once (box-local), while the tensor copy is in flight - the per-sample work shrinks
+    // from two IEEE divisions, two floors and two clamps to four table reads (the kernel was instruction-bound: ncu r02).
+    __shared__ uint16_t s_f[4][S];
+    if (threadIdx.x < 2 * S) {
+        const uint32_t axis = threadIdx.x / S, l = threadIdx.x % S;  // 0: x, 1: y
+        uint32_t t = (axis ? ty0 : tx0) + l;
+        t = t < dim ? t : dim - 1;
+        const uint32_t n = axis ? h : w;
+        const float u = (float(t) + 0.5f) / float(dim);
+        uint32_t i0, i1;
+        footprint(__fmaf_rn(u, float(n), -0.5f), n, i0, i1);
+        const uint32_t origin = axis ? sy0 : sx0;
+        s_f[2 * axis][l] = uint16_t(i0 - origin);
+        s_f[2 * axis + 1][l] = uint16_t(i1 - origin);
+    }
+    __syncthreads();  // the barrier is initialised and the tables are written for everybody
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     pyr::mbar_wait(&s_bar, 0);
 
-    for (uint32_t i = threadIdx.x; i < S * S; i += blockDim.x) {
+    for (uint32_t i = threadIdx.x; i < S * S; i += kPyrThreads) {
         const uint32_t lx = i % S, ly = i / S;
-        uint32_t x = tx0 + lx, y = ty0 + ly;
-        x = x < dim ? x : dim - 1;
-        y = y < dim ? y : dim - 1;
-        const float u = (float(x) + 0.5f) / float(dim);
-        const float v = (float(y) + 0.5f) / float(dim);
-        uint32_t x0, x1, y0, y1;
-        footprint(__fmaf_rn(u, float(w), -0.5f), w, x0, x1);
-        footprint(__fmaf_rn(v, float(h), -0.5f), h, y0, y1);
-        x0 -= sx0, x1 -= sx0, y0 -= sy0, y1 -= sy0;  // box-local (the host sized the box so that these fit)
-        const float a = s_src[y0 * boxW + x0], b = s_src[y0 * boxW + x1];
-        const float c = s_src[y1 * boxW + x0], d = s_src[y1 * boxW + x1];
-        const float m = gmin(gmin(a, b), gmin(c, d));
+        const uint32_t r0 = uint32_t(s_f[2][ly]) * boxW, r1 = uint32_t(s_f[3][ly]) * boxW;
+        const uint32_t c0 = s_f[0][lx], c1 = s_f[1][lx];
+        const float m = gmin(gmin(s_src[r0 + c0], s_src[r0 + c1]), gmin(s_src[r1 + c0], s_src[r1 + c1]));
         s_lv[i] = m;
-        if (lx < tile && ly < tile) pyr[uint64_t(y) * dim + x] = m;
+        if (lx < tile && ly < tile) pyr[uint64_t(ty0 + ly) * dim + (tx0 + lx)] = m;
     }
-    tile_levels(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
+    tile_levels<true>(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
 }
+
+struct PyrOffsets {  // start of every level in the texel chain (px) and in the footprint-min chain (fm); [levels] = total
+    uint32_t px[16], fm[16];
+};
 
 __device__ __forceinline__ float footmin_entry(const float* img, uint32_t n, uint32_t fx, uint32_t fy) {
     const uint32_t x0 = fx ? fx - 1 : 0, x1 = fx < n ? fx : n - 1;
@@ -233,7 +248,8 @@ __device__ __forceinline__ float footmin_entry(const float* img, uint32_t n, uin
 // one thread per entry. Launched with programmatic stream serialization: everything before griddepcontrol.wait
 // overlaps the tail of pyramid_build_kernel.
 __global__ void __launch_bounds__(kPyrThreads)
-pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels, uint32_t topLevel, uint32_t earlyTrigger) {
+pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels, uint32_t topLevel, uint32_t earlyTrigger,
+                     const __grid_constant__ PyrOffsets offs) {
     __shared__ float s_lv[kPyrTile * kPyrTile + (kPyrTile * kPyrTile) / 3 + 2];
     // earlyTrigger (RVE_UPPER_TRIGGER=1, off by default): a cull enqueued behind the build becomes resident now and waits for
     // this grid before its first Hi-Z batch. Measured on B200 (profiles/r02_fused_variants.txt): the persistent cull then
@@ -263,8 +279,9 @@ pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t d
         }
         return;
     }
-    const uint32_t first = uint32_t(footmin_level_offset(dim, 1));
-    const uint32_t end = uint32_t(footmin_level_offset(dim, topLevel < levels ? topLevel : levels));
+    // level offsets come from the host (PyrOffsets): deriving them per thread costs 64-bit divisions by 3
+    const uint32_t lastFm = topLevel < levels ? topLevel : levels;
+    const uint32_t first = offs.fm[1], end = offs.fm[lastFm];
     // two entries per thread (i, i + blockDim.x): the whole grid is resident in one wave at dim 1024
     const uint32_t base = (blockIdx.x - 1) * (2 * blockDim.x) + threadIdx.x + first;
     uint32_t idx[2], n[2], fx[2], fy[2];
@@ -273,12 +290,12 @@ pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t d
     for (int k = 0; k < 2; ++k) {
         const uint32_t i = base + k * blockDim.x;
         uint32_t level = 1;
-        while (level + 1 < levels && i >= uint32_t(footmin_level_offset(dim, level + 1))) ++level;
+        while (level + 1 < levels && i >= offs.fm[level + 1]) ++level;
         n[k] = dim >> level;
-        const uint32_t local = i - uint32_t(footmin_level_offset(dim, level));
-        fx[k] = local % (n[k] + 1);
+        const uint32_t local = i - offs.fm[level];
         fy[k] = local / (n[k] + 1);
-        img[k] = pyr + pyr_level_offset(dim, level);
+        fx[k] = local - fy[k] * (n[k] + 1);
+        img[k] = pyr + offs.px[level];
         idx[k] = i;
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -464,7 +481,13 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
             cfg.attrs = &attr;
             cfg.numAttrs = 1;
             static const uint32_t early = [] { const char* e = getenv("RVE_UPPER_TRIGGER"); return (e && atoi(e) != 0) ? 1u : 0u; }();
-            RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel, early));
+            PyrOffsets offs{};
+            for (uint32_t l = 0; l <= p->levels && l < 16; ++l) {
+                const uint64_t d0 = p->dim, dl = l < 32 ? (p->dim >> l) : 0;
+                offs.px[l] = uint32_t(4ull * (d0 * d0 - dl * dl) / 3ull);
+                offs.fm[l] = uint32_t(footmin_level_offset(p->dim, l));
+            }
+            RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel, early, offs));
             ctx->launches++;
         }
     }
