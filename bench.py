@@ -905,15 +905,26 @@ def run_e2e_balanced(sc: DeviceScene, args, torch, barrier, dist, rates: list[fl
     steps = max(2, min(args.steps, 10))
     # The split computed from the rates assumes the links keep those rates once the bytes move; they do not quite (the copy
     # engine and the zero-copy kernel share the helper's link, the box has one ceiling for all links): try the computed
-    # share of forwarded rows and two neighbours in short loops, keep the best (every rank sees the same max-over-ranks time).
+    # share of forwarded rows and its neighbours in short loops (a small hill climb), keep the best.
     tried = {}
     if role:
         fwd0 = n - k
-    for bias in (1.0, 0.8, 1.2):
+    def try_bias(bias):
+        nonlocal k
         if role:
             k = max(0, min(n, (n - int(fwd0 * bias)) // 64 * 64))
         dt_b, _, _ = _timed_host_loop(step, 3, barrier, torch, dist)
-        tried[bias] = dt_b / 3 * 1e3
+        tried[bias] = dt_b / 3 * 1e3  # max over ranks: every rank takes the same decisions below
+
+    try_bias(1.0)
+    try_bias(1.2)
+    if tried[1.2] < tried[1.0]:  # more forwarding helps: keep going while it does
+        for bias in (1.4, 1.6, 1.8):
+            try_bias(bias)
+            if tried[bias] > min(v for b_, v in tried.items() if b_ != bias):
+                break
+    else:
+        try_bias(0.8)
     best_bias = min(tried, key=tried.get)
     if role:
         k = max(0, min(n, (n - int(fwd0 * best_bias)) // 64 * 64))
