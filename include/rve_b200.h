@@ -369,6 +369,20 @@ RVE_API int rve_cull(rve_ctx* ctx, const RveCullingUBO* ubo, rve_buffer cubos,
  * the limit are dropped. Bitmap pass (set bits, block counts, scan, expand): four small launches, no comparison sort. */
 RVE_API int rve_sort_entity_ids(rve_ctx* ctx, rve_buffer entity_ids, uint32_t count, uint32_t id_limit, rve_buffer sorted_out);
 
+/* rve_sort_entity_ids without any allocation. This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). Same arguments, same result as rve_sort_entity_ids, but the scratch (bitmap, block
+ * sums, out-of-range counter) is a fixed file-scope device array in csrc/sort_ids.cu sized for id spaces of up to
+ * RVE_SORT_STATIC_MAX_IDS ids (1 MiB + 1 KiB, held by every GPU that loads the library until the process exits). The call
+ * makes no cudaMalloc / cudaFree / allocating library call: it enqueues one memset and four kernels on the context's
+ * stream (the first call on a device also resolves the array's device address with cudaGetSymbolAddress - make one call
+ * before starting a capture). id_limit > RVE_SORT_STATIC_MAX_IDS returns RVE_ERR_UNSUPPORTED with nothing enqueued (use
+ * rve_sort_entity_ids). All calls on a device share the one array, from every context and stream: it is cleared at the start
+ * of each call, and calls that overlap on the GPU (different streams, or graphs replayed concurrently) race - serialise
+ * them. */
+#define RVE_SORT_STATIC_MAX_IDS 8388608u
+RVE_API int rve_sort_entity_ids_static(rve_ctx* ctx, rve_buffer entity_ids, uint32_t count, uint32_t id_limit, rve_buffer sorted_out);
+
 /* View-batched cull (SURVEY 8e partition B, 8f-2): the reference runs cullTheRenderData once per view of a frame
  * (main camera, every shadow cascade / spot / point face: src/RenderEngine_Draw.cpp:1769-1866, 1875-1987), each
  * pass re-reading every transform. Here one launch reads each instance ONCE and tests it against all `num_views`

@@ -186,6 +186,11 @@ class Context:
         """rve_sort_entity_ids: ascending copy of an entity-id list (the cull's result does not depend on list order)"""
         _check(self.lib, self.lib.rve_sort_entity_ids(self.h, ids.handle, count, id_limit, out.handle))
 
+    def sort_entity_ids_static(self, ids: Buffer, count: int, id_limit: int, out: Buffer) -> None:
+        """rve_sort_entity_ids_static: the same sort with its scratch in a fixed device array (no allocation; id_limit <=
+        RVE_SORT_STATIC_MAX_IDS; calls that overlap on the GPU race)"""
+        _check(self.lib, self.lib.rve_sort_entity_ids_static(self.h, ids.handle, count, id_limit, out.handle))
+
     def skin(self, ubo: SkinningUBO, outs: list[Buffer], ins: list[Buffer], pose: Buffer, weights: Buffer) -> None:
         o = (C.c_uint32 * 5)(*[b.handle for b in outs])
         i = (C.c_uint32 * 5)(*[b.handle for b in ins])

@@ -123,3 +123,73 @@ extern "C" int rve_sort_entity_ids(rve_ctx* ctx, rve_buffer entity_ids, uint32_t
     RVE_CUDA(cudaGetLastError());
     return 0;
 }
+
+// ---- rve_sort_entity_ids_static: the same bitmap pass with its scratch in a file-scope device array ----
+//
+// For callers that must not reach cudaMalloc (stream capture, serving loops, harnesses that forbid it). The scratch of
+// the largest id space the variant accepts (RVE_SORT_STATIC_MAX_IDS ids: bitmap words, block sums + total, the
+// out-of-range counter) lives in g_sort_static; every GPU that loads the library holds it until the process exits.
+// In host code `g_sort_static` is only a stand-in for the symbol: the kernels are given the device address that
+// cudaGetSymbolAddress reports, looked up once per device with that device current.
+namespace rve {
+
+constexpr uint32_t kStaticMaxIds = RVE_SORT_STATIC_MAX_IDS;
+constexpr uint32_t kStaticMaxWords = kStaticMaxIds / 32u;
+constexpr uint32_t kStaticMaxBlocks = kStaticMaxWords / kSortBlock;
+static_assert(kStaticMaxIds % (32u * kSortBlock) == 0, "RVE_SORT_STATIC_MAX_IDS must be a whole number of bitmap blocks");
+constexpr size_t kStaticWords = size_t(kStaticMaxBlocks) * kSortBlock + kStaticMaxBlocks + 2;
+
+static __device__ __align__(256) uint32_t g_sort_static[kStaticWords];
+
+constexpr int kStaticMaxDevices = 64;
+static std::mutex g_sort_static_mutex;
+static uint32_t* g_sort_static_addr[kStaticMaxDevices] = {};
+
+// device address of g_sort_static on `device` (which must be current); nullptr + error code on failure
+static int sort_static_address(int device, uint32_t** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return set_error(RVE_ERR_UNSUPPORTED, "device ordinal %d is past the %d this entry point tracks", device, kStaticMaxDevices);
+    std::lock_guard<std::mutex> lock(g_sort_static_mutex);
+    if (!g_sort_static_addr[device]) {
+        void* p = nullptr;
+        RVE_CUDA(cudaGetSymbolAddress(&p, g_sort_static));
+        if (!p) return set_error(RVE_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static sort scratch");
+        g_sort_static_addr[device] = static_cast<uint32_t*>(p);
+    }
+    *out = g_sort_static_addr[device];
+    return 0;
+}
+
+}  // namespace rve
+
+extern "C" int rve_sort_entity_ids_static(rve_ctx* ctx, rve_buffer entity_ids, uint32_t count, uint32_t id_limit, rve_buffer sorted_out) {
+    if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
+    DeviceGuard g(ctx->device);
+    if (count == 0) return 0;
+    BufferRec* bi = get_buffer(ctx, entity_ids, "entity ids");
+    BufferRec* bo = get_buffer(ctx, sorted_out, "sorted entity ids");
+    if (!bi || !bo) return RVE_ERR_BAD_HANDLE;
+    RVE_REQUIRE(uint64_t(count) * 4 <= bi->bytes && uint64_t(count) * 4 <= bo->bytes, "id buffers smaller than count entries");
+    RVE_REQUIRE(id_limit >= 1, "id_limit is the size of the entity id space (ids are < id_limit)");
+    if (id_limit > kStaticMaxIds)
+        return set_error(RVE_ERR_UNSUPPORTED, "rve_sort_entity_ids_static: id_limit %u is past RVE_SORT_STATIC_MAX_IDS (%u); use rve_sort_entity_ids", id_limit,
+                         kStaticMaxIds);
+    const uint32_t words = (id_limit + 31u) / 32u;
+    const uint32_t blocks = (words + kSortBlock - 1) / kSortBlock;
+    uint32_t* scratch = nullptr;
+    int rc = sort_static_address(ctx->device, &scratch);
+    if (rc) return rc;
+    // same layout as the allocating entry point, inside the fixed array
+    uint32_t* bitmap = scratch;
+    uint32_t* sums = bitmap + size_t(blocks) * kSortBlock;
+    uint32_t* bad = sums + blocks + 1;
+    // the array keeps the last call's contents: the bitmap and the counter must start at zero (the sums are overwritten)
+    RVE_CUDA(cudaMemsetAsync(scratch, 0, (size_t(blocks) * kSortBlock + blocks + 2) * sizeof(uint32_t), ctx->stream));
+    const uint32_t setBlocks = std::min<uint32_t>((count + 255) / 256, uint32_t(ctx->sm_count) * 8u);
+    ids_set_bits_kernel<<<setBlocks, 256, 0, ctx->stream>>>(static_cast<const uint32_t*>(bi->ptr), count, id_limit, bitmap, bad);
+    ids_block_counts_kernel<<<blocks, kSortBlock, 0, ctx->stream>>>(bitmap, words, sums);
+    ids_scan_blocks_kernel<<<1, kSortBlock, 0, ctx->stream>>>(sums, blocks);
+    ids_expand_kernel<<<blocks, kSortBlock, 0, ctx->stream>>>(bitmap, words, sums, static_cast<uint32_t*>(bo->ptr), count);
+    ctx->launches += 4;
+    RVE_CUDA(cudaGetLastError());
+    return 0;
+}
