@@ -427,7 +427,12 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         "roofline": {"bound": "hbm", "kernel": "cull_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": cull_avg_ms, "slots": slots,
-                     "frac_of_8000_datasheet": achieved / 8000.0, "pyramid_kernel_ms": pyr_ms / max(pyr_n, 1)},
+                     "frac_of_8000_datasheet": achieved / 8000.0, "pyramid_kernel_ms": pyr_ms / max(pyr_n, 1),
+                     "note": ("fused encode: the pyramid launch stops after the tile levels (mips 0..5, footprint-min level 0) and cull_kernel "
+                              "derives the rest in its start-up - kernel_ms contains that work (about +2.3 us; 144.4 us = 0.80 of peak without it: "
+                              "profiles/r02f_pyramid_variants.txt), algorithmic_bytes_per_launch does not count it"
+                              if world_size == 1 and os.environ.get("RVE_BENCH_SPLIT_STEP") != "1" and os.environ.get("RVE_PYRAMID_DEFER") != "0"
+                              else "pyramid build and cull are separate launches here")},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
         "ms_per_step_by_rank": by_rank, "cull_kernel_ms_by_rank": cull_by_rank,
         "visible_per_slot": counts.tolist(),

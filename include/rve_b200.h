@@ -339,6 +339,11 @@ RVE_API int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer de
  * sample). It follows rve_depth_pyramid_build and rve_buffer_upload/copy/fill_zero on the texel buffer automatically;
  * call this after writing the texels any other way (own kernel through rve_buffer_device_ptr). */
 RVE_API int rve_depth_pyramid_texels_changed(rve_ctx* ctx, rve_pyramid pyr);
+/* The derived copy itself, for inspection (tests, debugging): per level of n x n texels an (n+1)^2 image
+ * F[j][i] = min over texels {i-1,i} x {j-1,j} clamped to the level, levels back to back (level L starts at
+ * 4*(dim^2 - n^2)/3 + 4*(dim - n) + L floats). No reference counterpart: the shader samples the mip chain with a
+ * min-reduction sampler (src/RenderEngine.cpp:323-331), this buffer holds what each such sample returns. */
+RVE_API int rve_depth_pyramid_footmin(rve_ctx* ctx, rve_pyramid pyr, rve_buffer* footmin);
 
 /* ------------------------------------------------------------------ */
 /* a-2 cull + LOD + indirect compaction — shaders/defaultcull.csh      */

@@ -177,6 +177,12 @@ class Context:
     def build_pyramid(self, pyr: Pyramid, depth: Buffer, width: int, height: int) -> None:
         _check(self.lib, self.lib.rve_depth_pyramid_build(self.h, pyr.handle, depth.handle, width, height))
 
+    def pyramid_footmin(self, pyr: Pyramid) -> Buffer:
+        """rve_depth_pyramid_footmin: the derived footprint-min chain the cull samples (inspection only)"""
+        out = C.c_uint32()
+        _check(self.lib, self.lib.rve_depth_pyramid_footmin(self.h, pyr.handle, C.byref(out)))
+        return Buffer(self, out.value, self.lib.rve_buffer_size(self.h, out.value))
+
     def cull(self, ubo: CullingUBO, cubos: Buffer, model: Buffer, layers: Buffer, flags: Buffer, pyr: Pyramid,
              num_groups_x: int) -> None:
         _check(self.lib, self.lib.rve_cull(self.h, C.byref(ubo), cubos.handle, model.handle, layers.handle, flags.handle,

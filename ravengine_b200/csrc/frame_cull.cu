@@ -217,7 +217,8 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     if (build) {
         // upload -> pyramid build -> pyramid upper -> cull: the build is a plain launch (it starts once the tables are
         // complete), the cull a programmatic dependent of the pyramid kernels that needs them only for its Hi-Z batches
-        rc = rve_depth_pyramid_build(ctx, pyramids[0], build->depth, build->width, build->height);
+        // single view with work to do: the cull kernel below finishes the pyramid's upper levels in its start-up
+        rc = pyramid_build_impl(ctx, pyramids[0], build->depth, build->width, build->height, !nviews && groups > 0);
         if (rc) return rc;
         static const bool late = [] { const char* e = getenv("RVE_CULL_LATE_WAIT"); return !e || atoi(e) != 0; }();
         if ((cullFlags & kCullTablesPrepared) && late) cullFlags |= kCullLateWait;

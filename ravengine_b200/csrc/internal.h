@@ -23,7 +23,10 @@ struct BufferRec {
 struct PyramidRec {
     uint32_t dim = 0, levels = 0;
     rve_buffer texels = RVE_BUFFER_INVALID;
-    rve_buffer counter = RVE_BUFFER_INVALID;  // u32 "blocks done" ticket for the fused build
+    // device words of the persistent build's grid barrier (arrivals [0], generation [32]) and of a deferred upper part
+    // (worker tickets [64], workers done [96]: zeroed by the build, counted by the cull that finishes the levels)
+    rve_buffer counter = RVE_BUFFER_INVALID;
+    bool upperPending = false;  // texel levels >= 6 and footprint-min levels >= 1 are still to be derived (see pyramid_build_impl)
     // Footprint-min copy of the chain (acceleration structure of rve_cull, derived from `texels`): per level of n x n
     // texels an (n+1)^2 image F[j][i] = min over the clamped 2x2 footprint {i-1,i} x {j-1,j}, i.e. the value of one
     // min-reduction sample whose footprint starts at texel (i-1, j-1). One load per sample instead of four.
@@ -34,6 +37,10 @@ struct PyramidRec {
     alignas(64) unsigned char depthMap[128] = {};
     const void* mapBase = nullptr;
     uint32_t mapW = 0, mapH = 0, boxW = 0, boxH = 0;
+    // persistent single-launch build: geometry chosen for the depth image `persFor` (grid 0: does not qualify)
+    const void* persFor = nullptr;
+    uint32_t persBox = 0, persGrid = 0, persStages = 0, persStageFloats = 0;
+    size_t persSmem = 0;
 };
 
 // Programmatic dependent launch: the kernel may become resident while its predecessor on the stream is still running;
@@ -113,6 +120,7 @@ struct rve_ctx {
     size_t d_sort_cap = 0;
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
     size_t pyramid_smem_opt_in = 48 * 1024;  // dynamic shared memory pyramid_build_tma_kernel has been opted in for
+    size_t pyramid_pers_smem_opt_in = 48 * 1024;  // ... and pyramid_persistent_kernel
     bool views_attr_set = false;  // cull_views_kernel's dynamic shared memory opt-in (per device, hence per context)
     uint32_t* d_gather_ticket = nullptr;  // [0] rve_gather_ids_p2p: CTAs-done counter; [1] CUBO entries with bad handles (cubo_prepare_kernel)
     // scratch: view-space light records for rve_cluster_assign
@@ -167,6 +175,11 @@ int cull_launch(rve_ctx* ctx, const RveCullingUBO* ubo, uint32_t num_views, cons
 int make_image_map(const void* base, uint64_t cols, uint64_t rows, uint32_t boxCols, uint32_t boxRows, void* out);
 // (re)derives the footprint-min chain of a pyramid from its texels when they changed since the last derivation
 int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel = 0);
+// rve_depth_pyramid_build with an option: allowDefer lets the build stop after the tile levels (mips 0..5, footprint-min
+// level 0) and leave PyramidRec::upperPending set - the caller enqueues a cull next, whose kernel finishes the upper levels
+// in its start-up (cull_launch merges them, or runs pyramid_finish_upper first when it cannot)
+int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height, bool allowDefer);
+int pyramid_finish_upper(rve_ctx* ctx, PyramidRec* p);  // no-op unless upperPending
 // marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)
 void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf);
 
@@ -291,5 +304,108 @@ __host__ __device__ inline uint64_t footmin_level_offset(uint32_t dim, uint32_t 
     const uint64_t d0 = dim, dl = dim >> level;
     return 4ull * (d0 * d0 - dl * dl) / 3ull + 4ull * (d0 - dl) + level;
 }
+
+// Level starts of a pyramid, computed once on the host (per-thread 64-bit divisions by 3 otherwise): px texel chain,
+// fm footprint-min chain ([levels] = total), run = first work item of each level for footmin_items.
+struct PyrOffsets {
+    uint32_t px[16], fm[16], run[16];
+};
+// Work items of footmin_items per level of n x n texels: runs of 8 consecutive entries of one row of the (n+1)^2
+// footprint-min image (n/8 + 1 runs per row; the last one is the single entry fx = n), or single entries while n < 8.
+inline uint32_t footmin_items_of_level(uint32_t n) { return (n & 7u) ? (n + 1) * (n + 1) : (n + 1) * (n / 8 + 1); }
+inline PyrOffsets make_pyr_offsets(uint32_t dim, uint32_t levels) {
+    PyrOffsets o{};
+    uint32_t items = 0;
+    for (uint32_t l = 0; l <= levels && l < 16; ++l) {
+        const uint64_t d0 = dim, dl = l < 32 ? (dim >> l) : 0;
+        o.px[l] = uint32_t(4ull * (d0 * d0 - dl * dl) / 3ull);
+        o.fm[l] = uint32_t(footmin_level_offset(dim, l));
+        o.run[l] = items;
+        if (l >= 1 && l < levels) items += footmin_items_of_level(dim >> l);
+    }
+    return o;
+}
+#ifdef __CUDACC__
+// Texel levels topLevel .. levels-1 (what is left above the tiles: an image of at most 32 x 32) and their footprint-min
+// levels, by ONE group of NT threads (tid < NT) in `scratch` (shared memory, >= n^2 * 4/3 + 2 floats for the n x n level
+// topLevel-1); sync() is the group's barrier. Same operand order as depthpyramid.csh's 2x2 min (reduce_level).
+template <int NT, class Sync>
+__device__ __forceinline__ void pyramid_top_chain(float* __restrict__ pyr, float* __restrict__ fm, const PyrOffsets& offs, uint32_t dim, uint32_t levels,
+                                                  uint32_t topLevel, float* scratch, uint32_t tid, Sync sync) {
+    const uint32_t r = dim >> (topLevel - 1);
+    const float* top = pyr + offs.px[topLevel - 1];
+    for (uint32_t k = tid; k < r * r; k += NT) scratch[k] = __ldcg(top + k);
+    sync();
+    uint32_t in_off = 0, n = r, level = topLevel;
+    while (n > 1 && level < levels) {
+        const uint32_t n_out = n / 2, out_off = in_off + n * n;
+        const float* lv = scratch + in_off;
+        float* out = scratch + out_off;
+        float* gdst = pyr + offs.px[level];
+        for (uint32_t k = tid; k < n_out * n_out; k += NT) {
+            const uint32_t x = k % n_out, y = k / n_out;
+            const float v = fminf(fminf(lv[(2 * y) * n + 2 * x], lv[(2 * y) * n + 2 * x + 1]), fminf(lv[(2 * y + 1) * n + 2 * x], lv[(2 * y + 1) * n + 2 * x + 1]));
+            out[k] = v;
+            gdst[k] = v;
+        }
+        sync();
+        float* f = fm + offs.fm[level];
+        const uint32_t m1 = n_out + 1;
+        for (uint32_t k = tid; k < m1 * m1; k += NT) {
+            const uint32_t fx = k % m1, fy = k / m1;
+            const uint32_t x0 = fx ? fx - 1 : 0, x1 = fx < n_out ? fx : n_out - 1;
+            const uint32_t y0 = fy ? fy - 1 : 0, y1 = fy < n_out ? fy : n_out - 1;
+            f[k] = fminf(fminf(out[y0 * n_out + x0], out[y0 * n_out + x1]), fminf(out[y1 * n_out + x0], out[y1 * n_out + x1]));
+        }
+        in_off = out_off;
+        n = n_out;
+        ++level;
+    }
+}
+// Footprint-min levels 1 .. lastFm-1 from their texel levels (already complete and visible; read through L2): worker
+// `worker` of `workers` takes items worker, worker + workers, ... A run of 8 entries costs one scalar and two 128-bit
+// loads per texel row instead of 32 scalar loads; entry (fx, fy) = min over texels {fx-1, fx} x {fy-1, fy} clamped, in
+// the same operand order as the one-entry-per-thread kernels.
+__device__ __forceinline__ void footmin_items(const float* __restrict__ pyr, float* __restrict__ fm, const PyrOffsets& offs, uint32_t dim,
+                                              uint32_t lastFm, uint32_t worker, uint32_t workers) {
+    const uint32_t end = offs.run[lastFm];
+    for (uint32_t it = worker; it < end; it += workers) {
+        uint32_t level = 1;
+        while (level + 1 < lastFm && it >= offs.run[level + 1]) ++level;
+        const uint32_t n = dim >> level, n1 = n + 1, local = it - offs.run[level];
+        const float* img = pyr + offs.px[level];
+        float* out = fm + offs.fm[level];
+        if (n & 7u) {
+            const uint32_t fy = local / n1, fx = local - fy * n1;
+            const uint32_t x0 = fx ? fx - 1 : 0, x1 = fx < n ? fx : n - 1;
+            const uint32_t y0 = fy ? fy - 1 : 0, y1 = fy < n ? fy : n - 1;
+            out[local] = fminf(fminf(__ldcg(img + y0 * n + x0), __ldcg(img + y0 * n + x1)), fminf(__ldcg(img + y1 * n + x0), __ldcg(img + y1 * n + x1)));
+            continue;
+        }
+        const uint32_t perRow = n / 8 + 1;
+        const uint32_t fy = local / perRow, fx0 = (local - fy * perRow) * 8;
+        const uint32_t y0 = fy ? fy - 1 : 0, y1 = fy < n ? fy : n - 1;
+        const float* ra = img + y0 * n;
+        const float* rb = img + y1 * n;
+        const uint32_t xl = fx0 ? fx0 - 1 : 0;
+        const float al = __ldcg(ra + xl), bl = __ldcg(rb + xl);
+        float* o = out + fy * n1 + fx0;
+        if (fx0 == n) {  // the entry past the last texel column: both columns clamp to n - 1
+            o[0] = fminf(fminf(al, al), fminf(bl, bl));
+            continue;
+        }
+        const float4 a0 = __ldcg(reinterpret_cast<const float4*>(ra + fx0)), a1 = __ldcg(reinterpret_cast<const float4*>(ra + fx0 + 4));
+        const float4 b0 = __ldcg(reinterpret_cast<const float4*>(rb + fx0)), b1 = __ldcg(reinterpret_cast<const float4*>(rb + fx0 + 4));
+        o[0] = fminf(fminf(al, a0.x), fminf(bl, b0.x));
+        o[1] = fminf(fminf(a0.x, a0.y), fminf(b0.x, b0.y));
+        o[2] = fminf(fminf(a0.y, a0.z), fminf(b0.y, b0.z));
+        o[3] = fminf(fminf(a0.z, a0.w), fminf(b0.z, b0.w));
+        o[4] = fminf(fminf(a0.w, a1.x), fminf(b0.w, b1.x));
+        o[5] = fminf(fminf(a1.x, a1.y), fminf(b1.x, b1.y));
+        o[6] = fminf(fminf(a1.y, a1.z), fminf(b1.y, b1.z));
+        o[7] = fminf(fminf(a1.z, a1.w), fminf(b1.z, b1.w));
+    }
+}
+#endif
 
 }  // namespace rve

@@ -185,9 +185,10 @@ __host__ __device__ inline uint32_t footprint_start(uint32_t t, uint32_t dim, ui
 // instruction" on sm_100a (tools/tma_probe.cu); boxes up to 256 x 128 texels in one copy are fine.
 __global__ void __launch_bounds__(kPyrThreads)
 pyramid_build_tma_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
-                         uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH) {
+                         uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH, uint32_t* __restrict__ deferSync) {
     extern __shared__ __align__(128) unsigned char s_dyn[];
     __shared__ uint64_t s_bar;
+    if (deferSync && blockIdx.x == 0 && threadIdx.x == 0) deferSync[64] = 0, deferSync[96] = 0;  // the upper part is left to the next cull
     float* s_src = reinterpret_cast<float*>(s_dyn);
     float* s_lv = s_src + boxW * boxH;
     constexpr uint32_t tile = kPyrTile, S = kPyrTile + 1;
@@ -232,10 +233,6 @@ pyramid_build_tma_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t 
     }
     tile_levels<true>(s_lv, pyr, fm, dim, levels, tile, tx0, ty0);
 }
-
-struct PyrOffsets {  // start of every level in the texel chain (px) and in the footprint-min chain (fm); [levels] = total
-    uint32_t px[16], fm[16];
-};
 
 __device__ __forceinline__ float footmin_entry(const float* img, uint32_t n, uint32_t fx, uint32_t fy) {
     const uint32_t x0 = fx ? fx - 1 : 0, x1 = fx < n ? fx : n - 1;
@@ -308,6 +305,200 @@ pyramid_upper_kernel(float* __restrict__ pyr, float* __restrict__ fm, uint32_t d
         if (idx[k] < end) fm[idx[k]] = v[k];
 }
 
+// ---- the whole build in ONE persistent launch -------------------------------------------------------------------------
+// Two CTAs per SM, all resident. A producer warp streams the tiles' source boxes through a ring of shared-memory stages
+// (TMA, full / empty mbarriers): with 3 stages per CTA nearly the whole 33 MB source is requested before the first tile is
+// sampled. Eight compute warps work in registers: warp w samples rows 4w .. 4w+4 of the 33 x 33 sample grid (lane = column;
+// the halo column by lanes 0..4), and from those five registers per lane come, by shuffles alone, mip 0, level 0 of the
+// footprint-min chain, mip 1 (two rows per warp) and mip 2 (one row per warp); the 8 x 8 mip-2 image crosses warps through
+// 256 B of shared memory and one warp finishes mips 3..5. ~6x fewer instructions per tile than the shared-memory ladder of
+// tile_levels (which the ncu capture showed instruction-bound), no __syncthreads ladder, one named barrier per tile.
+// Then a grid-wide barrier (sense-reversing, self re-arming - safe under graph replay) replaces the second launch: CTA 0
+// reduces the remaining 32 x 32 image (mips 6..10 + their footprint-min levels), the others derive footprint-min levels 1..5.
+// u = (t + 0.5) / dim is evaluated as (t + 0.5) * (1 / dim): dim is a power of two, so both are exact and equal.
+constexpr int kPersWarps = 8;
+constexpr int kPersComputeThreads = kPersWarps * 32;
+constexpr int kPersThreads = kPersComputeThreads + 32;  // + the producer warp
+constexpr int kPersMaxStages = 6;
+
+namespace pyr {
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+__device__ __forceinline__ void compute_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kPersComputeThreads) : "memory"); }
+__device__ __forceinline__ uint32_t ld_acquire(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release(uint32_t* p, uint32_t v) { asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+// clamped 2x2 footprint of sample t along an axis of n source texels (sample_min_src's arithmetic)
+__device__ __forceinline__ void axis_footprint(uint32_t t, float invDim, uint32_t n, uint32_t& i0, uint32_t& i1) {
+    const float u = (float(t) + 0.5f) * invDim;
+    footprint(__fmaf_rn(u, float(n), -0.5f), n, i0, i1);
+}
+}  // namespace pyr
+
+// all compute threads of all CTAs of the grid; sync[0] arrivals of the current generation, sync[32] the generation
+__device__ __forceinline__ void pers_grid_barrier(uint32_t* sync, uint32_t G) {
+    pyr::compute_sync();
+    if (threadIdx.x == 0) {
+        const uint32_t gen = pyr::ld_acquire(sync + 32);  // cannot advance before this CTA has arrived
+        __threadfence();
+        const uint32_t old = atomicInc(sync, G - 1);  // wraps to 0 with the last arrival: re-armed for the next launch
+        if (old == G - 1) pyr::st_release(sync + 32, gen + 1);
+        else
+            while (pyr::ld_acquire(sync + 32) == gen) __nanosleep(32);
+        __threadfence();
+    }
+    pyr::compute_sync();
+}
+
+__global__ void __launch_bounds__(kPersThreads, 2)
+pyramid_persistent_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
+                          uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH, uint32_t stages, uint32_t stageFloats, uint32_t topLevel,
+                          uint32_t* __restrict__ gridSync, const __grid_constant__ PyrOffsets offs, uint32_t debug, uint32_t deferUpper) {
+    extern __shared__ __align__(128) unsigned char s_dyn[];
+    __shared__ uint64_t s_full[kPersMaxStages], s_empty[kPersMaxStages];
+    __shared__ float s_l2[2][kPersWarps][8];
+    float* s_src = reinterpret_cast<float*>(s_dyn);
+    const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t tilesPerRow = dim / kPyrTile, numTiles = tilesPerRow * tilesPerRow;
+    const uint32_t G = gridDim.x;
+    const float invDim = 1.0f / float(dim);
+    constexpr uint32_t kFull = 0xffffffffu;
+    if (threadIdx.x == 0) {
+        if (deferUpper && blockIdx.x == 0) gridSync[64] = 0, gridSync[96] = 0;  // the upper part is left to the next cull
+        for (uint32_t s = 0; s < stages; ++s) {
+            pyr::mbar_init(&s_full[s], 1);
+            pyr::mbar_init(&s_empty[s], kPersWarps);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == kPersWarps) {  // producer: one lane feeds the ring, then the warp is done
+        if (lane == 0 && !(debug & 8u)) {
+            asm volatile("prefetch.tensormap [%0];" ::"l"(&depthMap) : "memory");
+            uint32_t i = 0;
+            for (uint32_t t = blockIdx.x; t < numTiles; t += G, ++i) {
+                const uint32_t s = i % stages, use = i / stages;
+                if (use) pyr::mbar_wait(&s_empty[s], (use - 1) & 1);
+                const uint32_t tx0 = (t % tilesPerRow) * kPyrTile, ty0 = (t / tilesPerRow) * kPyrTile;
+                uint32_t a, b, sx0, sy0;
+                pyr::axis_footprint(tx0, invDim, w, sx0, a);
+                pyr::axis_footprint(ty0, invDim, h, sy0, b);
+                sx0 &= ~3u;  // 16-byte aligned box start (see pyramid_build_tma_kernel)
+                pyr::mbar_expect_tx(&s_full[s], boxW * boxH * 4u);
+                pyr::tma_load_box(s_src + size_t(s) * stageFloats, &depthMap, int32_t(sx0), int32_t(sy0), &s_full[s]);
+            }
+        }
+        return;
+    }
+
+    const uint32_t n1 = dim + 1;
+    uint32_t i = 0;
+    for (uint32_t t = blockIdx.x; t < numTiles; t += G, ++i) {
+        const uint32_t s = i % stages, use = i / stages;
+        const uint32_t tx0 = (t % tilesPerRow) * kPyrTile, ty0 = (t / tilesPerRow) * kPyrTile;
+        uint32_t sx0, sy0, c0, c1, ch0, ch1, ra, rb;
+        pyr::axis_footprint(tx0, invDim, w, sx0, c0);
+        pyr::axis_footprint(ty0, invDim, h, sy0, c0);
+        sx0 &= ~3u;
+        // box-local footprints: this lane's sample column, the halo column (sample 32), and - in lanes 0..4 - one of the warp's rows
+        pyr::axis_footprint(tx0 + lane, invDim, w, c0, c1);
+        const uint32_t xh = tx0 + kPyrTile < dim ? tx0 + kPyrTile : dim - 1;
+        pyr::axis_footprint(xh, invDim, w, ch0, ch1);
+        uint32_t yr = ty0 + 4 * warp + (lane < 4 ? lane : 4);
+        yr = yr < dim ? yr : dim - 1;
+        pyr::axis_footprint(yr, invDim, h, ra, rb);
+        c0 -= sx0, c1 -= sx0, ch0 -= sx0, ch1 -= sx0;
+        ra = (ra - sy0) * boxW, rb = (rb - sy0) * boxW;
+
+        if (debug & 8u) continue;
+        pyr::mbar_wait(&s_full[s], use & 1);
+        if (debug & 4u) {  // RVE_PYRAMID_DEBUG (development only): loads without the tile work
+            __syncwarp();
+            if (lane == 0) pyr::mbar_arrive(&s_empty[s]);
+            continue;
+        }
+        const float* src = s_src + size_t(s) * stageFloats;
+        float m[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            const uint32_t r0 = __shfl_sync(kFull, ra, j), r1 = __shfl_sync(kFull, rb, j);
+            m[j] = gmin(gmin(src[r0 + c0], src[r0 + c1]), gmin(src[r1 + c0], src[r1 + c1]));
+        }
+        const float e = gmin(gmin(src[ra + ch0], src[ra + ch1]), gmin(src[rb + ch0], src[rb + ch1]));  // halo column, row 4w + lane (lanes 0..4)
+        __syncwarp();
+        if (lane == 0) pyr::mbar_arrive(&s_empty[s]);  // the stage may be refilled once all eight warps have read it
+
+        const uint32_t y0 = ty0 + 4 * warp;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) pyr[size_t(y0 + j) * dim + tx0 + lane] = m[j];
+        // level 0 of the footprint-min chain: F[y][x] = min of samples {x-1, x} x {y-1, y}; lane holds x - 1
+        float hd[5];
+#pragma unroll
+        for (int j = 0; j < 5; ++j) {
+            float nb = __shfl_down_sync(kFull, m[j], 1);
+            const float m32 = __shfl_sync(kFull, e, j);
+            nb = lane == 31 ? m32 : nb;
+            hd[j] = gmin(m[j], nb);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) fm[size_t(y0 + 1 + j) * n1 + tx0 + lane + 1] = gmin(hd[j], hd[j + 1]);
+        if (tx0 == 0 && lane == 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) fm[size_t(y0 + 1 + j) * n1] = gmin(m[j], m[j + 1]);
+        }
+        if (ty0 == 0 && warp == 0) {
+            fm[tx0 + lane + 1] = hd[0];
+            if (tx0 == 0 && lane == 0) fm[0] = m[0];
+        }
+        // mip 1: rows 2w, 2w+1 of the tile's 16 x 16 (even lanes); mip 2: row w of its 8 x 8 (every fourth lane) - depthpyramid.csh
+        const float p0 = gmin(m[0], __shfl_xor_sync(kFull, m[0], 1)), p1 = gmin(m[1], __shfl_xor_sync(kFull, m[1], 1));
+        const float p2 = gmin(m[2], __shfl_xor_sync(kFull, m[2], 1)), p3 = gmin(m[3], __shfl_xor_sync(kFull, m[3], 1));
+        const float l1a = gmin(p0, p1), l1b = gmin(p2, p3);
+        if ((lane & 1u) == 0) {
+            float* d1 = pyr + offs.px[1] + size_t((ty0 >> 1) + 2 * warp) * (dim >> 1) + (tx0 >> 1) + (lane >> 1);
+            d1[0] = l1a;
+            d1[dim >> 1] = l1b;
+        }
+        const float l2 = gmin(gmin(l1a, __shfl_xor_sync(kFull, l1a, 2)), gmin(l1b, __shfl_xor_sync(kFull, l1b, 2)));
+        if ((lane & 3u) == 0) {
+            pyr[offs.px[2] + size_t((ty0 >> 2) + warp) * (dim >> 2) + (tx0 >> 2) + (lane >> 2)] = l2;
+            s_l2[i & 1][warp][lane >> 2] = l2;
+        }
+        pyr::compute_sync();
+        if (warp == 0) {  // mips 3..5 of the tile from its 8 x 8 mip 2 (double-buffered: the next tile's writes go to the other copy)
+            const uint32_t x = lane & 3u, y = (lane >> 2) & 3u;
+            const float* q = &s_l2[i & 1][0][0];
+            const float v3 = gmin(gmin(q[(2 * y) * 8 + 2 * x], q[(2 * y) * 8 + 2 * x + 1]), gmin(q[(2 * y + 1) * 8 + 2 * x], q[(2 * y + 1) * 8 + 2 * x + 1]));
+            if (lane < 16) pyr[offs.px[3] + size_t((ty0 >> 3) + y) * (dim >> 3) + (tx0 >> 3) + x] = v3;
+            const float h4 = gmin(v3, __shfl_xor_sync(kFull, v3, 1));
+            const float v4 = gmin(h4, __shfl_xor_sync(kFull, h4, 4));
+            if (lane < 16 && (lane & 5u) == 0) pyr[offs.px[4] + size_t((ty0 >> 4) + (lane >> 3)) * (dim >> 4) + (tx0 >> 4) + ((lane >> 1) & 1u)] = v4;
+            const float h5 = gmin(v4, __shfl_xor_sync(kFull, v4, 2));
+            const float v5 = gmin(h5, __shfl_xor_sync(kFull, h5, 8));
+            if (lane == 0) pyr[offs.px[5] + size_t(ty0 >> 5) * (dim >> 5) + (tx0 >> 5)] = v5;
+        }
+    }
+
+    if ((debug & 2u) || deferUpper) return;
+    pers_grid_barrier(gridSync, G);
+    if (debug & 1u) return;
+
+    const uint32_t tid = threadIdx.x;  // < kPersComputeThreads
+    if (blockIdx.x == 0 && G > 1 && topLevel >= levels) return;  // (cannot happen: more than one tile means levels > topLevel)
+    if (blockIdx.x == 0 && topLevel < levels) {
+        // texel levels topLevel.. (the 32 x 32 or smaller image the tiles left) and their footprint-min levels; the ring is idle now
+        pyramid_top_chain<kPersComputeThreads>(pyr, fm, offs, dim, levels, topLevel, s_src, tid, [] { pyr::compute_sync(); });
+        if (G > 1) return;
+    }
+    // footprint-min levels 1 .. topLevel-1 from the texel levels every CTA wrote before the barrier (read through L2)
+    const uint32_t lastFm = topLevel < levels ? topLevel : levels;
+    footmin_items(pyr, fm, offs, dim, lastFm, (G > 1 ? blockIdx.x - 1 : 0) * kPersComputeThreads + tid, (G > 1 ? G - 1 : 1) * kPersComputeThreads);
+}
+
 // footprint-min chain (see PyramidRec::footmin): one thread per output, levels firstLevel.. in one launch
 __global__ void pyramid_footmin_kernel(const float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels,
                                        uint32_t firstLevel, uint32_t total) {
@@ -368,7 +559,7 @@ int rve_depth_pyramid_create(rve_ctx* ctx, uint32_t width, rve_pyramid* out) {
     const size_t texels = (4ull * dim * dim - 1) / 3;
     int rc = rve_buffer_create(ctx, texels * sizeof(float), &rec.texels);  // zero = "far" in reverse-Z: nothing occluded
     if (rc) return rc;
-    rc = rve_buffer_create(ctx, sizeof(uint32_t), &rec.counter);
+    rc = rve_buffer_create(ctx, 128 * sizeof(uint32_t), &rec.counter);  // PyramidRec::counter
     if (rc) return rc;
     rc = rve_buffer_create(ctx, footmin_level_offset(dim, rec.levels) * sizeof(float), &rec.footmin);
     if (rc) return rc;
@@ -408,12 +599,68 @@ int rve_depth_pyramid_info(rve_ctx* ctx, rve_pyramid pyr, uint32_t* dim, uint32_
     return 0;
 }
 
+int rve_depth_pyramid_footmin(rve_ctx* ctx, rve_pyramid pyr, rve_buffer* footmin) {
+    if (!ctx || !footmin) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    DeviceGuard g(ctx->device);
+    PyramidRec* p = get_pyramid(ctx, pyr);
+    if (!p) return RVE_ERR_BAD_HANDLE;
+    int rc = pyramid_finish_upper(ctx, p);  // (a deferring build is always followed by its cull; kept for safety)
+    if (rc) return rc;
+    rc = pyramid_refresh_footmin(ctx, p, 0);  // texels written behind the library's back since the last build
+    if (rc) return rc;
+    *footmin = p->footmin;
+    return 0;
+}
+
 int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height) {
+    return pyramid_build_impl(ctx, pyr, depth, width, height, false);
+}
+
+}  // extern "C"
+
+namespace rve {
+
+static int launch_upper(rve_ctx* ctx, PyramidRec* p, float* pyrPtr, float* fmPtr, uint32_t topLevel, bool programmatic) {
+    if (p->levels <= 1) return 0;
+    const uint32_t lastFm = topLevel < p->levels ? topLevel : p->levels;
+    const uint32_t entries = uint32_t(footmin_level_offset(p->dim, lastFm) - footmin_level_offset(p->dim, 1));
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(1 + (entries + 2 * kPyrThreads - 1) / (2 * kPyrThreads));
+    cfg.blockDim = dim3(kPyrThreads);
+    cfg.stream = ctx->stream;
+    cudaLaunchAttribute attr{};
+    attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr.val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = programmatic ? 1 : 0;
+    static const uint32_t early = [] { const char* e = getenv("RVE_UPPER_TRIGGER"); return (e && atoi(e) != 0) ? 1u : 0u; }();
+    const PyrOffsets offs = make_pyr_offsets(p->dim, p->levels);
+    RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel, programmatic ? early : 0u, offs));
+    ctx->launches++;
+    return 0;
+}
+
+// the part a deferring build left out, as a launch of its own (the consumer is not a cull that can take it along)
+int pyramid_finish_upper(rve_ctx* ctx, PyramidRec* p) {
+    if (!p->upperPending) return 0;
+    BufferRec* t = get_buffer(ctx, p->texels, "pyramid texels");
+    BufferRec* f = get_buffer(ctx, p->footmin, "pyramid footprint-min chain");
+    if (!t || !f) return RVE_ERR_BAD_HANDLE;
+    uint32_t topLevel = 1;
+    while ((1u << topLevel) <= uint32_t(kPyrTile)) ++topLevel;
+    const int rc = launch_upper(ctx, p, static_cast<float*>(t->ptr), static_cast<float*>(f->ptr), topLevel, false);
+    if (rc) return rc;
+    p->upperPending = false;
+    return 0;
+}
+
+int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height, bool allowDefer) {
     if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
     RVE_PROFILE_FN_N("generatePyramid");
     DeviceGuard g(ctx->device);
     PyramidRec* p = get_pyramid(ctx, pyr);
     if (!p) return RVE_ERR_BAD_HANDLE;
+    p->upperPending = false;  // whatever an earlier build left open is rewritten by this one
     BufferRec* d = get_buffer(ctx, depth, "depth");
     if (!d) return RVE_ERR_BAD_HANDLE;
     RVE_REQUIRE(width >= 1 && height >= 1, "depth buffer must be at least 1x1");
@@ -427,6 +674,15 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     while ((1u << topLevel) <= tile) ++topLevel;
     float* pyrPtr = static_cast<float*>(t->ptr);
     float* fmPtr = static_cast<float*>(f->ptr);
+    // Deferral (allowDefer: a cull follows at once): the build ends with the tile levels; the cull kernel derives the rest while
+    // its first rounds are in flight. RVE_PYRAMID_DEFER=0 switches it off, RVE_PYRAMID_DEFER_TILES=tma picks the one-box-per-CTA
+    // tile kernel instead of the persistent one (A/B runs).
+    const char* deferEnv = getenv("RVE_PYRAMID_DEFER");
+    const bool wantDefer = allowDefer && !(deferEnv && atoi(deferEnv) == 0) && tile == uint32_t(kPyrTile) && p->levels > 1;
+    const char* deferTiles = getenv("RVE_PYRAMID_DEFER_TILES");
+    const bool deferWithTma = wantDefer && deferTiles && deferTiles[0] == 't';
+    BufferRec* sync = get_buffer(ctx, p->counter, "pyramid counters");
+    if (!sync) return RVE_ERR_BAD_HANDLE;
     {
         ProfScope prof(ctx, RVE_PROF_PYRAMID);
         // TMA-fed tiles when the image qualifies (16-byte aligned rows, full 32-texel tiles, a source box that fits)
@@ -453,13 +709,60 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
                 }
             }
             const size_t smem = size_t(p->boxW) * p->boxH * 4 + sizeof(float) * ((kPyrTile + 1) * (kPyrTile + 1) + (kPyrTile * kPyrTile) / 3 + 2);
+            // The persistent kernel (a ring of >= 2 source boxes must fit a CTA). Deferring builds use it for the tile levels.
+            // As a complete build in one launch (tiles + grid barrier + upper levels) it measures 20.8 us against 19.6 us
+            // for the two launches below (profiles/r02f_pyramid_variants.txt: the grid barrier and the upper phase sit on the
+            // critical path either way), so a plain rve_depth_pyramid_build takes it only with RVE_PYRAMID_PERSISTENT=1.
+            const char* persEnv = getenv("RVE_PYRAMID_PERSISTENT");
+            const bool persistentOff = wantDefer ? deferWithTma : !(persEnv && atoi(persEnv) != 0);
+            if (p->mapBase == d->ptr && !persistentOff && p->levels > uint32_t(__builtin_ctz(kPyrTile))) {
+                if (p->persFor != d->ptr || p->persBox != p->boxW * p->boxH) {
+                    p->persGrid = 0;
+                    p->persFor = d->ptr;
+                    p->persBox = p->boxW * p->boxH;
+                    const size_t stageBytes = (size_t(p->boxW) * p->boxH * 4 + 127) & ~size_t(127);
+                    const char* ctasEnv = getenv("RVE_PYRAMID_PERS_CTAS");      // development: CTAs per SM (1 or 2)
+                    const char* stagesEnv = getenv("RVE_PYRAMID_PERS_STAGES");  // development: ring depth
+                    for (uint32_t perSm = ctasEnv ? uint32_t(atoi(ctasEnv)) : 2u; perSm >= 1 && !p->persGrid; --perSm) {
+                        const size_t budget = std::min<size_t>(227 * 1024, (228 * 1024) / perSm - 1024) - 1024;  // static shared memory + slack
+                        const uint32_t grid = std::min<uint32_t>(blocks, perSm * uint32_t(ctx->sm_count));
+                        const uint32_t tilesPerCta = (blocks + grid - 1) / grid;
+                        uint32_t st = uint32_t(std::min<size_t>(std::min<size_t>(budget / stageBytes, kPersMaxStages), tilesPerCta));
+                        if (stagesEnv) st = std::min<uint32_t>(st, uint32_t(atoi(stagesEnv)));
+                        if (st < 2 && st < tilesPerCta) continue;
+                        const size_t bytes = std::max<size_t>(st * stageBytes, sizeof(float) * (kPyrTile * kPyrTile + (kPyrTile * kPyrTile) / 3 + 2));
+                        if (bytes > ctx->pyramid_pers_smem_opt_in) {
+                            RVE_CUDA(cudaFuncSetAttribute(pyramid_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+                            ctx->pyramid_pers_smem_opt_in = bytes;
+                        }
+                        int occ = 0;  // the grid barrier needs every CTA resident
+                        RVE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, pyramid_persistent_kernel, kPersThreads, bytes));
+                        if (occ < int(perSm)) continue;
+                        p->persGrid = grid, p->persStages = st, p->persStageFloats = uint32_t(stageBytes / 4), p->persSmem = bytes;
+                    }
+                }
+                if (p->persGrid) {
+                    const PyrOffsets offs = make_pyr_offsets(p->dim, p->levels);
+                    const char* dbgEnv = getenv("RVE_PYRAMID_DEBUG");  // development only: 1 no upper phase, 2 no grid barrier, 4 no tile work, 8 no loads
+                    const uint32_t dbg = dbgEnv ? uint32_t(atoi(dbgEnv)) : 0u;
+                    pyramid_persistent_kernel<<<p->persGrid, kPersThreads, p->persSmem, ctx->stream>>>(
+                        *reinterpret_cast<const CUtensorMap*>(p->depthMap), width, height, pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH, p->persStages,
+                        p->persStageFloats, topLevel, static_cast<uint32_t*>(sync->ptr), offs, dbg, wantDefer ? 1u : 0u);
+                    ctx->launches++;
+                    RVE_CUDA(cudaGetLastError());
+                    p->footmin_valid = true;
+                    p->upperPending = wantDefer;
+                    return 0;
+                }
+            }
             if (p->mapBase == d->ptr && smem <= 96 * 1024) {
                 if (smem > ctx->pyramid_smem_opt_in) {
                     RVE_CUDA(cudaFuncSetAttribute(pyramid_build_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
                     ctx->pyramid_smem_opt_in = smem;
                 }
                 pyramid_build_tma_kernel<<<blocks, kPyrThreads, smem, ctx->stream>>>(*reinterpret_cast<const CUtensorMap*>(p->depthMap), width, height,
-                                                                                   pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH);
+                                                                                   pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH,
+                                                                                   wantDefer ? static_cast<uint32_t*>(sync->ptr) : nullptr);
                 tma = true;
             }
         }
@@ -468,31 +771,15 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
                                                                           p->levels, tile);
         ctx->launches++;
         RVE_CUDA(cudaGetLastError());
-        if (p->levels > 1) {
-            const uint32_t lastFm = topLevel < p->levels ? topLevel : p->levels;
-            const uint32_t entries = uint32_t(footmin_level_offset(p->dim, lastFm) - footmin_level_offset(p->dim, 1));
-            cudaLaunchConfig_t cfg{};
-            cfg.gridDim = dim3(1 + (entries + 2 * kPyrThreads - 1) / (2 * kPyrThreads));
-            cfg.blockDim = dim3(kPyrThreads);
-            cfg.stream = ctx->stream;
-            cudaLaunchAttribute attr{};
-            attr.id = cudaLaunchAttributeProgrammaticStreamSerialization;
-            attr.val.programmaticStreamSerializationAllowed = 1;
-            cfg.attrs = &attr;
-            cfg.numAttrs = 1;
-            static const uint32_t early = [] { const char* e = getenv("RVE_UPPER_TRIGGER"); return (e && atoi(e) != 0) ? 1u : 0u; }();
-            PyrOffsets offs{};
-            for (uint32_t l = 0; l <= p->levels && l < 16; ++l) {
-                const uint64_t d0 = p->dim, dl = l < 32 ? (p->dim >> l) : 0;
-                offs.px[l] = uint32_t(4ull * (d0 * d0 - dl * dl) / 3ull);
-                offs.fm[l] = uint32_t(footmin_level_offset(p->dim, l));
-            }
-            RVE_CUDA(cudaLaunchKernelEx(&cfg, pyramid_upper_kernel, pyrPtr, fmPtr, p->dim, p->levels, topLevel, early, offs));
-            ctx->launches++;
+        if (tma && wantDefer) {
+            p->upperPending = true;
+        } else {
+            const int rc = launch_upper(ctx, p, pyrPtr, fmPtr, topLevel, true);
+            if (rc) return rc;
         }
     }
     p->footmin_valid = true;
     return 0;
 }
 
-}  // extern "C"
+}  // namespace rve

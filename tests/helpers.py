@@ -71,3 +71,17 @@ def compare_cull_outputs(tables, materials, ref, got):
     for i, (a, b) in enumerate(zip(ref, got)):
         if a is not None and a.dtype == np.float32:
             np.testing.assert_array_equal(a, b)
+
+
+def footmin_chain(texels, dim, levels):
+    """The derived chain rve_cull samples (include/rve_b200.h, rve_depth_pyramid_footmin), from a texel chain: per level the
+    min over the clamped 2x2 footprint {i-1,i} x {j-1,j}, an (n+1)^2 image, levels back to back."""
+    import numpy as np
+
+    out, off = [], 0
+    for lv in range(levels):
+        n = dim >> lv
+        p = np.pad(texels[off:off + n * n].reshape(n, n), 1, mode="edge")
+        out.append(np.minimum(np.minimum(p[:-1, :-1], p[:-1, 1:]), np.minimum(p[1:, :-1], p[1:, 1:])).ravel())
+        off += n * n
+    return np.concatenate(out)

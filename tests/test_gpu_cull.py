@@ -8,7 +8,7 @@ import pytest
 import oracle
 from oracle import host_tables
 from ravengine_b200 import scenes
-from tests.helpers import compare_cull_outputs, device_cull, make_ubo, oracle_cull
+from tests.helpers import compare_cull_outputs, device_cull, footmin_chain, make_ubo, oracle_cull
 
 pytestmark = pytest.mark.gpu
 
@@ -227,31 +227,39 @@ def test_dynamic_tail_rounds_mixed_paths(ctx, n):
         _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=360, groups=(n - 70_000) // 64, nthreads=oracle.default_workers())
 
 
-@pytest.mark.parametrize("size", [(3840, 2160), (1920, 1080), (1280, 720), (2560, 1440), (7680, 4320), (1024, 1024), (1028, 4000), (36, 32)])
-def test_pyramid_tma_tiles_equal_the_lsu_tiles_and_the_oracle(ctx, size):
-    """The TMA-fed build (one tensor copy of the tile's source rectangle per CTA) against the LSU-fed kernel and the oracle,
-    at sizes with different source / pyramid ratios (1x .. 7.5x) and edge clamping on both axes."""
+@pytest.mark.parametrize("size", [(3840, 2160), (1920, 1080), (1280, 720), (2560, 1440), (7680, 4320), (1024, 1024), (1028, 4000), (36, 32), (64, 64), (200, 130)])
+def test_pyramid_build_paths_equal_each_other_and_the_oracle(ctx, size):
+    """The three builds - one persistent launch (TMA ring, register / shuffle tiles, grid barrier), two launches with one
+    tensor copy per CTA, two launches with LSU-fed tiles - against the oracle's texels and the footprint-min chain derived
+    from them, at sizes with different source / pyramid ratios (1x .. 7.5x) and edge clamping on both axes. Three builds
+    in a row per path: the grid barrier re-arms itself."""
     import os
 
     w, h = size
     rng = np.random.default_rng(w + 3 * h)
     depth = rng.random((h, w), dtype=np.float32)
     ref, dim, levels = oracle.pyramid_build(depth)
+    fm_ref = footmin_chain(ref, dim, levels)
     d = ctx.buffer_from_numpy(depth)
-    out = []
-    for no_tma in ("", "1"):
-        if no_tma:
-            os.environ["RVE_PYRAMID_NO_TMA"] = "1"
-        else:
-            os.environ.pop("RVE_PYRAMID_NO_TMA", None)
-        pyr = ctx.create_pyramid(min(w, h))
-        for _ in range(2):
-            ctx.build_pyramid(pyr, d, w, h)
-        ctx.synchronize()
-        out.append(pyr.texels.download(np.float32))
-    os.environ.pop("RVE_PYRAMID_NO_TMA", None)
-    np.testing.assert_array_equal(ref, out[0])
-    np.testing.assert_array_equal(ref, out[1])
+    junk = ctx.buffer_from_numpy(rng.random((h, w), dtype=np.float32))
+    saved = {k: os.environ.get(k) for k in ("RVE_PYRAMID_NO_TMA", "RVE_PYRAMID_PERSISTENT")}
+    try:
+        for env in ({"RVE_PYRAMID_PERSISTENT": "1"}, {}, {"RVE_PYRAMID_NO_TMA": "1"}):
+            for k in saved:
+                os.environ.pop(k, None)
+            os.environ.update(env)
+            pyr = ctx.create_pyramid(min(w, h))
+            ctx.build_pyramid(pyr, junk, w, h)  # other contents first: every texel and chain entry must be rewritten
+            for _ in range(2):
+                ctx.build_pyramid(pyr, d, w, h)
+            ctx.synchronize()
+            np.testing.assert_array_equal(ref, pyr.texels.download(np.float32), err_msg=str(env))
+            np.testing.assert_array_equal(fm_ref, ctx.pyramid_footmin(pyr).download(np.float32)[: fm_ref.size], err_msg=str(env))
+    finally:
+        for k, v in saved.items():
+            os.environ.pop(k, None)
+            if v is not None:
+                os.environ[k] = v
 
 
 def test_garbage_in_the_unwritten_cubo_tail_is_never_followed(ctx):

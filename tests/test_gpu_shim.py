@@ -12,7 +12,7 @@ from oracle import host_tables
 from oracle.host_tables import CUBO_DTYPE, SkinnedCommandDesc, SkinnedMeshDesc
 from ravengine_b200 import GridAssignUBO, GridBuildUBO, SkinningPrepareUBO, SkinningUBO, scenes
 from ravengine_b200.world import MAT_LIT_OPAQUE, MAT_UNLIT_OPAQUE, QUIRK_INDIRECT_SLOT, World
-from tests.helpers import make_ubo, oracle_cull
+from tests.helpers import footmin_chain, make_ubo, oracle_cull
 
 pytestmark = pytest.mark.gpu
 
@@ -393,6 +393,8 @@ def test_fused_pyramid_and_cull_encode_matches_oracle(ctx, n, size):
         w.cull_static_with_pyramid(cam.view_proj_cm, cam.pos, pyr, d, wd, hd)
         ctx.synchronize()
         np.testing.assert_array_equal(pyr_h, pyr.texels.download(np.float32))
+        fm_ref = footmin_chain(pyr_h, dim, levels)  # the upper levels are finished inside the cull kernel (deferred build)
+        np.testing.assert_array_equal(fm_ref, ctx.pyramid_footmin(pyr).download(np.float32)[: fm_ref.size])
         _compare_static(ctx, w, mat_ids, mats, t, ref)
         d.destroy()
     w.destroy()
@@ -415,7 +417,7 @@ def test_captured_frame_replays_with_new_per_entity_data(ctx):
     launches = ctx.launch_count
     graph = ctx.capture(lambda: w.cull_static_with_pyramid(cam.view_proj_cm, cam.pos, pyr, d_depth, 512, 288))
     recorded = ctx.launch_count - launches
-    assert recorded == 4  # upload, pyramid build, pyramid upper, cull - recorded, not executed
+    assert recorded == 3  # upload, pyramid tiles, cull (which finishes the pyramid's upper levels) - recorded, not executed
     rng = np.random.default_rng(3)
     for frame in range(3):
         model2 = scenes.random_transforms(rng, len(model), 120.0, 60.0)

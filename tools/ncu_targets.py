@@ -1,6 +1,6 @@
 #!/usr/bin/env python
 """Launches every hot kernel of the path a few times, for one `ncu --set full` capture (profiles/rNN_*_ncu_*):
-C2 step (pyramid_build_tma_kernel, pyramid_upper_kernel, upload_params_kernel, cull_kernel), the same cull over churned
+C2 step (pyramid_persistent_kernel, upload_params_kernel, cull_kernel), the same cull over churned
 entity lists (gather path), skin_kernel (C3 shape, 500 characters), cluster_assign_kernel (C4, one view),
 cull_views_kernel (8 views, 2 M instances), full_rows_kernel (48-B affine upload expand).
 
