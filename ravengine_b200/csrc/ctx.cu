@@ -116,14 +116,6 @@ static int alloc_slot(rve_ctx* ctx, void* ptr, size_t bytes, bool owned, rve_buf
 using namespace rve;
 
 namespace rve {
-constexpr uint32_t kUploadMaxSegs = 16;
-constexpr uint32_t kUploadMaxWords = 896;  // 3.5 KB of payload: the whole block stays under the 4 KB parameter limit
-struct UploadBlock {
-    uint32_t* dst[kUploadMaxSegs];
-    uint32_t first[kUploadMaxSegs], count[kUploadMaxSegs];
-    uint32_t n;
-    uint32_t data[kUploadMaxWords];
-};
 // one CTA per segment; the payload is read from the parameter (constant) bank
 __global__ void upload_params_kernel(const __grid_constant__ UploadBlock blk) {
     pdl_trigger();  // a programmatic dependent (cubo_prepare_kernel) may become resident; it waits for this grid's completion
@@ -133,26 +125,37 @@ __global__ void upload_params_kernel(const __grid_constant__ UploadBlock blk) {
     for (uint32_t i = threadIdx.x; i < blk.count[s]; i += blockDim.x) dst[i] = src[i];
 }
 
-int upload_batch_raw(rve_ctx* ctx, const RawSegment* segs, uint32_t n) {
+int make_upload_block(const RawSegment* segs, uint32_t n, UploadBlock* blk) {
+    blk->n = 0;
     if (n == 0) return 0;
     if (n > kUploadMaxSegs) return RVE_ERR_UNSUPPORTED;
-    UploadBlock blk{};
     uint32_t words = 0;
     for (uint32_t i = 0; i < n; ++i) {
         if ((segs[i].bytes & 3) || (reinterpret_cast<uintptr_t>(segs[i].dst) & 3) || words + segs[i].bytes / 4 > kUploadMaxWords)
             return RVE_ERR_UNSUPPORTED;
-        blk.dst[i] = static_cast<uint32_t*>(segs[i].dst);
-        blk.first[i] = words;
-        blk.count[i] = uint32_t(segs[i].bytes / 4);
-        if (segs[i].bytes) memcpy(blk.data + words, segs[i].src, segs[i].bytes);
+        blk->dst[i] = static_cast<uint32_t*>(segs[i].dst);
+        blk->first[i] = words;
+        blk->count[i] = uint32_t(segs[i].bytes / 4);
+        if (segs[i].bytes) memcpy(blk->data + words, segs[i].src, segs[i].bytes);
         words += uint32_t(segs[i].bytes / 4);
     }
-    if (!words) return 0;
-    blk.n = n;
-    upload_params_kernel<<<n, 128, 0, ctx->stream>>>(blk);
+    if (words) blk->n = n;
+    return 0;
+}
+
+int upload_block(rve_ctx* ctx, const UploadBlock& blk) {
+    if (!blk.n) return 0;
+    upload_params_kernel<<<blk.n, 128, 0, ctx->stream>>>(blk);
     ctx->launches++;
     RVE_CUDA(cudaGetLastError());
     return 0;
+}
+
+int upload_batch_raw(rve_ctx* ctx, const RawSegment* segs, uint32_t n) {
+    UploadBlock blk{};
+    const int rc = make_upload_block(segs, n, &blk);
+    if (rc) return rc;
+    return upload_block(ctx, blk);
 }
 }  // namespace rve
 

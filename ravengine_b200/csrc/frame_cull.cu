@@ -164,6 +164,9 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     const uint32_t groups = uint32_t(std::ceil(totalEntities / 64.f));
     const uint32_t passes = passByPass ? nviews : 1u;
     uint32_t cullFlags = 0;
+    UploadBlock carryBlk;  // tables of a fused encode, written by its pyramid launch
+    carryBlk.n = 0;
+    bool haveCarry = false;
     for (uint32_t pass = 0; pass < passes; ++pass) {
         std::vector<RveCullingUBOinstance> cuboPass = cuboStaging;
         if (passByPass)
@@ -193,7 +196,13 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
             for (auto& lp : lodHost)
                 if (!lp) lp = kNoLods;
             if (ok && cull_host_tables(ctx, cuboPass.data(), globalCubo.numCubos, lodHost.data(), &hostTables, &raw) == 0) {
-                rc = upload_batch_raw(ctx, raw.data(), uint32_t(raw.size()));
+                if (build && !nviews && !passByPass && groups > 0) {
+                    // fused encode: the pyramid launch below carries the block (pyramid_build_impl) - no launch of its own
+                    rc = make_upload_block(raw.data(), uint32_t(raw.size()), &carryBlk);
+                    haveCarry = rc == 0;
+                } else {
+                    rc = upload_batch_raw(ctx, raw.data(), uint32_t(raw.size()));
+                }
                 if (rc == 0) cullFlags = kCullTablesPrepared;
                 else if (rc != RVE_ERR_UNSUPPORTED) return rc;
             }
@@ -218,7 +227,7 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
         // upload -> pyramid build -> pyramid upper -> cull: the build is a plain launch (it starts once the tables are
         // complete), the cull a programmatic dependent of the pyramid kernels that needs them only for its Hi-Z batches
         // single view with work to do: the cull kernel below finishes the pyramid's upper levels in its start-up
-        rc = pyramid_build_impl(ctx, pyramids[0], build->depth, build->width, build->height, !nviews && groups > 0);
+        rc = pyramid_build_impl(ctx, pyramids[0], build->depth, build->width, build->height, !nviews && groups > 0, haveCarry ? &carryBlk : nullptr);
         if (rc) return rc;
         static const bool late = [] { const char* e = getenv("RVE_CULL_LATE_WAIT"); return !e || atoi(e) != 0; }();
         if ((cullFlags & kCullTablesPrepared) && late) cullFlags |= kCullLateWait;

@@ -155,6 +155,19 @@ struct RawSegment {
     size_t bytes;
 };
 int upload_batch_raw(rve_ctx* ctx, const RawSegment* segs, uint32_t n);
+// The parameter block such an upload travels in (one CTA - or CTA-sized group of threads - per segment). A kernel that is
+// launched anyway just ahead of the tables' consumer can carry it instead of upload_params_kernel (the persistent pyramid
+// kernel of a fused encode does: one launch less per frame).
+constexpr uint32_t kUploadMaxSegs = 16;
+constexpr uint32_t kUploadMaxWords = 896;  // 3.5 KB of payload: the whole block stays under the 4 KB parameter limit
+struct UploadBlock {
+    uint32_t* dst[kUploadMaxSegs];
+    uint32_t first[kUploadMaxSegs], count[kUploadMaxSegs];
+    uint32_t n;
+    uint32_t data[kUploadMaxWords];
+};
+int make_upload_block(const RawSegment* segs, uint32_t n, UploadBlock* blk);  // 0 (blk->n == 0: nothing to write) or RVE_ERR_UNSUPPORTED
+int upload_block(rve_ctx* ctx, const UploadBlock& blk);                       // upload_params_kernel
 // The tables cubo_prepare_kernel derives from a CUBO array, built on the host instead (cull.cu) for a caller that has the
 // CUBOs and the LOD distances in host memory (the shim): appended as raw segments aimed at the context's scratch tables.
 // `keep` owns the staging memory until the upload call returns.
@@ -178,7 +191,9 @@ int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel = 0
 // rve_depth_pyramid_build with an option: allowDefer lets the build stop after the tile levels (mips 0..5, footprint-min
 // level 0) and leave PyramidRec::upperPending set - the caller enqueues a cull next, whose kernel finishes the upper levels
 // in its start-up (cull_launch merges them, or runs pyramid_finish_upper first when it cannot)
-int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height, bool allowDefer);
+// `carry` (deferring builds only): tables to be written ahead of that cull; the build's kernel writes them, or they go out first
+int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height, bool allowDefer,
+                       const UploadBlock* carry = nullptr);
 int pyramid_finish_upper(rve_ctx* ctx, PyramidRec* p);  // no-op unless upperPending
 // marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)
 void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf);

@@ -354,10 +354,10 @@ __device__ __forceinline__ void pers_grid_barrier(uint32_t* sync, uint32_t G) {
     pyr::compute_sync();
 }
 
-__global__ void __launch_bounds__(kPersThreads, 2)
-pyramid_persistent_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
-                          uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH, uint32_t stages, uint32_t stageFloats, uint32_t topLevel,
-                          uint32_t* __restrict__ gridSync, const __grid_constant__ PyrOffsets offs, uint32_t debug, uint32_t deferUpper) {
+__device__ __forceinline__ void
+pyramid_persistent_body(const CUtensorMap& depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm, uint32_t dim, uint32_t levels,
+                        uint32_t boxW, uint32_t boxH, uint32_t stages, uint32_t stageFloats, uint32_t topLevel, uint32_t* __restrict__ gridSync,
+                        const PyrOffsets& offs, uint32_t debug, uint32_t deferUpper) {
     extern __shared__ __align__(128) unsigned char s_dyn[];
     __shared__ uint64_t s_full[kPersMaxStages], s_empty[kPersMaxStages];
     __shared__ float s_l2[2][kPersWarps][8];
@@ -497,6 +497,28 @@ pyramid_persistent_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t
     // footprint-min levels 1 .. topLevel-1 from the texel levels every CTA wrote before the barrier (read through L2)
     const uint32_t lastFm = topLevel < levels ? topLevel : levels;
     footmin_items(pyr, fm, offs, dim, lastFm, (G > 1 ? blockIdx.x - 1 : 0) * kPersComputeThreads + tid, (G > 1 ? G - 1 : 1) * kPersComputeThreads);
+}
+
+__global__ void __launch_bounds__(kPersThreads, 2)
+pyramid_persistent_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
+                          uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH, uint32_t stages, uint32_t stageFloats, uint32_t topLevel,
+                          uint32_t* __restrict__ gridSync, const __grid_constant__ PyrOffsets offs, uint32_t debug, uint32_t deferUpper) {
+    pyramid_persistent_body(depthMap, w, h, pyr, fm, dim, levels, boxW, boxH, stages, stageFloats, topLevel, gridSync, offs, debug, deferUpper);
+}
+
+// The same build carrying a table upload (UploadBlock, internal.h) for the kernel that follows it: the fused encode's
+// indirect-command / CUBO / prepared cull tables are written here instead of by a launch of their own.
+__global__ void __launch_bounds__(kPersThreads, 2)
+pyramid_persistent_carry_kernel(const __grid_constant__ CUtensorMap depthMap, uint32_t w, uint32_t h, float* __restrict__ pyr, float* __restrict__ fm,
+                                uint32_t dim, uint32_t levels, uint32_t boxW, uint32_t boxH, uint32_t stages, uint32_t stageFloats, uint32_t topLevel,
+                                uint32_t* __restrict__ gridSync, const __grid_constant__ PyrOffsets offs, uint32_t debug, uint32_t deferUpper,
+                                const __grid_constant__ UploadBlock carry) {
+    for (uint32_t seg = blockIdx.x; seg < carry.n; seg += gridDim.x) {
+        const uint32_t* src = carry.data + carry.first[seg];
+        uint32_t* dst = carry.dst[seg];
+        for (uint32_t i = threadIdx.x; i < carry.count[seg]; i += blockDim.x) dst[i] = src[i];
+    }
+    pyramid_persistent_body(depthMap, w, h, pyr, fm, dim, levels, boxW, boxH, stages, stageFloats, topLevel, gridSync, offs, debug, deferUpper);
 }
 
 // footprint-min chain (see PyramidRec::footmin): one thread per output, levels firstLevel.. in one launch
@@ -654,7 +676,7 @@ int pyramid_finish_upper(rve_ctx* ctx, PyramidRec* p) {
     return 0;
 }
 
-int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height, bool allowDefer) {
+int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height, bool allowDefer, const UploadBlock* carry) {
     if (!ctx) return set_error(RVE_ERR_INVALID_ARGUMENT, "ctx is null");
     RVE_PROFILE_FN_N("generatePyramid");
     DeviceGuard g(ctx->device);
@@ -733,6 +755,7 @@ int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t
                         const size_t bytes = std::max<size_t>(st * stageBytes, sizeof(float) * (kPyrTile * kPyrTile + (kPyrTile * kPyrTile) / 3 + 2));
                         if (bytes > ctx->pyramid_pers_smem_opt_in) {
                             RVE_CUDA(cudaFuncSetAttribute(pyramid_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
+                            RVE_CUDA(cudaFuncSetAttribute(pyramid_persistent_carry_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(bytes)));
                             ctx->pyramid_pers_smem_opt_in = bytes;
                         }
                         int occ = 0;  // the grid barrier needs every CTA resident
@@ -745,15 +768,32 @@ int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t
                     const PyrOffsets offs = make_pyr_offsets(p->dim, p->levels);
                     const char* dbgEnv = getenv("RVE_PYRAMID_DEBUG");  // development only: 1 no upper phase, 2 no grid barrier, 4 no tile work, 8 no loads
                     const uint32_t dbg = dbgEnv ? uint32_t(atoi(dbgEnv)) : 0u;
-                    pyramid_persistent_kernel<<<p->persGrid, kPersThreads, p->persSmem, ctx->stream>>>(
-                        *reinterpret_cast<const CUtensorMap*>(p->depthMap), width, height, pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH, p->persStages,
-                        p->persStageFloats, topLevel, static_cast<uint32_t*>(sync->ptr), offs, dbg, wantDefer ? 1u : 0u);
+                    // a carried upload is written by this launch only when the consumer waits for the launch's completion at its
+                    // entry - the cull of a deferring build does
+                    if (carry && carry->n && wantDefer) {
+                        pyramid_persistent_carry_kernel<<<p->persGrid, kPersThreads, p->persSmem, ctx->stream>>>(
+                            *reinterpret_cast<const CUtensorMap*>(p->depthMap), width, height, pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH,
+                            p->persStages, p->persStageFloats, topLevel, static_cast<uint32_t*>(sync->ptr), offs, dbg, 1u, *carry);
+                    } else {
+                        if (carry) {
+                            const int urc = upload_block(ctx, *carry);
+                            if (urc) return urc;
+                        }
+                        pyramid_persistent_kernel<<<p->persGrid, kPersThreads, p->persSmem, ctx->stream>>>(
+                            *reinterpret_cast<const CUtensorMap*>(p->depthMap), width, height, pyrPtr, fmPtr, p->dim, p->levels, p->boxW, p->boxH,
+                            p->persStages, p->persStageFloats, topLevel, static_cast<uint32_t*>(sync->ptr), offs, dbg, wantDefer ? 1u : 0u);
+                    }
                     ctx->launches++;
                     RVE_CUDA(cudaGetLastError());
                     p->footmin_valid = true;
                     p->upperPending = wantDefer;
                     return 0;
                 }
+            }
+            if (carry) {  // no persistent launch took it along
+                const int urc = upload_block(ctx, *carry);
+                if (urc) return urc;
+                carry = nullptr;
             }
             if (p->mapBase == d->ptr && smem <= 96 * 1024) {
                 if (smem > ctx->pyramid_smem_opt_in) {
@@ -765,6 +805,10 @@ int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t
                                                                                    wantDefer ? static_cast<uint32_t*>(sync->ptr) : nullptr);
                 tma = true;
             }
+        }
+        if (carry) {  // (images that do not qualify for TMA at all)
+            const int urc = upload_block(ctx, *carry);
+            if (urc) return urc;
         }
         if (!tma)
             pyramid_build_kernel<<<blocks, kPyrThreads, 0, ctx->stream>>>(static_cast<const float*>(d->ptr), width, height, pyrPtr, fmPtr, p->dim,
