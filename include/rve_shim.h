@@ -65,10 +65,11 @@ RVE_API int rvs_material_set_command_entities(rvs_world* w, uint32_t material, u
 RVE_API int rvs_cull_static(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
                             uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid);
 /* generatePyramid for the camera's target (src/RenderEngine_Draw.cpp:2475-2514) and cullTheRenderData for that camera
- * (:1221-1407) as ONE encode: the pass tables go up first, then the pyramid kernels, then the cull as a programmatic
- * dependent launch that needs the pyramid only for its Hi-Z batches. (Letting the cull become resident before the pyramid
- * grids drain is possible - RVE_UPPER_TRIGGER=1 - but measured slower on B200, so by default it launches as they drain.)
- * Same results as rve_depth_pyramid_build followed by rvs_cull_static. */
+ * (:1221-1407) as ONE encode of two launches: a persistent pyramid kernel that builds the tile levels (mips 0..5) and
+ * writes the pass tables it carries as a parameter block, then the cull, whose first CTAs derive the pyramid's upper
+ * levels while the first frustum phases run (every warp checks that they are done before its first Hi-Z batch).
+ * Same results as rve_depth_pyramid_build followed by rvs_cull_static - including the complete pyramid, which other
+ * consumers may read once this call's work has run. RVE_PYRAMID_DEFER=0 keeps upload, pyramid (two launches) and cull apart. */
 RVE_API int rvs_cull_static_with_pyramid(rvs_world* w, const float view_proj[16], const float cam_pos[3], uint32_t camera_layers,
                                          uint32_t shadow_pass, uint32_t pass_mask, rve_pyramid pyramid, rve_buffer depth,
                                          uint32_t depth_width, uint32_t depth_height);

@@ -8,6 +8,9 @@
 // per entry while one extra block reduces the remaining 32x32 image (mips 6..10) and their
 // footprint-min levels out of shared memory. No ticket counter, no grid-wide fence, no serial tail
 // inside the big kernel (the r01l ncu capture had 45 % of its samples there).
+// r02f: pyramid_persistent_kernel (further down) builds the tile levels from a TMA ring with register / shuffle tiles; as
+// part of a fused encode it stops there and the cull kernel that follows derives the upper levels in its start-up
+// (pyramid_build_impl / PyramidRec::upperPending).
 //
 // Sampler model = oracle.cpp sample_min(): min over the clamped 2x2 bilinear footprint
 // floor(u*W-0.5)+{0,1} (src/RenderEngine.cpp:323-331, reduction mode Minimum).
