@@ -114,6 +114,7 @@ PROTOTYPES = {
     "rve_depth_pyramid_info": (C.c_int, [VP, u32, C.POINTER(u32), C.POINTER(u32), C.POINTER(u32)]),
     "rve_depth_pyramid_footmin": (C.c_int, [VP, u32, C.POINTER(u32)]),
     "rve_depth_pyramid_build": (C.c_int, [VP, u32, u32, u32, u32]),
+    "rve_depth_pyramid_build_deferred": (C.c_int, [VP, u32, u32, u32, u32]),
     "rve_depth_pyramid_texels_changed": (C.c_int, [VP, u32]),
     "rve_cull": (C.c_int, [VP, C.POINTER(CullingUBO), u32, u32, u32, u32, u32, u32]),
     "rve_sort_entity_ids": (C.c_int, [VP, u32, u32, u32, u32]),

@@ -174,8 +174,10 @@ class Context:
         nbytes = self.lib.rve_buffer_size(self.h, tex.value)
         return Pyramid(out.value, dim.value, lv.value, Buffer(self, tex.value, nbytes))
 
-    def build_pyramid(self, pyr: Pyramid, depth: Buffer, width: int, height: int) -> None:
-        _check(self.lib, self.lib.rve_depth_pyramid_build(self.h, pyr.handle, depth.handle, width, height))
+    def build_pyramid(self, pyr: Pyramid, depth: Buffer, width: int, height: int, deferred: bool = False) -> None:
+        """rve_depth_pyramid_build; deferred=True: rve_depth_pyramid_build_deferred (the cull enqueued next finishes the upper levels)"""
+        fn = self.lib.rve_depth_pyramid_build_deferred if deferred else self.lib.rve_depth_pyramid_build
+        _check(self.lib, fn(self.h, pyr.handle, depth.handle, width, height))
 
     def pyramid_footmin(self, pyr: Pyramid) -> Buffer:
         """rve_depth_pyramid_footmin: the derived footprint-min chain the cull samples (inspection only)"""

@@ -641,6 +641,10 @@ int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uin
     return pyramid_build_impl(ctx, pyr, depth, width, height, false);
 }
 
+int rve_depth_pyramid_build_deferred(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height) {
+    return pyramid_build_impl(ctx, pyr, depth, width, height, true);
+}
+
 }  // extern "C"
 
 namespace rve {

@@ -26,7 +26,7 @@ def oracle_cull(tables, ubo, model, layers, flags, pyr, dim, levels, groups=None
     return bl
 
 
-def device_cull(ctx, tables, ubo, model, layers, flags, depth=None, pyr_width=1024, groups=None, pyramid_texels=None):
+def device_cull(ctx, tables, ubo, model, layers, flags, depth=None, pyr_width=1024, groups=None, pyramid_texels=None, deferred=False):
     """Same inputs through rve_cull. Returns the downloaded bindless list (same indexing as the oracle's)."""
     dev = [ctx.buffer_from_numpy(b) for b in tables.bindless]
     cubos = tables.cubos.copy()
@@ -39,7 +39,7 @@ def device_cull(ctx, tables, ubo, model, layers, flags, depth=None, pyr_width=10
     pyr = ctx.create_pyramid(pyr_width)
     if depth is not None:
         d_depth = ctx.buffer_from_numpy(depth)
-        ctx.build_pyramid(pyr, d_depth, depth.shape[1], depth.shape[0])
+        ctx.build_pyramid(pyr, d_depth, depth.shape[1], depth.shape[0], deferred=deferred)
     elif pyramid_texels is not None:
         pyr.texels.upload(pyramid_texels)
     groups = (tables.total_entities + 63) // 64 if groups is None else groups

@@ -33,7 +33,7 @@ def _scene(n, seed, n_mats=2, lods=(math.inf,), extent=200.0, extent_y=200.0, fl
 
 
 def _run_both(ctx, model, layers, flags, mats, cam, depth=None, pyr_width=1024, shadow=False, cam_layers=0xFFFFFFFF,
-              groups=None, nthreads=4):
+              groups=None, nthreads=4, deferred=False):
     t = host_tables.build_static_tables(mats)
     ubo = make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos, layers=cam_layers, shadow=shadow)
     if depth is not None:
@@ -42,7 +42,7 @@ def _run_both(ctx, model, layers, flags, mats, cam, depth=None, pyr_width=1024, 
         dim, levels = oracle.pyramid_dims(pyr_width)
         pyr = np.zeros((4 * dim * dim - 1) // 3, np.float32)
     ref = oracle_cull(t, ubo, model, layers, flags, pyr, dim, levels, groups=groups, nthreads=nthreads)
-    got, pyr_dev = device_cull(ctx, t, ubo, model, layers, flags, depth=depth, pyr_width=pyr_width, groups=groups)
+    got, pyr_dev = device_cull(ctx, t, ubo, model, layers, flags, depth=depth, pyr_width=pyr_width, groups=groups, deferred=deferred)
     np.testing.assert_array_equal(pyr, pyr_dev)
     compare_cull_outputs(t, mats, ref, got)
     return t, ref
@@ -299,3 +299,66 @@ def test_garbage_in_the_unwritten_cubo_tail_is_never_followed(ctx):
     np.testing.assert_array_equal(got3[h0], ref[h0])
     h1 = int(t.cubos[1]["indirectOutputBufferBindlessHandle"])
     assert not got3[h1][:, 1].any()  # the broken command drew nothing
+
+
+@pytest.mark.parametrize("n,size", [(40, (640, 360)), (5000, (640, 360)), (300_000, (640, 360)), (300_000, (3840, 2160)), (2_000_000, (1920, 1080)),
+                                    (5000, (36, 32))])
+def test_deferred_pyramid_build_is_finished_by_the_cull_that_follows(ctx, n, size):
+    """rve_depth_pyramid_build_deferred + rve_cull: the build stops after the tile levels, the cull kernel derives mips >= 6 and
+    footprint-min levels >= 1 in its start-up (one worker CTA for the smallest dispatch, 3 x 148 for the largest) - same
+    pyramid, same cull as the oracle's."""
+    model, layers, flags, mats = _scene(n, 17, n_mats=2, lods=(0.0, 40.0, 120.0), extent=400.0, extent_y=60.0, flags_val=0xFFFF, frac_nocull=0.1)
+    cam = scenes.default_camera(z_far=1000.0)
+    depth = scenes.synth_depth(size[0], size[1], cam, n_occluders=30)
+    _run_both(ctx, model, layers, flags, mats, cam, depth=depth, pyr_width=min(size), nthreads=oracle.default_workers(), deferred=True)
+
+
+def test_deferred_pyramid_build_is_finished_for_every_other_consumer(ctx):
+    """A deferring build followed by something that is not a single-view cull: the footprint-min accessor and a view batch each
+    complete the pyramid with a launch of their own first (pyramid_finish_upper); a second build supersedes a pending one."""
+    from ravengine_b200.world import World
+
+    rng = np.random.default_rng(5)
+    w_, h_ = 1280, 720
+    cam = scenes.default_camera(z_far=1000.0)
+    depth_a, depth_b = rng.random((h_, w_), dtype=np.float32), scenes.synth_depth(w_, h_, cam, n_occluders=25)
+    d_a, d_b = ctx.buffer_from_numpy(depth_a), ctx.buffer_from_numpy(depth_b)
+    pyr = ctx.create_pyramid(h_)
+    ref_a, dim, levels = oracle.pyramid_build(depth_a, h_)
+    ref_b, _, _ = oracle.pyramid_build(depth_b, h_)
+    # accessor
+    ctx.build_pyramid(pyr, d_a, w_, h_, deferred=True)
+    fm = ctx.pyramid_footmin(pyr).download(np.float32)
+    np.testing.assert_array_equal(footmin_chain(ref_a, dim, levels), fm[: footmin_chain(ref_a, dim, levels).size])
+    np.testing.assert_array_equal(ref_a, pyr.texels.download(np.float32))
+    # pending build superseded by another deferring build, then a view batch
+    ctx.build_pyramid(pyr, d_a, w_, h_, deferred=True)
+    ctx.build_pyramid(pyr, d_b, w_, h_, deferred=True)
+    n = 20_000
+    model, layers, flags, mats = _scene(n, 23, n_mats=2, lods=(0.0, 40.0, 120.0), extent=400.0, extent_y=60.0, flags_val=0xFFFF)
+    outs = []
+    for deferred in (True, False):
+        w = World(ctx)
+        bufs = [ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(layers), ctx.buffer_from_numpy(flags)]
+        w.set_entity_buffers(*bufs)
+        mids = []
+        for m in mats:
+            mid = w.material()
+            for c in m.commands:
+                k = len(c.mesh.lod_distances)
+                mesh = w.mesh_collection(c.mesh.radius, c.mesh.lod_distances, [36, 24, 12][:k], [0, 36, 60][:k], [0, 24, 40][:k])
+                ids = ctx.buffer_from_numpy(c.entity_ids)
+                bufs.append(ids)
+                w.add_command(mid, mesh, ids, len(c.entity_ids))
+            mids.append(mid)
+        if not deferred:
+            ctx.build_pyramid(pyr, d_b, w_, h_)
+        views = [(cam.view_proj_cm, cam.pos, 0xFFFFFFFF, False)] * 2
+        w.cull_static_views(views, [pyr, pyr])
+        ctx.synchronize()
+        outs.append([(w.material_outputs(m)[1].download(np.uint32), np.sort(w.material_outputs(m)[0].download(np.uint32))) for m in mids])
+        np.testing.assert_array_equal(ref_b, pyr.texels.download(np.float32))
+        w.destroy()
+    for (i0, s0), (i1, s1) in zip(*outs):
+        np.testing.assert_array_equal(i0, i1)
+        np.testing.assert_array_equal(s0, s1)
