@@ -168,8 +168,9 @@ class DeviceScene:
         if before_cull or os.environ.get("RVE_BENCH_SPLIT_STEP") == "1":
             # N > 1: the pyramid build does not touch the indirect buffers, so it is enqueued BEFORE the wait for last frame's
             # count exchange (before_cull) and runs while the slowest peer catches up (the fused order cost 15 us per step at N = 8)
-            # (a deferring build: the cull below finishes the pyramid's upper levels in its start-up, like the fused encode)
-            self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1], deferred=os.environ.get("RVE_BENCH_NO_DEFER") != "1")
+            # (a complete build: here it runs in the shadow of that wait, so deferring its upper levels into the cull only
+            # lengthens the cull - N=2: 165.5 us per step as it is, 167.6 us with rve_depth_pyramid_build_deferred; RVE_BENCH_DEFER=1)
+            self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1], deferred=os.environ.get("RVE_BENCH_DEFER") == "1")
             if before_cull:
                 before_cull()
             self.world.cull_static(self.vp, self.cam_pos, self.pyr)
@@ -433,8 +434,8 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                               "derives the rest in its start-up - kernel_ms contains that work (about +2.3 us; 144.4 us = 0.80 of peak without it: "
                               "profiles/r02f_pyramid_variants.txt), algorithmic_bytes_per_launch does not count it"
                               if world_size == 1 and os.environ.get("RVE_BENCH_SPLIT_STEP") != "1" and os.environ.get("RVE_PYRAMID_DEFER") != "0"
-                              else "pyramid build (deferring: tile levels only) and cull are separate calls here - the build is enqueued before the wait "
-                                   "for last frame's count exchange; kernel_ms contains the pyramid's upper levels as in the fused encode")},
+                              else "pyramid build (complete, two launches) and cull are separate calls here - the build is enqueued before the wait "
+                                   "for last frame's count exchange and runs in its shadow")},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
         "ms_per_step_by_rank": by_rank, "cull_kernel_ms_by_rank": cull_by_rank,
         "visible_per_slot": counts.tolist(),
