@@ -144,27 +144,54 @@ class DeviceScene:
         self.t_depth = torch.from_numpy(depth).to(dev)
         self.depth = c.wrap_tensor(self.t_depth)
         self.pyr = c.create_pyramid(min(C2["depth"]))
-        self.world = World(c)
-        self.world.set_entity_buffers(self.model, self.layers, self.flags)
+        self.id_slices = []
+        self.world, self.mats = self._make_world()
+        self.worlds, self.mats_of = [self.world], [self.mats]
+        self.vp, self.cam_pos = self.cam.view_proj_cm, self.cam.pos
+        self.slots = C2["materials"] * len(C2["lod_distances"])
+        c.synchronize()
+
+    def _make_world(self):
+        """a render world over the scene's entity arrays: its own materials, commands and output (indirect / culling) buffers"""
+        from ravengine_b200.world import World
+
+        c, n = self.ctx, self.n
+        world = World(c)
+        world.set_entity_buffers(self.model, self.layers, self.flags)
         m = C2["materials"]
         bounds = [n * i // m for i in range(m + 1)]
-        self.id_slices, self.mats = [], []
+        mats = []
         for i in range(m):
             cnt = bounds[i + 1] - bounds[i]
             sl = c.wrap_tensor(self.t_ids[bounds[i]:bounds[i + 1]]) if cnt else c.create_buffer(16)
             radius = 1.7320508 if i % 2 == 0 else 1.74  # meshes/cube.obj, meshes/sphere.obj
-            mesh = self.world.mesh_collection(radius, C2["lod_distances"], [36, 24, 12], [0, 36, 60], [0, 24, 40])
-            mat = self.world.material()
-            self.world.add_command(mat, mesh, sl, cnt)
+            mesh = world.mesh_collection(radius, C2["lod_distances"], [36, 24, 12], [0, 36, 60], [0, 24, 40])
+            mat = world.material()
+            world.add_command(mat, mesh, sl, cnt)
             self.id_slices.append(sl)
-            self.mats.append(mat)
-        self.vp, self.cam_pos = self.cam.view_proj_cm, self.cam.pos
-        self.slots = m * len(C2["lod_distances"])
-        c.synchronize()
+            mats.append(mat)
+        return world, mats
 
-    def step(self, before_cull=None):
+    def add_frame_slot(self) -> int:
+        """Second frame in flight: another world over the same entity arrays, i.e. a second set of indirect-command and culling
+        buffers, so that frame f+1's encode does not have to wait until frame f's counts have been read (N > 1: the exchange
+        kernel on the side stream). Returns the slot index for step(slot=..)."""
+        w, mats = self._make_world()
+        self.worlds.append(w)
+        self.mats_of.append(mats)
+        self.ctx.synchronize()
+        return len(self.worlds) - 1
+
+    def step(self, before_cull=None, slot: int = 0, fused: bool = False):
         """one pass of the hot path for one view: pyramid build + table build/upload + indirect re-init + cull, as one encode
-        (rvs_cull_static_with_pyramid); RVE_BENCH_SPLIT_STEP=1 issues the two reference-shaped calls instead"""
+        (rvs_cull_static_with_pyramid); RVE_BENCH_SPLIT_STEP=1 issues the two reference-shaped calls instead. slot: which
+        frame slot's world (output buffers) the pass writes; fused=True with before_cull: the wait first, then the one encode
+        (two frames in flight: the wait is for the exchange of two frames ago and does not stall)"""
+        if fused and os.environ.get("RVE_BENCH_SPLIT_STEP") != "1":
+            if before_cull:
+                before_cull()
+            self.worlds[slot].cull_static_with_pyramid(self.vp, self.cam_pos, self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
+            return
         if before_cull or os.environ.get("RVE_BENCH_SPLIT_STEP") == "1":
             # N > 1: the pyramid build does not touch the indirect buffers, so it is enqueued BEFORE the wait for last frame's
             # count exchange (before_cull) and runs while the slowest peer catches up (the fused order cost 15 us per step at N = 8)
@@ -173,14 +200,14 @@ class DeviceScene:
             self.ctx.build_pyramid(self.pyr, self.depth, C2["depth"][0], C2["depth"][1], deferred=os.environ.get("RVE_BENCH_DEFER") == "1")
             if before_cull:
                 before_cull()
-            self.world.cull_static(self.vp, self.cam_pos, self.pyr)
+            self.worlds[slot].cull_static(self.vp, self.cam_pos, self.pyr)
             return
-        self.world.cull_static_with_pyramid(self.vp, self.cam_pos, self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
+        self.worlds[slot].cull_static_with_pyramid(self.vp, self.cam_pos, self.pyr, self.depth, C2["depth"][0], C2["depth"][1])
 
-    def visible_counts(self) -> np.ndarray:
+    def visible_counts(self, slot: int = 0) -> np.ndarray:
         out = []
-        for mat in self.mats:
-            _, ind, lods, _ = self.world.material_outputs(mat)
+        for mat in self.mats_of[slot]:
+            _, ind, lods, _ = self.worlds[slot].material_outputs(mat)
             out.append(ind.download(np.uint32).reshape(-1, 5)[:lods, 1])
         return np.concatenate(out)
 
@@ -195,7 +222,8 @@ class DeviceScene:
     def release(self):
         """free the scene's device memory (the C5 scene needs the room at N = 1)"""
         self.ctx.synchronize()
-        self.world.destroy()
+        for w in self.worlds:
+            w.destroy()
         self.ctx.close()
         for k in ("t_model", "t_layers", "t_flags", "t_ids", "t_depth"):
             setattr(self, k, None)
@@ -309,7 +337,20 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # N > 1: two frames in flight. Each frame slot has its own indirect / culling buffers, so a frame's encode does not wait
+    # for the previous frame's count exchange (side stream) to have read them, and the step is the same fused encode as at N = 1.
+    two_frames = world_size > 1 and not args.one_frame_in_flight
+    if two_frames:
+        ex.add_frame_slot(sc.worlds[sc.add_frame_slot()], sc.mats_of[1])
+    frame = [0]
+
     def one_step():
+        if two_frames:
+            slot = frame[0] & 1
+            frame[0] += 1
+            sc.step(lambda: ex.begin_cull(slot), slot=slot, fused=True)
+            ex.exchange(slot=slot)
+            return
         sc.step(ex.begin_cull if ex else None)
         if ex:
             ex.exchange()
@@ -425,7 +466,9 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                    "device_of_rank0": device, "placement": args.placement,
                    "sharding": ("instance range per rank; per-slot counts exchanged by "
                                 + ("one kernel over NVLink peer memory (peer stores + flags + scan)" if ex_mode == "p2p"
-                                   else "NCCL all-gather + device offset scan")) if world_size > 1 else "single GPU"},
+                                   else "NCCL all-gather + device offset scan")
+                                + ("; two frames in flight (two sets of indirect / culling buffers: a frame's encode does not wait for "
+                                   "the previous frame's exchange)" if two_frames else "; one frame in flight")) if world_size > 1 else "single GPU"},
         "roofline": {"bound": "hbm", "kernel": "cull_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": cull_avg_ms, "slots": slots,
@@ -433,7 +476,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
                      "note": ("fused encode: the pyramid launch stops after the tile levels (mips 0..5, footprint-min level 0) and cull_kernel "
                               "derives the rest in its start-up - kernel_ms contains that work (about +2.3 us; 144.4 us = 0.80 of peak without it: "
                               "profiles/r02f_pyramid_variants.txt), algorithmic_bytes_per_launch does not count it"
-                              if world_size == 1 and os.environ.get("RVE_BENCH_SPLIT_STEP") != "1" and os.environ.get("RVE_PYRAMID_DEFER") != "0"
+                              if (world_size == 1 or two_frames) and os.environ.get("RVE_BENCH_SPLIT_STEP") != "1" and os.environ.get("RVE_PYRAMID_DEFER") != "0"
                               else "pyramid build (complete, two launches) and cull are separate calls here - the build is enqueued before the wait "
                                    "for last frame's count exchange and runs in its shadow")},
         "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks, "host_enqueue_ms_per_step": host_enqueue_ms,
@@ -1009,6 +1052,8 @@ def main():
                     help="100 %-dirty transform upload: copy engine into staging + expand kernels (RVS_SYNC_FULL) or one zero-copy kernel (RVS_SYNC_FULL_PULL)")
     ap.add_argument("--e2e-headline-only", action="store_true", help="skip the by_layout / by_dirty_fraction e2e variants")
     ap.add_argument("--placement", default="spread", choices=["spread", "packed"], help="rank -> GPU mapping when the box has more GPUs than ranks")
+    ap.add_argument("--one-frame-in-flight", action="store_true",
+                    help="N>1: one set of output buffers (r02c behaviour): every frame's encode waits for the previous frame's count exchange")
     ap.add_argument("--no-balance", action="store_true", help="N>1: never forward part of a slow rank's upload through a faster rank's link")
     ap.add_argument("--no-numa-bind", action="store_true", help="leave the process where the launcher put it (diagnostics)")
     ap.add_argument("--no-gather", action="store_true", help="N>1: skip the device-side id gather leg")

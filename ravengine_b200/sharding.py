@@ -210,15 +210,33 @@ class ShardedCull:
             self.b_off.append(self.ctx2.wrap_tensor(self.t_off[i]))
             self.b_tot.append(self.ctx2.wrap_tensor(self.t_tot[i]))
         self.k = 0
-        self._indirect = None
-        self._indirect2 = None
-        self.pending = None
+        # Frame slots: with two frames in flight every slot has its own world (its own indirect / culling buffers), so the
+        # exchange of frame f reads slot f & 1 while the cull of frame f + 1 re-initialises the other one - no wait between
+        # them (add_frame_slot). Slot 0 is the world passed to the constructor.
+        self.targets = [(world_obj, materials)]
+        self._indirect = [None]
+        self._indirect2 = [None]
+        self._pending = [None]
         # fused: the exchange kernel gathers the counts itself (one launch less on the cull's stream); RVE_EXCHANGE_FUSED=0
         # restores the separate gather launch
         self.fused = os.environ.get("RVE_EXCHANGE_FUSED", "1") == "1" and not self.inline
         self.rank, self.mode = rank, "nccl"
         if world_size > 1 and exchange in ("auto", "p2p"):
             self._setup_p2p(strict=exchange == "p2p")
+
+    def add_frame_slot(self, world_obj, materials: list[int]) -> int:
+        """A second (third ..) set of output buffers: a world with the same materials / commands as slot 0's. Returns its slot."""
+        self.targets.append((world_obj, materials))
+        self._indirect.append(None)
+        self._indirect2.append(None)
+        self._pending.append(None)
+        if getattr(self, "_local_ids2", None) is not None:
+            self._local_ids2.append(None)
+        return len(self.targets) - 1
+
+    @property
+    def pending(self):
+        return self._pending[0]
 
     def _setup_p2p(self, strict: bool) -> None:
         """Mailboxes: one cudaMalloc block per rank, zero-filled, exchanged as CUDA IPC handles through the process group."""
@@ -281,7 +299,7 @@ class ShardedCull:
                 self._dst[q] = self.global_ids if q == self.rank else [self.ctx2.ipc_import(h, max(4 * n, 16))
                                                                         for h, n in zip(allh[q], self.gplan.global_slots)]
             self._gather_boxes = self.peers
-        self._local_ids2 = None
+        self._local_ids2 = [None] * len(self.targets)
 
     def _solo_mailbox(self):
         self.mailbox = self.ctx2.create_buffer(self.ctx2.mailbox_bytes(1, self.slots))
@@ -291,51 +309,53 @@ class ShardedCull:
         self.peers = [self.mailbox]
         return self.mailbox
 
-    def gather(self, b: int) -> None:
+    def gather(self, b: int, slot: int = 0) -> None:
         """Enqueue the id gather of the exchange that just filled buffer set `b` (side stream, behind the exchange kernel)."""
         import torch
 
-        if self._local_ids2 is None:  # this rank's culling buffers, seen from the side-stream context
-            bufs = [self.world_obj.material_outputs(m)[0] for m in self.mats]
-            self._local_ids2 = [self.ctx2.wrap_pointer(x.ptr, x.nbytes, keepalive=x) for x in bufs]
+        if self._local_ids2[slot] is None:  # this rank's culling buffers, seen from the side-stream context
+            w, mats = self.targets[slot]
+            bufs = [w.material_outputs(m)[0] for m in mats]
+            self._local_ids2[slot] = [self.ctx2.wrap_pointer(x.ptr, x.nbytes, keepalive=x) for x in bufs]
         mask = sum(1 << q for q in self.consumers)
-        self.ctx2.gather_ids_p2p(self._local_ids2, self.gplan, self._dst, mask, self.id_base, self.b_off[b], self.b_tot[b],
+        self.ctx2.gather_ids_p2p(self._local_ids2[slot], self.gplan, self._dst, mask, self.id_base, self.b_off[b], self.b_tot[b],
                                  self._gather_boxes, self.rank, self.ws, self.k, self.status)
         self.done[b] = torch.cuda.Event()
         self.done[b].record(self.side)
-        self.pending = self.done[b]  # the next cull rewrites the local slices: it must wait for this gather too
+        self._pending[slot] = self.done[b]  # the next cull of this slot rewrites the local slices: it must wait for this gather too
 
-    def _indirect_buffers(self):
-        bufs = [self.world_obj.material_outputs(m)[1] for m in self.mats]
-        return bufs
+    def _indirect_buffers(self, slot: int = 0):
+        w, mats = self.targets[slot]
+        return [w.material_outputs(m)[1] for m in mats]
 
-    def exchange(self, refresh_buffers: bool = False) -> int:
-        """Returns the index (0/1) of the buffer set this frame's counts / offsets / totals land in."""
+    def exchange(self, refresh_buffers: bool = False, slot: int = 0) -> int:
+        """Returns the index (0/1) of the buffer set this frame's counts / offsets / totals land in. `slot`: the frame slot
+        (world) whose cull has just been enqueued."""
         import torch
         import torch.distributed as dist
 
         b = self.k & 1
         self.k += 1
-        if self._indirect is None or refresh_buffers:  # handles change only when the shim reallocates (entity counts changed)
-            self._indirect = self._indirect_buffers()
-            self._indirect2 = None
+        if self._indirect[slot] is None or refresh_buffers:  # handles change only when the shim reallocates (entity counts changed)
+            self._indirect[slot] = self._indirect_buffers(slot)
+            self._indirect2[slot] = None
         if self.mode == "p2p" and self.fused:
             # no launch on the cull's stream at all: the exchange kernel (side stream) reads the counts out of the
-            # indirect buffers itself; begin_cull() keeps the next frame's re-initialisation behind it
-            if self._indirect2 is None:
-                self._indirect2 = [self.ctx2.wrap_pointer(x.ptr, x.nbytes, keepalive=x) for x in self._indirect]
+            # indirect buffers itself; begin_cull() keeps the slot's next re-initialisation behind it
+            if self._indirect2[slot] is None:
+                self._indirect2[slot] = [self.ctx2.wrap_pointer(x.ptr, x.nbytes, keepalive=x) for x in self._indirect[slot]]
             ev = torch.cuda.Event()
             ev.record(self.stream)
             self.side.wait_event(ev)
-            self.ctx2.exchange_counts_p2p_indirect(self._indirect2, [0] * len(self.mats), self.lods, self.peers, self.rank, self.ws,
+            self.ctx2.exchange_counts_p2p_indirect(self._indirect2[slot], [0] * len(self.mats), self.lods, self.peers, self.rank, self.ws,
                                                    self.k, self.b_off[b], self.b_tot[b], self.status)
             self.done[b] = torch.cuda.Event()
             self.done[b].record(self.side)
-            self.pending = self.done[b]
+            self._pending[slot] = self.done[b]
             return b
         if self.done[b] is not None:
             self.stream.wait_event(self.done[b])  # the exchange that last used this buffer set has finished
-        self.ctx.gather_instance_counts_multi(self._indirect, [0] * len(self.mats), self.lods, self.b_local[b])
+        self.ctx.gather_instance_counts_multi(self._indirect[slot], [0] * len(self.mats), self.lods, self.b_local[b])
         ev = torch.cuda.Event()
         ev.record(self.stream)
         self.side.wait_event(ev)
@@ -355,12 +375,13 @@ class ShardedCull:
         self.done[b].record(self.side)
         return b
 
-    def begin_cull(self) -> None:
-        """Call between the pyramid build and the cull of the next frame: the cull re-initialises the indirect commands,
-        which the (fused-gather) exchange of the previous frame may still be reading on the side stream."""
-        if self.pending is not None:
-            self.stream.wait_event(self.pending)
-            self.pending = None
+    def begin_cull(self, slot: int = 0) -> None:
+        """Call before the cull of a frame (between its pyramid build and the cull when they are separate calls): the cull
+        re-initialises the slot's indirect commands, which the (fused-gather) exchange of the slot's previous frame may still
+        be reading on the side stream. With two frame slots that exchange is two frames old: the wait is over before it starts."""
+        if self._pending[slot] is not None:
+            self.stream.wait_event(self._pending[slot])
+            self._pending[slot] = None
 
     def finish(self) -> None:
         self.stream.wait_stream(self.side)
