@@ -246,6 +246,16 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
                 ts.append(time.perf_counter() - t0)
             extra["cpu"] = {"ms": float(np.median(ts)) * 1e3, "cores": workers, "kind": "port", "sample": "the full stage, median of 3"}
         yield line("pyramid", "3840x2160 depth -> 1024^2, 11 levels", med, best, algo, "hbm", extra)
+        # the build as the fused encode issues it: tile levels only (persistent kernel), the rest rides in the cull that follows
+        med, best = timed(ctx, lambda: ctx.build_pyramid(pyr, d, 3840, 2160, deferred=True), reps, flush)
+        n0 = pyr.dim
+        tile_written = 4 * sum((n0 >> l) ** 2 for l in range(6)) + 4 * (n0 + 1) ** 2  # mips 0..5 + footprint-min level 0
+        yield line("pyramid_tile_levels", "3840x2160 depth -> mips 0..5 of 1024^2 + footprint-min level 0 (rve_depth_pyramid_build_deferred: what the "
+                   "fused encode launches; mips 6..10 and footprint-min levels >= 1 are derived in the start-up of the cull that follows)",
+                   med, best, min(4 * 3840 * 2160, 16 * n0 ** 2) + tile_written, "hbm + launch latency",
+                   {"dim": pyr.dim, "l2": "flushed between launches", "dram_bytes_expected": 4 * 3840 * 2160 + tile_written,
+                    "note": "an empty launch of this kernel's shape measures 8.6 us between the same events (profiles/r02f_pyramid_variants.txt)"})
+        ctx.build_pyramid(pyr, d, 3840, 2160)  # leave the pyramid complete
 
     if want("c3"):
         nv, no, nb = 20_000, c3_objects, 64
