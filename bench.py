@@ -348,8 +348,10 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         if two_frames:
             slot = frame[0] & 1
             frame[0] += 1
-            sc.step(lambda: ex.begin_cull(slot), slot=slot, fused=True)
-            ex.exchange(slot=slot)
+            dbg = os.environ.get("RVE_BENCH_EXCHANGE_DEBUG", "")  # timing experiments only: "nowait" skips begin_cull, "noexchange" the exchange
+            sc.step(None if dbg else (lambda: ex.begin_cull(slot)), slot=slot, fused=True)
+            if dbg != "noexchange":
+                ex.exchange(slot=slot)
             return
         sc.step(ex.begin_cull if ex else None)
         if ex:
