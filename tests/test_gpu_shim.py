@@ -373,7 +373,7 @@ def test_frame_encode_equals_the_reference_pass_schedule(ctx):
     w2.destroy()
 
 
-@pytest.mark.parametrize("n,size", [(6000, (512, 288)), (300_000, (3840, 2160)), (6000, (100, 37))])
+@pytest.mark.parametrize("n,size", [(6000, (512, 288)), (300_000, (3840, 2160)), (6000, (100, 37)), (6000, (101, 50)), (6000, (30, 20))])
 def test_fused_pyramid_and_cull_encode_matches_oracle(ctx, n, size):
     """rvs_cull_static_with_pyramid (tables -> pyramid kernels -> cull overlapping the pyramid's tail, its programmatic
     dependency wait moved to the first Hi-Z batch) gives the oracle's pyramid and the oracle's cull, frame after frame
