@@ -224,6 +224,22 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
         yield cull_case(ctx, 10_000_000, (0.0, 40.0, 120.0), True, True, (3840, 2160), reps,
                         "C2 variant: fully shuffled lists through their ascending device copies", None, False, SORT_ENTITY_LISTS)
 
+    if want("c2sorted"):
+        # what rebuilding one such copy costs (rve_sort_entity_ids: memset + 4 launches; the shim does it when a list changed)
+        n_ids, id_space = 2_500_000, 10_000_000
+        rng = np.random.default_rng(4)
+        src = ctx.buffer_from_numpy(rng.choice(id_space, size=n_ids, replace=False).astype(np.uint32))
+        dst = ctx.create_buffer(4 * n_ids)
+        med, best = timed(ctx, lambda: ctx.sort_entity_ids(src, n_ids, id_space, dst), reps, flush)
+        words = (id_space + 31) // 32
+        yield line("sort_entity_ids", "one 2.5 M-entity list of the C2 scene (10 M-entity id space): bitmap set / block counts / scan / expand", med, best,
+                   8 * n_ids + 3 * 4 * words, "latency of five small launches + scattered atomicOr",
+                   {"ids": n_ids, "id_space": id_space, "gids_per_s": n_ids / med / 1e6,
+                    "note": "all four lists of C2: 4 x this; pays for itself after one cull of churned lists (0.216 -> 0.145 ms) only when the lists "
+                            "change less often than every frame"})
+        src.destroy()
+        dst.destroy()
+
     if want("pyramid"):
         cam = scenes.default_camera(z_far=1000.0)
         depth = scenes.synth_depth(3840, 2160, cam)
