@@ -378,8 +378,13 @@ RVE_API int rve_cull(rve_ctx* ctx, const RveCullingUBO* ubo, rve_buffer cubos,
  * list; the engine's lists are swap-remove dense arrays (include/RavEngine/SparseSet.hpp:34-47) and lose their runs as
  * entities come and go. A CUBO may name the sorted copy as its entityIDInputBufferBindlessHandle; rebuild it when the list
  * changed. Ids must be unique and < id_limit (the entity id space, e.g. the element count of worldTransforms); ids past
- * the limit are dropped. Bitmap pass (set bits, block counts, scan, expand): four small launches, no comparison sort. */
+ * the limit are dropped. Bitmap pass (set bits; block counts + scan + expand in one look-back pass): two launches, no
+ * comparison sort. */
 RVE_API int rve_sort_entity_ids(rve_ctx* ctx, rve_buffer entity_ids, uint32_t count, uint32_t id_limit, rve_buffer sorted_out);
+/* The same for n_lists lists of one id space (the commands of a world whose lists changed this frame) with TWO launches
+ * per 16 lists instead of two per list: one sets the bits of every list, one counts, scans (decoupled look-back) and expands. */
+RVE_API int rve_sort_entity_ids_batch(rve_ctx* ctx, uint32_t n_lists, const rve_buffer* entity_ids, const uint32_t* counts, uint32_t id_limit,
+                                      const rve_buffer* sorted_out);
 
 /* rve_sort_entity_ids without any allocation. This entry point has no counterpart in the reference; it was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving

@@ -118,6 +118,7 @@ PROTOTYPES = {
     "rve_depth_pyramid_texels_changed": (C.c_int, [VP, u32]),
     "rve_cull": (C.c_int, [VP, C.POINTER(CullingUBO), u32, u32, u32, u32, u32, u32]),
     "rve_sort_entity_ids": (C.c_int, [VP, u32, u32, u32, u32]),
+    "rve_sort_entity_ids_batch": (C.c_int, [VP, u32, C.POINTER(u32), C.POINTER(u32), u32, C.POINTER(u32)]),
     "rve_sort_entity_ids_static": (C.c_int, [VP, u32, u32, u32, u32]),
     "rve_cull_views": (C.c_int, [VP, C.POINTER(CullingUBO), u32, C.POINTER(u32), VP, u32, u32, u32, u32, u32]),
     "rve_cull_views_matrices": (C.c_int, [VP, C.POINTER(CullingUBO), u32, u32, C.POINTER(u32), C.POINTER(u32), VP, u32, u32, u32, u32, u32]),

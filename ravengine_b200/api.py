@@ -194,6 +194,14 @@ class Context:
         """rve_sort_entity_ids: ascending copy of an entity-id list (the cull's result does not depend on list order)"""
         _check(self.lib, self.lib.rve_sort_entity_ids(self.h, ids.handle, count, id_limit, out.handle))
 
+    def sort_entity_ids_batch(self, ids: list[Buffer], counts: list[int], id_limit: int, outs: list[Buffer]) -> None:
+        """rve_sort_entity_ids_batch: ascending copies of several lists of one id space, two launches per 16 lists"""
+        n = len(ids)
+        a = (C.c_uint32 * n)(*[b.handle for b in ids])
+        c = (C.c_uint32 * n)(*counts)
+        o = (C.c_uint32 * n)(*[b.handle for b in outs])
+        _check(self.lib, self.lib.rve_sort_entity_ids_batch(self.h, n, a, c, id_limit, o))
+
     def sort_entity_ids_static(self, ids: Buffer, count: int, id_limit: int, out: Buffer) -> None:
         """rve_sort_entity_ids_static: the same sort with its scratch in a fixed device array (no allocation; id_limit <=
         RVE_SORT_STATIC_MAX_IDS; calls that overlap on the GPU race)"""

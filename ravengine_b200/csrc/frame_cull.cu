@@ -52,18 +52,31 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     // a list shuffled by swap-remove erases costs the cull its tile path), rebuilt only when the list changed
     if (w->flags & RVS_SORT_ENTITY_LISTS) {
         const uint64_t idLimit = rve_buffer_size(w->ctx, w->model) / 64;
+        // every list that changed goes into ONE batch (two launches per 16 lists, rve_sort_entity_ids_batch)
+        std::vector<rve_buffer> srcs, dsts;
+        std::vector<uint32_t> counts;
+        std::vector<decltype(&w->materials[0].commands[0])> stale;
         for (auto& m : w->materials)
             for (auto& c : m.commands) {
                 if (!c.count) continue;
                 if (c.sortedValid && c.sortedOf == c.entityIds && c.sortedCount == c.count) continue;
-                int src = realloc_buffer(w, &c.sortedIds, &c.sortedBytes, c.count, sizeof(uint32_t));
+                const int src = realloc_buffer(w, &c.sortedIds, &c.sortedBytes, c.count, sizeof(uint32_t));
                 if (src) return src;
-                src = rve_sort_entity_ids(w->ctx, c.entityIds, c.count, uint32_t(std::min<uint64_t>(idLimit, 0xFFFFFFFFull)), c.sortedIds);
-                if (src) return src;
-                c.sortedOf = c.entityIds;
-                c.sortedCount = c.count;
-                c.sortedValid = true;
+                srcs.push_back(c.entityIds);
+                dsts.push_back(c.sortedIds);
+                counts.push_back(c.count);
+                stale.push_back(&c);
             }
+        if (!stale.empty()) {
+            const int src = rve_sort_entity_ids_batch(w->ctx, uint32_t(stale.size()), srcs.data(), counts.data(),
+                                                      uint32_t(std::min<uint64_t>(idLimit, 0xFFFFFFFFull)), dsts.data());
+            if (src) return src;
+            for (auto* c : stale) {
+                c->sortedOf = c->entityIds;
+                c->sortedCount = c->count;
+                c->sortedValid = true;
+            }
+        }
     }
     // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch
     uint32_t totalEntities = 0;

@@ -118,6 +118,8 @@ struct rve_ctx {
     size_t d_view_stride_cap = 0;
     void* d_sort = nullptr;  // rve_sort_entity_ids: bitmap + block sums
     size_t d_sort_cap = 0;
+    uint64_t sort_clean_geometry = 0;  // (blocks, lists) for which the sort scratch's bitmaps are known to be zero
+    bool sort_dirty = false;           // a sort was enqueued only in part: clear the scratch before the next one
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
     size_t pyramid_smem_opt_in = 48 * 1024;  // dynamic shared memory pyramid_build_tma_kernel has been opted in for
     size_t pyramid_pers_smem_opt_in = 48 * 1024;  // ... and pyramid_persistent_kernel

@@ -110,8 +110,9 @@ def test_cull_over_churned_entity_lists_matches_oracle(ctx):
 
 @pytest.mark.parametrize("count,id_limit", [(1, 1), (1, 70_000), (33, 64), (5000, 5000), (100_000, 3_000_000), (1_000_003, 33_554_433)])
 def test_sort_entity_ids_is_numpy_sort(ctx, count, id_limit):
-    """rve_sort_entity_ids (bitmap pass: set bits, block counts, scan, expand) against np.sort, over id spaces from one
-    bitmap word to several scan blocks; twice on the same context (the scratch is re-zeroed)."""
+    """rve_sort_entity_ids (bitmap pass: set bits, then block counts + look-back scan + expand in one launch) against np.sort,
+    over id spaces from one bitmap word to several thousand look-back blocks; twice on the same context (the pass leaves its
+    bitmap clean)."""
     rng = np.random.default_rng(count)
     for _ in range(2):
         ids = rng.choice(id_limit, size=count, replace=False).astype(np.uint32)
@@ -121,6 +122,33 @@ def test_sort_entity_ids_is_numpy_sort(ctx, count, id_limit):
         assert np.array_equal(dst.download(np.uint32)[:count], np.sort(ids))
         src.destroy()
         dst.destroy()
+
+
+def test_sort_entity_ids_batch_is_numpy_sort_per_list(ctx):
+    """rve_sort_entity_ids_batch: several lists of one id space in two launches per 16 lists (bits of every list set by one
+    launch; counts + look-back scan + expansion by the other). Lists of very different lengths, an empty one, more than 16,
+    ids past the limit (dropped), and batches of different geometry back to back (the scratch is re-zeroed when it changes)."""
+    rng = np.random.default_rng(77)
+    for id_limit, counts in ((3_000_000, [250_000, 1, 0, 40_000, 999_999]), (64, [3, 64]), (5_000_000, [20_000] * 19), (1_000, [1000]),
+                             (3_000_000, [700_000, 5])):
+        lists = [rng.choice(id_limit, size=c, replace=False).astype(np.uint32) for c in counts]
+        if id_limit == 1_000:
+            lists[0][::50] += 1_000  # 20 ids past the limit
+        srcs = [ctx.buffer_from_numpy(l) if len(l) else ctx.create_buffer(16) for l in lists]
+        outs = [ctx.create_buffer(max(4 * len(l), 16)) for l in lists]
+        for o in outs:
+            o.upload(np.full(o.nbytes // 4, 0xFFFFFFFF, np.uint32))
+        l0 = ctx.launch_count
+        ctx.sort_entity_ids_batch(srcs, counts, id_limit, outs)
+        assert ctx.launch_count - l0 == 2 * ((sum(1 for c in counts if c) + 15) // 16 if len(counts) <= 16 else 2)
+        ctx.synchronize()
+        for l, o in zip(lists, outs):
+            got = o.download(np.uint32)
+            keep = np.sort(l[l < id_limit])
+            assert np.array_equal(got[: len(keep)], keep)
+            assert np.all(got[len(keep):] == 0xFFFFFFFF)  # nothing written past the ids that were kept
+        for b in srcs + outs:
+            b.destroy()
 
 
 def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
@@ -176,7 +204,7 @@ def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
     w.cull_static(cam.view_proj_cm, cam.pos, pyr)  # nothing changed: no re-sort, no list upload
     ctx.synchronize()
     steady = ctx.launch_count - l0
-    assert steady == 2 and first == steady + 2 * 4  # upload + cull; first frame: + two sorts (4 launches each; the set's first sync is one direct copy)
+    assert steady == 2 and first == steady + 2  # upload + cull; first frame: + ONE batch sorting both lists (two launches; the set's first sync is one direct copy)
     check()
     gone = rng.choice(s.dense(), size=1500, replace=False)  # the set changes: only its copy is rebuilt
     s.erase_many(gone)
@@ -184,7 +212,7 @@ def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
     l0 = ctx.launch_count
     w.cull_static(cam.view_proj_cm, cam.pos, pyr)
     ctx.synchronize()
-    assert 2 + 4 <= ctx.launch_count - l0 <= 2 + 4 + 2
+    assert 2 + 2 <= ctx.launch_count - l0 <= 2 + 2 + 2  # upload + cull + a one-list batch (+ the set's scatter kernels)
     check()
     raw_ids = rng.permutation(raw_ids)[:-300]  # the caller-owned list changes: set_command_entities announces it
     raw_buf2 = ctx.buffer_from_numpy(raw_ids)
@@ -192,7 +220,7 @@ def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
     l0 = ctx.launch_count
     w.cull_static(cam.view_proj_cm, cam.pos, pyr)
     ctx.synchronize()
-    assert ctx.launch_count - l0 == 2 + 4
+    assert ctx.launch_count - l0 == 2 + 2
     check()
     w.destroy()
     s.destroy()
