@@ -1,3 +1,10 @@
+#!/usr/bin/env python
+"""Per-kernel times of the entity-list sort (rve_sort_entity_ids) on a random list and on a churned contiguous range (what the
+engine's lists look like), for a launch list:
+
+  python tools/sort_probe.py && ncu --metrics gpu__time_duration.sum --clock-control none -c 40 --csv \
+      --log-file gpurun_out/sort_launches.csv python tools/sort_probe.py
+"""
 import sys
 sys.path.insert(0, ".")
 import numpy as np, torch
