@@ -339,8 +339,9 @@ RVE_API int rve_depth_pyramid_build(rve_ctx* ctx, rve_pyramid pyr, rve_buffer de
  * that camera, src/RenderEngine_Draw.cpp:2475-2514 then :1221-1407): the launch may stop after the tile levels (mips 0..5)
  * and leave the upper levels to the first CTAs of that cull, off the critical path. The library completes the
  * pyramid whichever of ITS calls touches it next - rve_cull / rvs_cull_static* inside the cull kernel, rve_cull_views and
- * rve_depth_pyramid_footmin with a launch of their own, the next build by rewriting everything; only code that reads mips
- * >= 6 of the texel buffer through its raw device pointer BEFORE any of those must use rve_depth_pyramid_build instead. */
+ * rve_depth_pyramid_footmin, rve_buffer_download and rve_buffer_copy (of the texel buffer) with a launch of their own, the
+ * next build by rewriting everything; only code that reads mips >= 6 of the texel buffer through its raw device pointer
+ * BEFORE any of those must use rve_depth_pyramid_build instead. */
 RVE_API int rve_depth_pyramid_build_deferred(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t width, uint32_t height);
 /* The library keeps a derived copy of the chain for rve_cull (the min over each 2x2 sampler footprint, one load per
  * sample). It follows rve_depth_pyramid_build and rve_buffer_upload/copy/fill_zero on the texel buffer automatically;

@@ -464,6 +464,8 @@ int rve_buffer_download(rve_ctx* ctx, rve_buffer buf, size_t src_offset, void* h
     if (!b) return RVE_ERR_BAD_HANDLE;
     if (src_offset + bytes > b->bytes) return set_error(RVE_ERR_INVALID_ARGUMENT, "download out of range");
     if (!bytes) return 0;
+    const int prc = pyramid_before_buffer_read(ctx, buf);
+    if (prc) return prc;
     RVE_CUDA(cudaMemcpyAsync(host_dst, static_cast<const char*>(b->ptr) + src_offset, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     RVE_CUDA(cudaStreamSynchronize(ctx->stream));
     return 0;
@@ -478,6 +480,8 @@ int rve_buffer_copy(rve_ctx* ctx, rve_buffer src, size_t src_offset, rve_buffer 
     if (src_offset + bytes > s->bytes || dst_offset + bytes > d->bytes)
         return set_error(RVE_ERR_INVALID_ARGUMENT, "copy out of range");
     if (!bytes) return 0;
+    const int prc = pyramid_before_buffer_read(ctx, src);
+    if (prc) return prc;
     RVE_CUDA(cudaMemcpyAsync(static_cast<char*>(d->ptr) + dst_offset, static_cast<const char*>(s->ptr) + src_offset, bytes,
                              cudaMemcpyDeviceToDevice, ctx->stream));
     pyramid_note_buffer_write(ctx, dst);

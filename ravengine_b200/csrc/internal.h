@@ -199,6 +199,9 @@ int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t
 int pyramid_finish_upper(rve_ctx* ctx, PyramidRec* p);  // no-op unless upperPending
 // marks pyramids whose texel buffer is `buf` as changed (buffer upload / copy / fill paths)
 void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf);
+// ... and before the library reads a buffer on the caller's behalf (download, copy source): a pyramid whose upper levels a
+// deferring build left open is completed first when `buf` is its texel buffer
+int pyramid_before_buffer_read(rve_ctx* ctx, rve_buffer buf);
 
 // RAII: brackets a kernel launch with events when ctx->profiling
 struct ProfScope {

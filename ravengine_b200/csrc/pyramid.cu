@@ -557,6 +557,15 @@ int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel) {
     return 0;
 }
 
+int pyramid_before_buffer_read(rve_ctx* ctx, rve_buffer buf) {
+    for (auto& p : ctx->pyramids)
+        if (p.live && p.upperPending && (p.texels == buf || p.footmin == buf)) {
+            const int rc = pyramid_finish_upper(ctx, &p);
+            if (rc) return rc;
+        }
+    return 0;
+}
+
 void pyramid_note_buffer_write(rve_ctx* ctx, rve_buffer buf) {
     for (auto& p : ctx->pyramids)
         if (p.live && p.texels == buf) p.footmin_valid = false;
@@ -689,7 +698,6 @@ int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t
     DeviceGuard g(ctx->device);
     PyramidRec* p = get_pyramid(ctx, pyr);
     if (!p) return RVE_ERR_BAD_HANDLE;
-    p->upperPending = false;  // whatever an earlier build left open is rewritten by this one
     BufferRec* d = get_buffer(ctx, depth, "depth");
     if (!d) return RVE_ERR_BAD_HANDLE;
     RVE_REQUIRE(width >= 1 && height >= 1, "depth buffer must be at least 1x1");
@@ -712,6 +720,7 @@ int pyramid_build_impl(rve_ctx* ctx, rve_pyramid pyr, rve_buffer depth, uint32_t
     const bool deferWithTma = wantDefer && deferTiles && deferTiles[0] == 't';
     BufferRec* sync = get_buffer(ctx, p->counter, "pyramid counters");
     if (!sync) return RVE_ERR_BAD_HANDLE;
+    p->upperPending = false;  // whatever an earlier build left open is rewritten by this one (arguments are valid: it will launch)
     {
         ProfScope prof(ctx, RVE_PROF_PYRAMID);
         // TMA-fed tiles when the image qualifies (16-byte aligned rows, full 32-texel tiles, a source box that fits)

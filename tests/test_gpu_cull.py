@@ -326,6 +326,9 @@ def test_deferred_pyramid_build_is_finished_for_every_other_consumer(ctx):
     pyr = ctx.create_pyramid(h_)
     ref_a, dim, levels = oracle.pyramid_build(depth_a, h_)
     ref_b, _, _ = oracle.pyramid_build(depth_b, h_)
+    # a download of the texel buffer through the library
+    ctx.build_pyramid(pyr, d_a, w_, h_, deferred=True)
+    np.testing.assert_array_equal(ref_a, pyr.texels.download(np.float32))
     # accessor
     ctx.build_pyramid(pyr, d_a, w_, h_, deferred=True)
     fm = ctx.pyramid_footmin(pyr).download(np.float32)
