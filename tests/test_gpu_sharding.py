@@ -174,6 +174,54 @@ def test_sharded_cull_gather_world_size_1(ctx):
     w.destroy()
 
 
+def test_two_frame_slots_keep_their_own_counts(ctx):
+    """ShardedCull.add_frame_slot (two frames in flight: a second world = a second set of indirect / culling buffers): frames
+    alternate between the slots with different cameras and no wait on the other slot's exchange; every exchange reports the
+    counts of the slot it was given, and the slot's buffers are not touched by the other slot's frame."""
+    import torch
+
+    from ravengine_b200.sharding import ShardedCull
+
+    rng, model, layers, flags, cam, depth = _scene()
+    lists = _lists(rng, 0, E)
+    keep = []
+    worlds = [_world(ctx, model, layers, flags, lists, keep) for _ in range(2)]
+    cams = [cam, scenes.default_camera(z_far=1000.0, eye=(120.0, 10.0, 60.0), target=(0.0, 0.0, -80.0))]
+    pyr = ctx.create_pyramid(180)
+    d = ctx.buffer_from_numpy(depth)
+    ctx.build_pyramid(pyr, d, depth.shape[1], depth.shape[0])
+    stream = torch.cuda.ExternalStream(ctx.stream) if ctx.stream else torch.cuda.current_stream()
+    sh = ShardedCull(ctx, worlds[0][0], worlds[0][1], [4, 2], 1, stream)
+    assert sh.add_frame_slot(worlds[1][0], worlds[1][1]) == 1
+    sh._solo_mailbox()
+    sh.mode = "p2p"  # one rank: the peer-memory kernel with itself as the only peer (the fused, wait-free exchange path)
+    expected = []
+    for slot in range(2):  # what each camera sees, from a plain cull
+        w, mats = worlds[slot]
+        w.cull_static(cams[slot].view_proj_cm, cams[slot].pos, pyr)
+        ctx.synchronize()
+        expected.append(np.concatenate([w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:, 1] for m in mats]))
+    assert not np.array_equal(expected[0], expected[1])
+    for frame in range(6):
+        slot = frame & 1
+        w, mats = worlds[slot]
+        sh.begin_cull(slot)
+        w.cull_static(cams[slot].view_proj_cm, cams[slot].pos, pyr)
+        b = sh.exchange(slot=slot)
+        sh.finish()
+        ctx.synchronize()
+        torch.cuda.synchronize()
+        assert not sh.timed_out()
+        totals = sh.t_tot[b].cpu().numpy().view(np.uint32)
+        assert np.array_equal(totals, expected[slot]), (frame, slot)
+        other = worlds[1 - slot]
+        got_other = np.concatenate([other[0].material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:, 1] for m in other[1]])
+        assert np.array_equal(got_other, expected[1 - slot])
+    sh.close()
+    for w, _ in worlds:
+        w.destroy()
+
+
 @pytest.mark.parametrize("world,policy", [(1, "range"), (2, "strided"), (4, "strided"), (4, "range")])
 def test_views_per_rank_equal_the_single_gpu_view_batch(ctx, world, policy):
     """Partition B: rank r culls its share of the views with ShardedViews; its per-view layouts must equal the corresponding
