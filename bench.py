@@ -448,7 +448,7 @@ def run_ours(args, rank: int, world_size: int, local_rank: int):
         from ravengine_b200 import Context
 
         st_ctx = Context(device, st_stream.cuda_stream)
-        stages = list(stage_bench.run_stages(st_ctx, st_stream, reps=10, only={"c1", "c2s", "c2churn", "c2sorted", "pyramid", "c3", "c4"}, cpu=not args.no_cpu_baseline))
+        stages = list(stage_bench.run_stages(st_ctx, st_stream, reps=10, only={"c1", "c2s", "c2churn", "c2sorted", "c2live", "pyramid", "c3", "c4"}, cpu=not args.no_cpu_baseline))
         st_ctx.close()
     cpu = None
     if not args.no_cpu_baseline:

@@ -93,6 +93,10 @@ RVE_API int rvs_material_outputs(rvs_world* w, uint32_t material, rve_buffer* cu
                                  uint32_t* num_lods_total, uint32_t* num_entities_total);
 /* the world's CUBO buffer and the numCubos / totalEntities of the last static cull (for inspection) */
 RVE_API int rvs_last_cull_info(rvs_world* w, rve_buffer* cubo_buffer, uint32_t* num_cubos, uint32_t* total_entities);
+/* RVS_SORT_ENTITY_LISTS bookkeeping since the world was created (for inspection): lists whose ascending copy was rebuilt from
+ * the whole list, and lists whose copy followed a small change of their sparse set through the command's own bitmap (only the
+ * ids that entered / left the set applied, copy re-expanded) */
+RVE_API int rvs_sorted_list_stats(rvs_world* w, uint32_t* full_rebuilds, uint32_t* delta_updates);
 
 /* ---- skinned path ---- */
 /* MeshAssetSkinned: vertex/index ranges in the shared arena, radius, weights buffer */

@@ -158,6 +158,7 @@ PROTOTYPES.update({
     "rvs_cull_static_views": (C.c_int, [VP, u32, VP, UP, u32]),
     "rvs_material_outputs": (C.c_int, [VP, u32, UP, UP, UP, UP]),
     "rvs_last_cull_info": (C.c_int, [VP, UP, UP, UP]),
+    "rvs_sorted_list_stats": (C.c_int, [VP, UP, UP]),
     "rvs_skinned_mesh_create": (C.c_int, [VP, u32, u32, u32, u32, f32, u32, UP]),
     "rvs_skinned_material_create": (C.c_int, [VP, u32, UP]),
     "rvs_skinned_material_add_command": (C.c_int, [VP, u32, u32, u32, u32, u32, VP]),

@@ -50,7 +50,10 @@ int rvs_world_destroy(rvs_world* w) {
     for (auto& m : w->materials) {
         kill(m.cullingBuffer);
         kill(m.indirectBuffer);
-        for (auto& c : m.commands) kill(c.sortedIds);
+        for (auto& c : m.commands) {
+            kill(c.sortedIds);
+            kill(c.sortBitmap);
+        }
     }
     for (auto& m : w->skinnedMaterials) {
         kill(m.cullingBuffer);
@@ -139,6 +142,13 @@ int rvs_material_outputs(rvs_world* w, uint32_t material, rve_buffer* culling_bu
     if (indirect_buffer) *indirect_buffer = m.indirectBuffer;
     if (num_lods_total) *num_lods_total = m.numLODs;
     if (num_entities_total) *num_entities_total = m.numEntities;
+    return 0;
+}
+
+int rvs_sorted_list_stats(rvs_world* w, uint32_t* full_rebuilds, uint32_t* delta_updates) {
+    if (!w) return set_error(RVE_ERR_INVALID_ARGUMENT, "null world");
+    if (full_rebuilds) *full_rebuilds = w->sortFullRebuilds;
+    if (delta_updates) *delta_updates = w->sortDeltaUpdates;
     return 0;
 }
 

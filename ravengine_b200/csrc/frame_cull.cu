@@ -1,6 +1,7 @@
 // frame_cull.cu — cullTheRenderData (src/RenderEngine_Draw.cpp:1221-1407) and the clustered-light
 // prologue of renderFromPerspective (:928-974), restated over the rve_* C-ABI. Host C++ only.
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -52,30 +53,64 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
     // a list shuffled by swap-remove erases costs the cull its tile path), rebuilt only when the list changed
     if (w->flags & RVS_SORT_ENTITY_LISTS) {
         const uint64_t idLimit = rve_buffer_size(w->ctx, w->model) / 64;
-        // every list that changed goes into ONE batch (two launches per 16 lists, rve_sort_entity_ids_batch)
+        const uint32_t idLimit32 = uint32_t(std::min<uint64_t>(idLimit, 0xFFFFFFFFull));
+        // every list that changed goes into ONE batch (two launches per 16 lists): caller-owned lists through the context's
+        // scratch bitmaps (rve_sort_entity_ids_batch), sparse-set-backed lists through a bitmap of their own, to which a small
+        // change is applied as a delta (the ids the set reports as entered / left) instead of rebuilding it from the list
         std::vector<rve_buffer> srcs, dsts;
         std::vector<uint32_t> counts;
         std::vector<decltype(&w->materials[0].commands[0])> stale;
+        std::vector<SortedListUpdate> owned;
+        std::vector<std::vector<uint32_t>> deltas;  // entered / left ids of the owned lists, alive until the batch is enqueued
         for (auto& m : w->materials)
             for (auto& c : m.commands) {
                 if (!c.count) continue;
                 if (c.sortedValid && c.sortedOf == c.entityIds && c.sortedCount == c.count) continue;
-                const int src = realloc_buffer(w, &c.sortedIds, &c.sortedBytes, c.count, sizeof(uint32_t));
+                int src = realloc_buffer(w, &c.sortedIds, &c.sortedBytes, c.count, sizeof(uint32_t));
                 if (src) return src;
-                srcs.push_back(c.entityIds);
-                dsts.push_back(c.sortedIds);
-                counts.push_back(c.count);
                 stale.push_back(&c);
+                if (!c.set) {
+                    srcs.push_back(c.entityIds);
+                    dsts.push_back(c.sortedIds);
+                    counts.push_back(c.count);
+                    continue;
+                }
+                const size_t before = c.sortBitmapBytes;
+                src = realloc_buffer(w, &c.sortBitmap, &c.sortBitmapBytes, sort_region_bytes(idLimit32), 1);
+                if (src) return src;
+                SortedListUpdate u{c.entityIds, c.count, c.sortedIds, c.sortBitmap, nullptr, 0, nullptr, 0, true};
+                deltas.emplace_back();
+                deltas.emplace_back();
+                std::vector<uint32_t>&entered = deltas[deltas.size() - 2], &left = deltas.back();
+                static std::atomic<uint64_t> nextOwner{1};
+                if (!c.sortOwnerId) c.sortOwnerId = nextOwner.fetch_add(1);
+                const bool tracked = sparse_set_take_changes(c.set, c.sortOwnerId, &entered, &left);
+                if (tracked && c.bitmapValid && c.bitmapIdLimit == idLimit32 && c.sortBitmapBytes == before &&
+                    entered.size() + left.size() <= size_t(c.count) / 4) {
+                    u.full = false;
+                    u.setIds = entered.data(), u.nSet = uint32_t(entered.size());
+                    u.clearIds = left.data(), u.nClear = uint32_t(left.size());
+                } else if (!tracked) {
+                    sparse_set_track_changes(c.set, c.sortOwnerId);  // from this full build on the set reports its changes to this command
+                }
+                c.bitmapValid = false;  // until the batch is enqueued
+                owned.push_back(u);
             }
-        if (!stale.empty()) {
-            const int src = rve_sort_entity_ids_batch(w->ctx, uint32_t(stale.size()), srcs.data(), counts.data(),
-                                                      uint32_t(std::min<uint64_t>(idLimit, 0xFFFFFFFFull)), dsts.data());
+        if (!srcs.empty()) {
+            const int src = rve_sort_entity_ids_batch(w->ctx, uint32_t(srcs.size()), srcs.data(), counts.data(), idLimit32, dsts.data());
             if (src) return src;
-            for (auto* c : stale) {
-                c->sortedOf = c->entityIds;
-                c->sortedCount = c->count;
-                c->sortedValid = true;
-            }
+        }
+        if (!owned.empty()) {
+            const int src = sort_lists_persistent(w->ctx, owned.data(), uint32_t(owned.size()), idLimit32);
+            if (src) return src;
+        }
+        w->sortFullRebuilds += uint32_t(srcs.size());
+        for (const SortedListUpdate& u : owned) (u.full ? w->sortFullRebuilds : w->sortDeltaUpdates) += 1;
+        for (auto* c : stale) {
+            c->sortedOf = c->entityIds;
+            c->sortedCount = c->count;
+            c->sortedValid = true;
+            if (c->set) c->bitmapValid = true, c->bitmapIdLimit = idLimit32;
         }
     }
     // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch

@@ -6,6 +6,14 @@
 
 #include "../../include/rve_shim.h"
 
+namespace rve {
+// change log of a sparse set (csrc/sync.cu): off until switched on; take_changes returns the net ids that entered / left the
+// set since the last call and restarts the log - false when the log was off or overflowed (the consumer rebuilds from the list)
+// (`owner`: the one consumer the log is kept for - a second one is refused and keeps rebuilding)
+bool sparse_set_track_changes(rvs_sparse_set* s, uint64_t owner);
+bool sparse_set_take_changes(rvs_sparse_set* s, uint64_t owner, std::vector<uint32_t>* entered, std::vector<uint32_t>* left);
+}  // namespace rve
+
 namespace rvs {
 
 struct LODMesh {
@@ -32,6 +40,13 @@ struct Command {
     rve_buffer sortedOf = RVE_BUFFER_INVALID;
     uint32_t sortedCount = 0;
     bool sortedValid = false;
+    // ... for a sparse-set-backed list the copy is maintained through a bitmap the command owns: after a small change only
+    // the ids that entered / left the set are applied to it and the copy is re-expanded (csrc/sort_ids.cu, sort_lists_persistent)
+    rve_buffer sortBitmap = RVE_BUFFER_INVALID;
+    size_t sortBitmapBytes = 0;
+    uint32_t bitmapIdLimit = 0;
+    bool bitmapValid = false;
+    uint64_t sortOwnerId = 0;  // this command's identity towards the set's change log
 };
 
 // MDICommandBase + MDIICommand (World.hpp:334-349)
@@ -78,6 +93,7 @@ struct rvs_world {
     rve_buffer cuboBuffer = RVE_BUFFER_INVALID;
     size_t cuboBytes = 0;
     uint32_t lastNumCubos = 0, lastTotalEntities = 0;
+    uint32_t sortFullRebuilds = 0, sortDeltaUpdates = 0;  // rvs_sorted_list_stats
     // lightClusterBuffer (src/RenderEngine.cpp:839-845)
     rve_buffer clusterBuffer = RVE_BUFFER_INVALID;
     size_t clusterBytes = 0;

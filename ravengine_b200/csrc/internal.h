@@ -118,6 +118,8 @@ struct rve_ctx {
     size_t d_view_stride_cap = 0;
     void* d_sort = nullptr;  // rve_sort_entity_ids: bitmap + block sums
     size_t d_sort_cap = 0;
+    void* d_sort_delta = nullptr;  // ids that entered / left lists with a persistent bitmap (sort_lists_persistent)
+    size_t d_sort_delta_cap = 0;
     uint64_t sort_clean_geometry = 0;  // (blocks, lists) for which the sort scratch's bitmaps are known to be zero
     bool sort_dirty = false;           // a sort was enqueued only in part: clear the scratch before the next one
     int cull_blocks_per_sm = 0;  // occupancy of cull_kernel, queried once
@@ -189,6 +191,22 @@ int cull_launch(rve_ctx* ctx, const RveCullingUBO* ubo, uint32_t num_views, cons
 // cull.cu: CUtensorMap (128 bytes, 64-byte aligned, passed as void*) of a row-major f32 image, boxes of boxRows x boxCols
 int make_image_map(const void* base, uint64_t cols, uint64_t rows, uint32_t boxCols, uint32_t boxRows, void* out);
 // (re)derives the footprint-min chain of a pyramid from its texels when they changed since the last derivation
+// Ascending copies of entity lists that OWN their bitmap (csrc/sort_ids.cu; the shim's sparse-set-backed commands): `full`
+// rebuilds the bitmap from the list, otherwise only the ids that entered (setIds) / left (clearIds) the list since the last
+// update are applied; either way `out` receives the `count` ids in ascending order. Two launches per 16 lists.
+struct SortedListUpdate {
+    rve_buffer ids;     // the list (read by a full build)
+    uint32_t count;     // its length now
+    rve_buffer out;     // >= count ids
+    rve_buffer bitmap;  // >= sort_region_bytes(id_limit), owned by the list
+    const uint32_t* setIds;
+    uint32_t nSet;
+    const uint32_t* clearIds;
+    uint32_t nClear;
+    bool full;
+};
+size_t sort_region_bytes(uint32_t id_limit);
+int sort_lists_persistent(rve_ctx* ctx, const SortedListUpdate* u, uint32_t n_lists, uint32_t id_limit);
 int pyramid_refresh_footmin(rve_ctx* ctx, PyramidRec* p, uint32_t firstLevel = 0);
 // rve_depth_pyramid_build with an option: allowDefer lets the build stop after the tile levels (mips 0..5, footprint-min
 // level 0) and leave PyramidRec::upperPending set - the caller enqueues a cull next, whose kernel finishes the upper levels

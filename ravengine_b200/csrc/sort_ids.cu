@@ -12,6 +12,8 @@
 // space, count bits per 1024-word block, scan the block counts, expand the bits in order. O(id space / 32 + list) words
 // of traffic; no comparison sort, no library call. rve_sort_entity_ids / _batch do it in two launches for up to 16 lists
 // (further down); the four-kernel sequence right below is what rve_sort_entity_ids_static still runs over its fixed scratch.
+#include <cstring>
+
 #include "internal.h"
 
 namespace rve {
@@ -100,10 +102,13 @@ __global__ void __launch_bounds__(kSortBlock) ids_expand_kernel(const uint32_t* 
 // are cleared as they are read: the scratch is left ready for the next sort, no memset.
 constexpr uint32_t kSortBatch = 16;
 struct SortList {
-    const uint32_t* ids;
+    const uint32_t* ids;    // full build: the list itself
     uint32_t* out;
-    uint32_t count;
-    uint32_t pad;
+    uint32_t* region;       // bitmap | look-back state | ticket, out-of-range count (sort_region_words)
+    const uint32_t* delta;  // persistent bitmap, small change: nSet ids that entered the list, then nClear ids that left it
+    uint32_t count;         // entries of the list (= ids the expansion writes)
+    uint32_t nSet, nClear;
+    uint32_t keep;          // 1: the bitmap belongs to the list and survives the expansion (next change: a delta); 0: scratch, cleared as it is read
 };
 struct SortBatch {
     SortList l[kSortBatch];
@@ -111,9 +116,9 @@ struct SortBatch {
 // per-list scratch region (words): bitmap [blocks * 1024] | look-back state, u64 per block [2 * blocks] | ticket, out-of-range count
 __host__ __device__ inline uint32_t sort_region_words(uint32_t blocks) { return blocks * kSortBlock + 2u * blocks + 2u; }
 
-__global__ void ids_set_bits_batch_kernel(const SortBatch b, uint32_t idLimit, uint32_t* __restrict__ scratch, uint32_t blocks) {
+__global__ void ids_set_bits_batch_kernel(const SortBatch b, uint32_t idLimit, uint32_t blocks) {
     const SortList& L = b.l[blockIdx.y];
-    uint32_t* region = scratch + size_t(blockIdx.y) * sort_region_words(blocks);
+    uint32_t* region = L.region;
     uint32_t* ctl = region + size_t(blocks) * kSortBlock + 2u * blocks;
     // look-back state and ticket of the expand launch that follows (nobody reads them during this one)
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < 2u * blocks; i += gridDim.x * blockDim.x) region[size_t(blocks) * kSortBlock + i] = 0u;
@@ -124,6 +129,20 @@ __global__ void ids_set_bits_batch_kernel(const SortBatch b, uint32_t idLimit, u
     // are not adjacent, but costs one pass per distinct word: 73 us on random ids, where this costs nothing extra).
     const uint32_t lane = threadIdx.x & 31u;
     const uint32_t stride = gridDim.x * blockDim.x;
+    if (L.delta) {
+        // the list's own bitmap, a small change: ids that entered are set, ids that left are cleared (disjoint by construction)
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < L.nSet + L.nClear; i += stride) {
+            const uint32_t id = __ldg(L.delta + i);
+            if (id >= idLimit) {
+                if (i < L.nSet) atomicAdd(ctl + 1, 1u);
+            } else if (i < L.nSet) {
+                atomicOr(region + (id >> 5), 1u << (id & 31u));
+            } else {
+                atomicAnd(region + (id >> 5), ~(1u << (id & 31u)));
+            }
+        }
+        return;
+    }
     for (uint32_t base = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); base < L.count; base += stride) {  // warp-uniform trip count
         const uint32_t i = base + lane;
         uint32_t id = 0xFFFFFFFFu;
@@ -154,11 +173,11 @@ __device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned l
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-__global__ void __launch_bounds__(kSortBlock) ids_expand_lookback_kernel(const SortBatch b, uint32_t words, uint32_t* __restrict__ scratch, uint32_t blocks) {
+__global__ void __launch_bounds__(kSortBlock) ids_expand_lookback_kernel(const SortBatch b, uint32_t words, uint32_t blocks) {
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_blk, s_prefix;
     const SortList& L = b.l[blockIdx.y];
-    uint32_t* region = scratch + size_t(blockIdx.y) * sort_region_words(blocks);
+    uint32_t* region = L.region;
     unsigned long long* state = reinterpret_cast<unsigned long long*>(region + size_t(blocks) * kSortBlock);  // (status << 32) | value; status 1 aggregate, 2 prefix
     uint32_t* ctl = region + size_t(blocks) * kSortBlock + 2u * blocks;
     if (threadIdx.x == 0) s_blk = atomicAdd(ctl, 1u);
@@ -168,7 +187,7 @@ __global__ void __launch_bounds__(kSortBlock) ids_expand_lookback_kernel(const S
     uint32_t bits = 0;
     if (w < words) {
         bits = region[w];
-        if (bits) region[w] = 0u;  // the bitmap is clean again when this launch ends
+        if (bits && !L.keep) region[w] = 0u;  // scratch bitmaps are clean again when this launch ends
     }
     const uint32_t n = uint32_t(__popc(bits));
     const uint32_t incl = block_scan_1024(n, s_warp);
@@ -219,7 +238,7 @@ __global__ void __launch_bounds__(kSortBlock) ids_expand_lookback_kernel(const S
 }
 
 // sorts lists[0..n) (n <= kSortBatch) of one id space with two launches; the context's sort scratch holds one region per list
-static int sort_batch(rve_ctx* ctx, const SortBatch& batch, uint32_t n, uint32_t maxCount, uint32_t id_limit) {
+static int sort_batch(rve_ctx* ctx, SortBatch& batch, uint32_t n, uint32_t maxCount, uint32_t id_limit) {
     const uint32_t words = (id_limit + 31u) / 32u;
     const uint32_t blocks = (words + kSortBlock - 1) / kSortBlock;
     const size_t need = size_t(n) * sort_region_words(blocks) * sizeof(uint32_t);
@@ -234,12 +253,81 @@ static int sort_batch(rve_ctx* ctx, const SortBatch& batch, uint32_t n, uint32_t
     }
     ctx->sort_dirty = true;
     uint32_t* scratch = static_cast<uint32_t*>(ctx->d_sort);
+    for (uint32_t i = 0; i < n; ++i) batch.l[i].region = scratch + size_t(i) * sort_region_words(blocks);
     const uint32_t setBlocks = std::max<uint32_t>(1u, std::min<uint32_t>((maxCount + 255) / 256, uint32_t(ctx->sm_count) * 8u / n + 1u));
-    ids_set_bits_batch_kernel<<<dim3(setBlocks, n), 256, 0, ctx->stream>>>(batch, id_limit, scratch, blocks);
-    ids_expand_lookback_kernel<<<dim3(blocks, n), kSortBlock, 0, ctx->stream>>>(batch, words, scratch, blocks);
+    ids_set_bits_batch_kernel<<<dim3(setBlocks, n), 256, 0, ctx->stream>>>(batch, id_limit, blocks);
+    ids_expand_lookback_kernel<<<dim3(blocks, n), kSortBlock, 0, ctx->stream>>>(batch, words, blocks);
     ctx->launches += 2;
     RVE_CUDA(cudaGetLastError());
     ctx->sort_dirty = false;
+    return 0;
+}
+
+// Lists that own their bitmap (internal.h: SortedListUpdate): a full build zeroes the bitmap and sets the bits of the whole
+// list, a delta only touches the ids that entered or left; the expansion leaves the bitmap in place. Two launches per 16 lists.
+size_t sort_region_bytes(uint32_t id_limit) {
+    const uint32_t words = (id_limit + 31u) / 32u;
+    return size_t(sort_region_words((words + kSortBlock - 1) / kSortBlock)) * sizeof(uint32_t);
+}
+
+int sort_lists_persistent(rve_ctx* ctx, const SortedListUpdate* u, uint32_t n_lists, uint32_t id_limit) {
+    if (n_lists == 0) return 0;
+    DeviceGuard g(ctx->device);
+    const uint32_t words = (id_limit + 31u) / 32u;
+    const uint32_t blocks = (words + kSortBlock - 1) / kSortBlock;
+    for (uint32_t first = 0; first < n_lists; first += kSortBatch) {
+        SortBatch batch{};
+        uint32_t n = 0, maxWork = 0;
+        size_t deltaWords = 0;
+        for (uint32_t i = first; i < n_lists && i < first + kSortBatch; ++i)
+            if (!u[i].full) deltaWords += size_t(u[i].nSet) + u[i].nClear;
+        // the deltas of the batch travel in one staged copy
+        std::vector<uint32_t> host(deltaWords);
+        int rc = ensure_scratch(ctx, &ctx->d_sort_delta, &ctx->d_sort_delta_cap, std::max<size_t>(deltaWords, 1) * sizeof(uint32_t));
+        if (rc) return rc;
+        size_t at = 0;
+        for (uint32_t i = first; i < n_lists && i < first + kSortBatch; ++i) {
+            const SortedListUpdate& x = u[i];
+            if (x.count == 0) continue;
+            BufferRec* bo = get_buffer(ctx, x.out, "sorted entity ids");
+            BufferRec* br = get_buffer(ctx, x.bitmap, "entity id bitmap");
+            if (!bo || !br) return RVE_ERR_BAD_HANDLE;
+            RVE_REQUIRE(uint64_t(x.count) * 4 <= bo->bytes && sort_region_bytes(id_limit) <= br->bytes, "sorted id / bitmap buffers too small");
+            SortList& L = batch.l[n];
+            L = SortList{};
+            L.out = static_cast<uint32_t*>(bo->ptr);
+            L.region = static_cast<uint32_t*>(br->ptr);
+            L.count = x.count;
+            L.keep = 1u;
+            if (x.full) {
+                BufferRec* bi = get_buffer(ctx, x.ids, "entity ids");
+                if (!bi) return RVE_ERR_BAD_HANDLE;
+                RVE_REQUIRE(uint64_t(x.count) * 4 <= bi->bytes, "id buffer smaller than count entries");
+                L.ids = static_cast<const uint32_t*>(bi->ptr);
+                RVE_CUDA(cudaMemsetAsync(br->ptr, 0, size_t(blocks) * kSortBlock * sizeof(uint32_t), ctx->stream));
+                maxWork = std::max(maxWork, x.count);
+            } else {
+                if (x.nSet) std::memcpy(host.data() + at, x.setIds, size_t(x.nSet) * 4);
+                if (x.nClear) std::memcpy(host.data() + at + x.nSet, x.clearIds, size_t(x.nClear) * 4);
+                L.delta = static_cast<const uint32_t*>(ctx->d_sort_delta) + at;
+                L.nSet = x.nSet;
+                L.nClear = x.nClear;
+                at += size_t(x.nSet) + x.nClear;
+                maxWork = std::max(maxWork, x.nSet + x.nClear);
+            }
+            ++n;
+        }
+        if (!n) continue;
+        if (at) {
+            rc = staged_h2d(ctx, ctx->d_sort_delta, host.data(), at * sizeof(uint32_t));
+            if (rc) return rc;
+        }
+        const uint32_t setBlocks = std::max<uint32_t>(1u, std::min<uint32_t>((maxWork + 255) / 256, uint32_t(ctx->sm_count) * 8u / n + 1u));
+        ids_set_bits_batch_kernel<<<dim3(setBlocks, n), 256, 0, ctx->stream>>>(batch, id_limit, blocks);
+        ids_expand_lookback_kernel<<<dim3(blocks, n), kSortBlock, 0, ctx->stream>>>(batch, words, blocks);
+        ctx->launches += 2;
+        RVE_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 
@@ -264,7 +352,10 @@ extern "C" int rve_sort_entity_ids_batch(rve_ctx* ctx, uint32_t n_lists, const r
             BufferRec* bo = get_buffer(ctx, sorted_out[i], "sorted entity ids");
             if (!bi || !bo) return RVE_ERR_BAD_HANDLE;
             RVE_REQUIRE(uint64_t(counts[i]) * 4 <= bi->bytes && uint64_t(counts[i]) * 4 <= bo->bytes, "id buffers smaller than count entries");
-            batch.l[n] = SortList{static_cast<const uint32_t*>(bi->ptr), static_cast<uint32_t*>(bo->ptr), counts[i], 0u};
+            batch.l[n] = SortList{};
+            batch.l[n].ids = static_cast<const uint32_t*>(bi->ptr);
+            batch.l[n].out = static_cast<uint32_t*>(bo->ptr);
+            batch.l[n].count = counts[i];
             maxCount = std::max(maxCount, counts[i]);
             ++n;
         }

@@ -17,6 +17,8 @@
 #include <unistd.h>
 
 #include "frame_internal.h"
+#include <algorithm>
+
 #include "internal.h"
 
 namespace rve {
@@ -837,7 +839,56 @@ struct rvs_sparse_set {
     rvs_vector* dense = nullptr;
     std::vector<uint32_t> sparse{0xFFFFFFFFu};  // sparse_set{ default_index } (SparseSet.hpp:15)
     std::vector<uint32_t> reverse;              // reverse_map: dense index -> sparse index
+    // change log for a consumer that maintains something per VALUE (the shim's sorted device copy of the list): (value << 1) |
+    // entered, in call order. Off until sparse_set_track_changes; gives up (overflow) past kChangeLogMax entries.
+    bool track = false, overflow = false;
+    uint64_t logOwner = 0;  // the one consumer the log is kept for (taking it empties it: a second reader would miss changes)
+    std::vector<uint64_t> log;
 };
+constexpr size_t kChangeLogMax = size_t(1) << 22;
+
+namespace rve {
+bool sparse_set_track_changes(rvs_sparse_set* s, uint64_t owner) {
+    if (s->track && s->logOwner != owner) return false;  // somebody else's log: this consumer keeps rebuilding from the list
+    s->track = true;
+    s->logOwner = owner;
+    s->overflow = false;
+    s->log.clear();
+    return true;
+}
+
+bool sparse_set_take_changes(rvs_sparse_set* s, uint64_t owner, std::vector<uint32_t>* entered, std::vector<uint32_t>* left) {
+    entered->clear();
+    left->clear();
+    if (!s->track || s->logOwner != owner) return false;
+    const bool ok = !s->overflow;
+    if (ok) {
+        // values are unique inside the set, so the calls on one value alternate: the net effect is the sum of +1 / -1 per value
+        std::sort(s->log.begin(), s->log.end());
+        for (size_t i = 0; i < s->log.size();) {
+            const uint32_t value = uint32_t(s->log[i] >> 1);
+            int net = 0;
+            for (; i < s->log.size() && uint32_t(s->log[i] >> 1) == value; ++i) net += (s->log[i] & 1u) ? 1 : -1;
+            if (net > 0) entered->push_back(value);
+            else if (net < 0) left->push_back(value);
+        }
+    }
+    s->overflow = false;
+    s->log.clear();
+    return ok;
+}
+}  // namespace rve
+
+static void log_change(rvs_sparse_set* s, uint32_t value, bool entered) {
+    if (!s->track || s->overflow) return;
+    if (s->log.size() >= kChangeLogMax) {
+        s->overflow = true;
+        s->log.clear();
+        s->log.shrink_to_fit();
+        return;
+    }
+    s->log.push_back((uint64_t(value) << 1) | (entered ? 1u : 0u));
+}
 
 extern "C" {
 
@@ -882,6 +933,7 @@ int rvs_sparse_set_emplace(rvs_sparse_set* s, uint32_t sparse_index, uint32_t va
         s->sparse.resize(want, 0xFFFFFFFFu);
     }
     s->sparse[sparse_index] = n;
+    log_change(s, value, true);
     return 0;
 }
 
@@ -892,6 +944,7 @@ int rvs_sparse_set_erase(rvs_sparse_set* s, uint32_t sparse_index) {
     const uint32_t denseidx = s->sparse[sparse_index];
     const uint32_t last = rvs_vector_size(s->dense) - 1;
     auto* host = static_cast<uint32_t*>(rvs_vector_host(s->dense));
+    log_change(s, host[denseidx], false);
     if (denseidx < last) {  // a move happens: the last element lands in the hole
         const uint32_t moved = host[last];
         const int rc = rvs_vector_set(s->dense, denseidx, &moved);  // marks the dense index modified

@@ -142,6 +142,12 @@ class World:
         _check(self.lib, self.lib.rvs_last_cull_info(self.h, C.byref(b), C.byref(n), C.byref(t)))
         return self._buf(b.value), n.value, t.value
 
+    def sorted_list_stats(self):
+        """rvs_sorted_list_stats: (full rebuilds, delta updates) of the ascending list copies since the world was created"""
+        f, d = C.c_uint32(), C.c_uint32()
+        _check(self.lib, self.lib.rvs_sorted_list_stats(self.h, C.byref(f), C.byref(d)))
+        return f.value, d.value
+
     # ---- skinned ----
     def skinned_mesh(self, num_verts, num_indices, index_start, vertex_start, radius, weights: Buffer) -> int:
         out = C.c_uint32()

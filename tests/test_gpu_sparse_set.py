@@ -204,7 +204,7 @@ def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
     w.cull_static(cam.view_proj_cm, cam.pos, pyr)  # nothing changed: no re-sort, no list upload
     ctx.synchronize()
     steady = ctx.launch_count - l0
-    assert steady == 2 and first == steady + 2  # upload + cull; first frame: + ONE batch sorting both lists (two launches; the set's first sync is one direct copy)
+    assert steady == 2 and first == steady + 4  # upload + cull; first frame: + one two-launch batch per kind of list (caller-owned: scratch bitmap; set-backed: its own bitmap)
     check()
     gone = rng.choice(s.dense(), size=1500, replace=False)  # the set changes: only its copy is rebuilt
     s.erase_many(gone)
@@ -222,5 +222,71 @@ def test_sorted_entity_lists_give_the_same_cull_and_follow_list_changes(ctx):
     ctx.synchronize()
     assert ctx.launch_count - l0 == 2 + 2
     check()
+    w.destroy()
+    s.destroy()
+
+
+
+def test_sorted_copy_of_a_set_backed_list_follows_per_frame_churn_by_deltas(ctx):
+    """A sparse-set-backed command under RVS_SORT_ENTITY_LISTS, many frames with a few hundred erases / inserts each: after the
+    first frame the ascending copy is maintained through the command's own bitmap - only the ids that entered / left the set are
+    applied (rvs_sorted_list_stats), an id erased and re-inserted in one frame nets to nothing - and the cull matches the oracle
+    in every frame. A burst that replaces more than a quarter of the list, and growth of the list, fall back to a full rebuild."""
+    from ravengine_b200.vram_vector import SparseSet
+    from ravengine_b200.world import SORT_ENTITY_LISTS
+
+    rng = np.random.default_rng(12)
+    n = 40_000
+    model = scenes.random_transforms(rng, n, 200.0, 60.0)
+    layers = np.full(n, 0xFFFFFFFF, np.uint32)
+    flags = np.full(n, 0xFFFF, np.uint16)
+    cam = scenes.default_camera(z_far=500.0)
+    depth = scenes.synth_depth(512, 288, cam, n_occluders=30, seed=4)
+    pyr_h, dim, levels = oracle.pyramid_build(depth, 288)
+    mesh = scenes.simple_mesh(scenes.CUBE_RADIUS, (0.0, 40.0, 120.0))
+    w = World(ctx, SORT_ENTITY_LISTS)
+    w.set_entity_buffers(ctx.buffer_from_numpy(model), ctx.buffer_from_numpy(layers), ctx.buffer_from_numpy(flags))
+    mid = w.mesh_collection(mesh.radius, mesh.lod_distances, [l.index_count for l in mesh.lods], [l.index_start for l in mesh.lods],
+                            [l.base_vertex for l in mesh.lods])
+    s = SparseSet(ctx)
+    inside = rng.permutation(n)[:30_000].astype(np.uint32)
+    s.emplace_many(inside)
+    mat = w.material()
+    w.add_command_set(mat, mid, s)
+    pyr = ctx.create_pyramid(288)
+    ctx.build_pyramid(pyr, ctx.buffer_from_numpy(depth), 512, 288)
+
+    def check():
+        w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+        ctx.synchronize()
+        omats = [scenes.MaterialDraws([scenes.DrawCommand(mesh, s.dense())])]
+        t = host_tables.build_static_tables(omats)
+        ref = oracle_cull(t, make_ubo(cam.view_proj_cm, cam.pos, t.num_cubos), model, layers, flags, pyr_h, dim, levels, nthreads=4)
+        cull_b, ind_b, lods, ents = w.material_outputs(mat)
+        cb = t.cubos[0]
+        r_ind, r_ids = ref[int(cb["indirectOutputBufferBindlessHandle"])], ref[int(cb["idOutputBufferBindlessHandle"])]
+        g_ind, g_ids = ind_b.download(np.uint32).reshape(-1, 5)[:lods], cull_b.download(np.uint32)[: lods * ents]
+        np.testing.assert_array_equal(g_ind, r_ind)
+        for x, y in zip(host_tables.sorted_slices(r_ind, r_ids, t.cubos, range(1)), host_tables.sorted_slices(g_ind, g_ids, t.cubos, range(1))):
+            np.testing.assert_array_equal(x, y)
+
+    check()
+    assert w.sorted_list_stats() == (1, 0)
+    for frame in range(8):
+        members = s.dense().copy()
+        gone = rng.choice(members, size=300, replace=False)
+        s.erase_many(gone)
+        outside = np.setdiff1d(np.arange(n, dtype=np.uint32), s.dense())
+        s.emplace_many(np.concatenate([rng.choice(outside, size=250, replace=False), gone[:50]]).astype(np.uint32))  # same size; 50 ids left and came back
+        check()
+        assert w.sorted_list_stats() == (1, frame + 1)
+    s.emplace_many(rng.choice(np.setdiff1d(np.arange(n, dtype=np.uint32), s.dense()), size=500, replace=False).astype(np.uint32))  # the list grows
+    check()
+    full, delta = w.sorted_list_stats()
+    assert (full, delta) in ((1, 9), (2, 8))  # a delta into the re-created copy buffer, or a rebuild: either is right
+    members = s.dense().copy()
+    s.erase_many(rng.choice(members, size=len(members) // 2, replace=False))  # a burst: more than a quarter of the list
+    check()
+    assert w.sorted_list_stats()[0] == full + 1
     w.destroy()
     s.destroy()

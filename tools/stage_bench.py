@@ -196,6 +196,74 @@ def cull_case(ctx, n, lods, occlusion, shuffle, depth_wh, reps, name, flush, cpu
     return line("cull", name, k_ms, k_ms, algo, "hbm", extra)
 
 
+def live_churn_case(ctx, n, per_frame, frames, sort_lists):
+    """C2 with every material's list held in a BufferedVRAMSparseSet stand-in that CHANGES every frame: after an initial 10 % churn
+    each frame erases `per_frame` random members of every list and inserts as many other entities (host calls, not timed), then
+    enqueues the cull (set sync = packed scatter of the touched slots, sorted copies kept by deltas when `sort_lists`, cull).
+    Returns the median GPU time of a frame's enqueued work."""
+    from ravengine_b200.vram_vector import SparseSet
+    from ravengine_b200.world import SORT_ENTITY_LISTS
+
+    dev = torch.device("cuda", ctx.device)
+    st = torch.cuda.ExternalStream(ctx.stream)
+    with torch.cuda.stream(st):
+        t_model = torch.empty((n, 16), dtype=torch.float32, device=dev)
+        t_layers, t_flags = torch.empty(n, dtype=torch.int32, device=dev), torch.empty(n, dtype=torch.int16, device=dev)
+        t_ids = torch.empty(n, dtype=torch.int32, device=dev)
+    model, layers, flags, ids = (ctx.wrap_tensor(t) for t in (t_model, t_layers, t_flags, t_ids))
+    ctx.gen_instances(SceneGenParams(20240, 500.0, 50.0, 0.5, 2.0, 0.05, 0.05, 0), 0, n, model, layers, flags, ids)
+    ctx.synchronize()
+    cam = scenes.default_camera(z_near=0.1, z_far=1000.0)
+    w = World(ctx, SORT_ENTITY_LISTS if sort_lists else 0)
+    w.set_entity_buffers(model, layers, flags)
+    rng = np.random.default_rng(1)
+    n_mats = 4
+    per = n // n_mats
+    sets, spare = [], []
+    for i in range(n_mats):
+        base = np.arange(i * per, (i + 1) * per, dtype=np.uint32)
+        ss = SparseSet(ctx)
+        live = base[: per - per // 50]  # 2 % of the range stays free for insertions
+        ss.emplace_many(live)
+        gone = rng.choice(live, size=per // 10, replace=False)
+        ss.erase_many(gone)
+        ss.emplace_many(rng.permutation(gone))
+        sets.append(ss)
+        spare.append(list(base[per - per // 50:]))
+        mesh = w.mesh_collection(1.7320508 if i % 2 == 0 else 1.74, (0.0, 40.0, 120.0), [36, 24, 12], [0, 36, 60], [0, 24, 40])
+        w.add_command_set(w.material(), mesh, ss)
+    pyr = ctx.create_pyramid(2160)
+    d = ctx.buffer_from_numpy(scenes.synth_depth(3840, 2160, cam))
+    ctx.build_pyramid(pyr, d, 3840, 2160)
+    for _ in range(2):
+        w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+    ctx.synchronize()
+    ts = []
+    for f in range(frames):
+        for i, ss in enumerate(sets):
+            members = ss.dense()
+            out = members[rng.integers(0, len(members), size=per_frame)]
+            out = np.unique(out)
+            ss.erase_many(out)
+            take = [spare[i].pop() for _ in range(len(out))]
+            ss.emplace_many(np.asarray(take, dtype=np.uint32))
+            spare[i] = list(out) + spare[i]
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(st):
+            torch.cuda._sleep(12_000_000)  # ~6 ms: the stream is busy while the host scans the sets' flags and enqueues the frame,
+        a.record(st)                       # so the events bracket the GPU's execution of that work, not the host's preparation
+        w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+        b.record(st)
+        b.synchronize()
+        ts.append(a.elapsed_time(b))
+    stats = w.sorted_list_stats()
+    vis = int(sum(int(w.material_outputs(m)[1].download(np.uint32).reshape(-1, 5)[:3, 1].sum()) for m in range(n_mats)))
+    w.destroy()
+    for ss in sets:
+        ss.destroy()
+    return float(np.median(ts)), float(min(ts)), stats, vis
+
+
 def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
     """Generator of stage dicts (see module docstring)."""
     want = lambda s: only is None or s in only  # noqa: E731
@@ -256,6 +324,16 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
                     "note": "a cull of these lists gains ~71 us from reading the sorted copies (0.216 -> 0.145 ms)"})
         for b in srcs + dsts:
             b.destroy()
+
+    if want("c2live"):
+        n_live, per_frame = 10_000_000, 500
+        for sort_lists in (False, True):
+            med, best, stats, vis = live_churn_case(ctx, n_live, per_frame, max(reps, 8), sort_lists)
+            yield line("frame_with_live_lists", f"C2 with sparse-set-backed lists that change every frame ({per_frame} erases + {per_frame} inserts per list and "
+                       f"frame, after 10 % churn): set sync + " + ("sorted copies kept by deltas + cull of the copies" if sort_lists else "cull of the lists as they are")
+                       + " - GPU time of the frame's enqueued work", med, best, n_live * 74 + vis * 4, "hbm",
+                       {"instances": n_live, "visible": vis, "sorted_copy_full_rebuilds": stats[0], "sorted_copy_delta_updates": stats[1],
+                        "l2": "inputs exceed L2"})
 
     if want("pyramid"):
         cam = scenes.default_camera(z_far=1000.0)
