@@ -221,6 +221,7 @@ PROTOTYPES.update({
     "rvs_vector_encode_sync": (C.c_int, [VP, u32, u32, C.POINTER(SyncStats)]),
     "rvs_vector_private_buffer": (u32, [VP]),
     "rvs_vector_encode_sync_rows": (C.c_int, [VP, u32, u32, u32, C.POINTER(SyncStats)]),
+    "rvs_vectors_encode_sync_batch": (C.c_int, [C.POINTER(VP), u32, u32, C.POINTER(SyncStats)]),
     "rvs_vector_share": (C.c_int, [VP, C.POINTER(i32), C.POINTER(i32), C.POINTER(u64)]),
     "rve_host_import": (C.c_int, [VP, i32, i32, u64, C.POINTER(VP)]),
     "rve_host_release": (C.c_int, [VP, VP, u64]),

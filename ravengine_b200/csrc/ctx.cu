@@ -223,6 +223,9 @@ int rve_ctx_destroy(rve_ctx* ctx) {
     if (ctx->d_slices) cudaFree(ctx->d_slices);
     if (ctx->d_sort) cudaFree(ctx->d_sort);
     if (ctx->d_sort_delta) cudaFree(ctx->d_sort_delta);
+    if (ctx->sync_stage_host) cudaFreeHost(ctx->sync_stage_host);
+    if (ctx->sync_stage_dev) cudaFree(ctx->sync_stage_dev);
+    if (ctx->sync_stage_free) cudaEventDestroy(ctx->sync_stage_free);
     if (ctx->d_gather_ticket) cudaFree(ctx->d_gather_ticket);
     for (auto& b : ctx->buffers)
         if (b.live && b.ipc_imported && b.ptr) cudaIpcCloseMemHandle(b.ptr);

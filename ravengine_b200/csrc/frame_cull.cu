@@ -38,17 +38,28 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
 
     // entity lists held in sparse sets: EncodeSync first (the reference syncs its BufferedVRAM structures ahead of the encode),
     // then the command reads the set's private buffer and DenseSize()
-    for (auto& m : w->materials)
-        for (auto& c : m.commands)
-            if (c.set) {
-                rvs_vector* v = rvs_sparse_set_vector(c.set);
-                rvs_sync_stats st{};
-                const int src = rvs_vector_encode_sync(v, RVS_SYNC_PACKED, 256, &st);
-                if (src) return src;
-                if (st.ranges) c.sortedValid = false;  // the list changed
-                c.entityIds = rvs_vector_private_buffer(v);
+    {
+        // (all sets in one rvs_vectors_encode_sync_batch: lists with small changes share one staging copy and one scatter launch)
+        std::vector<rvs_vector*> vecs;
+        std::vector<decltype(&w->materials[0].commands[0])> owners;
+        for (auto& m : w->materials)
+            for (auto& c : m.commands)
+                if (c.set) {
+                    vecs.push_back(rvs_sparse_set_vector(c.set));
+                    owners.push_back(&c);
+                }
+        if (!vecs.empty()) {
+            std::vector<rvs_sync_stats> sts(vecs.size());
+            const int src = rvs_vectors_encode_sync_batch(vecs.data(), uint32_t(vecs.size()), 256, sts.data());
+            if (src) return src;
+            for (size_t i = 0; i < vecs.size(); ++i) {
+                auto& c = *owners[i];
+                if (sts[i].ranges) c.sortedValid = false;  // the list changed
+                c.entityIds = rvs_vector_private_buffer(vecs[i]);
                 c.count = rvs_sparse_set_dense_size(c.set);
             }
+        }
+    }
     // RVS_SORT_ENTITY_LISTS: the cull reads an ascending copy of every list (its result does not depend on list order;
     // a list shuffled by swap-remove erases costs the cull its tile path), rebuilt only when the list changed
     if (w->flags & RVS_SORT_ENTITY_LISTS) {

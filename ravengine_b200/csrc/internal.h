@@ -118,6 +118,12 @@ struct rve_ctx {
     size_t d_view_stride_cap = 0;
     void* d_sort = nullptr;  // rve_sort_entity_ids: bitmap + block sums
     size_t d_sort_cap = 0;
+    // staging of rvs_vectors_encode_sync_batch: one pinned block + its device twin, reused once the previous copy has completed
+    unsigned char* sync_stage_host = nullptr;
+    void* sync_stage_dev = nullptr;
+    size_t sync_stage_bytes = 0;
+    cudaEvent_t sync_stage_free = nullptr;
+    bool sync_stage_busy = false;
     void* d_sort_delta = nullptr;  // ids that entered / left lists with a persistent bitmap (sort_lists_persistent)
     size_t d_sort_delta_cap = 0;
     uint64_t sort_clean_geometry = 0;  // (blocks, lists) for which the sort scratch's bitmaps are known to be zero

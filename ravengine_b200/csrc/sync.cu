@@ -244,6 +244,36 @@ int launch_full(rve_ctx* ctx, cudaStream_t stream, const unsigned char* src, uns
 
 }  // namespace rve
 
+namespace rve {
+// rvs_vectors_encode_sync_batch: the modified rows of up to kSyncBatchSegs vectors, staged as one block of 4-byte words
+// [rows of segment 0 | rows of segment 1 | ..] + one u32 row index per staged row, scattered by ONE launch
+constexpr uint32_t kSyncBatchSegs = 16;
+struct SyncBatchSeg {
+    uint32_t* dst;       // private buffer of the vector
+    uint32_t rowWords;   // 4-byte words per row
+    uint32_t rowStart;   // first staged row of the segment (index array)
+    uint32_t wordStart;  // first staged word of the segment
+    uint32_t words;      // rows * rowWords
+    uint32_t pad;
+};
+struct SyncBatch {
+    SyncBatchSeg s[kSyncBatchSegs];
+    uint32_t n, totalWords;
+    const uint32_t* data;
+    const uint32_t* idx;
+};
+__global__ void scatter_rows_batch_kernel(const SyncBatch b) {
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < b.totalWords; t += gridDim.x * blockDim.x) {
+        uint32_t k = 0;
+        while (k + 1 < b.n && t >= b.s[k + 1].wordStart) ++k;
+        const SyncBatchSeg& g = b.s[k];
+        const uint32_t local = t - g.wordStart;
+        const uint32_t row = local / g.rowWords, w = local - row * g.rowWords;
+        g.dst[size_t(__ldg(b.idx + g.rowStart + row)) * g.rowWords + w] = __ldg(b.data + t);
+    }
+}
+}  // namespace rve
+
 using namespace rve;
 
 extern "C" int rve_scatter_rows(rve_ctx* ctx, rve_buffer dst, uint32_t elem_bytes, rve_buffer staging, uint64_t indices_offset,
@@ -824,6 +854,124 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
     }
     pyramid_note_buffer_write(ctx, v->priv);
     if (stats) *stats = st;
+    return 0;
+}
+
+// EncodeSync of SEVERAL vectors at once. Frames in which many structures change a little (entity lists, layers, attributes: a
+// few hundred rows each) pay per vector one staging copy and one scatter launch - ~10 us of latency each. Here the modified
+// rows of all vectors whose changes are small (only short ranges, <= 64 Ki rows, 4-byte-multiple rows, no reallocation due)
+// travel in ONE pinned staging block and ONE copy, and are scattered by ONE launch per 16 vectors; every other vector takes
+// its own rvs_vector_encode_sync(RVS_SYNC_PACKED). stats: one entry per vector (may be null).
+int rvs_vectors_encode_sync_batch(rvs_vector* const* vs, uint32_t n, uint32_t direct_min_rows, rvs_sync_stats* stats) {
+    if (n == 0) return 0;
+    if (!vs) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
+    RVE_PROFILE_FN_N("EncodeSync (batch)");
+    rve_ctx* ctx = nullptr;
+    struct Item {
+        uint32_t i;
+        uint64_t rows;
+    };
+    std::vector<Item> batched;
+    uint64_t totalRows = 0, totalWords = 0;
+    for (uint32_t i = 0; i < n; ++i) {
+        rvs_vector* v = vs[i];
+        if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
+        if (stats) stats[i] = rvs_sync_stats{};
+        if (!ctx) ctx = v->ctx;
+        bool small = v->ctx == ctx && !v->affine && (v->elemBytes % 4) == 0 && v->count > 0 && v->priv != RVE_BUFFER_INVALID &&
+                     v->privBytes == size_t(v->capacity) * v->devElemBytes;
+        uint64_t rows = 0;
+        if (small && v->anyDirty) {
+            compute_ranges(v->track, v->count, v->ranges);
+            for (size_t r = 0; r + 1 < v->ranges.size() && small; r += 2) {
+                if (v->ranges[r + 1] - v->ranges[r] >= direct_min_rows) small = false;
+                for (uint32_t k = v->ranges[r]; k < v->ranges[r + 1]; ++k) rows += v->track[k] ? 1u : 0u;
+            }
+            if (rows > 65536) small = false;
+        }
+        if (!small) {
+            const int rc = rvs_vector_encode_sync(v, RVS_SYNC_PACKED, direct_min_rows, stats ? &stats[i] : nullptr);
+            if (rc) return rc;
+            continue;
+        }
+        if (!v->anyDirty || v->ranges.empty()) {  // clean: free, like the single-vector call
+            v->anyDirty = false;
+            v->ranges.clear();
+            continue;
+        }
+        batched.push_back({i, rows});
+        totalRows += rows;
+        totalWords += rows * (v->elemBytes / 4);
+    }
+    if (batched.empty()) return 0;
+    DeviceGuard g(ctx->device);
+    const size_t idxOffset = size_t(totalWords) * 4;
+    const size_t need = idxOffset + size_t(totalRows) * 4;
+    if (need > ctx->sync_stage_bytes) {
+        if (ctx->sync_stage_busy) RVE_CUDA(cudaEventSynchronize(ctx->sync_stage_free));
+        ctx->sync_stage_busy = false;
+        if (ctx->sync_stage_host) cudaFreeHost(ctx->sync_stage_host);
+        if (ctx->sync_stage_dev) RVE_CUDA(cudaFreeAsync(ctx->sync_stage_dev, ctx->stream));
+        const size_t cap = need + need / 2 + 4096;
+        RVE_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ctx->sync_stage_host), cap, cudaHostAllocDefault));
+        RVE_CUDA(cudaMallocAsync(&ctx->sync_stage_dev, cap, ctx->stream));
+        ctx->sync_stage_bytes = cap;
+        if (!ctx->sync_stage_free) RVE_CUDA(cudaEventCreateWithFlags(&ctx->sync_stage_free, cudaEventDisableTiming));
+    }
+    if (ctx->sync_stage_busy) RVE_CUDA(cudaEventSynchronize(ctx->sync_stage_free));  // the previous batch's copy consumed the block
+    ctx->sync_stage_busy = false;
+    auto* words = reinterpret_cast<uint32_t*>(ctx->sync_stage_host);
+    auto* idx = reinterpret_cast<uint32_t*>(ctx->sync_stage_host + idxOffset);
+    std::vector<SyncBatch> launches;
+    uint64_t rowAt = 0, wordAt = 0;
+    for (const Item& it : batched) {
+        rvs_vector* v = vs[it.i];
+        const uint32_t rowWords = v->elemBytes / 4;
+        if (launches.empty() || launches.back().n == kSyncBatchSegs) launches.emplace_back();
+        SyncBatch& b = launches.back();
+        SyncBatchSeg& sg = b.s[b.n++];
+        sg.dst = static_cast<uint32_t*>(rve_buffer_device_ptr(ctx, v->priv));
+        if (!sg.dst) return RVE_ERR_BAD_HANDLE;
+        sg.rowWords = rowWords;
+        sg.rowStart = uint32_t(rowAt);
+        sg.wordStart = uint32_t(wordAt);
+        sg.words = uint32_t(it.rows * rowWords);
+        rvs_sync_stats st{};
+        st.ranges = uint32_t(v->ranges.size() / 2);
+        for (size_t r = 0; r + 1 < v->ranges.size(); r += 2) {
+            const uint32_t rb = v->ranges[r], re = v->ranges[r + 1];
+            st.rows_in_ranges += re - rb;
+            for (uint32_t k = rb; k < re; ++k)
+                if (v->track[k]) {
+                    std::memcpy(words + wordAt, v->host + size_t(k) * v->elemBytes, v->elemBytes);
+                    wordAt += rowWords;
+                    idx[rowAt++] = k;
+                }
+            std::memset(v->track + rb, 0, re - rb);
+        }
+        st.packed_rows = uint32_t(it.rows);
+        st.packed_bytes = it.rows * (v->elemBytes + 4);
+        if (stats) stats[it.i] = st;
+        v->anyDirty = false;
+        pyramid_note_buffer_write(ctx, v->priv);
+    }
+    RVE_CUDA(cudaMemcpyAsync(ctx->sync_stage_dev, ctx->sync_stage_host, need, cudaMemcpyHostToDevice, ctx->stream));
+    RVE_CUDA(cudaEventRecord(ctx->sync_stage_free, ctx->stream));
+    ctx->sync_stage_busy = true;
+    const auto* dwords = static_cast<const uint32_t*>(ctx->sync_stage_dev);
+    const auto* didx = reinterpret_cast<const uint32_t*>(static_cast<const unsigned char*>(ctx->sync_stage_dev) + idxOffset);
+    for (SyncBatch& b : launches) {
+        const uint32_t first = b.s[0].wordStart, last = b.s[b.n - 1].wordStart + b.s[b.n - 1].words;
+        // the kernel indexes the staged words of ITS segments from zero
+        for (uint32_t k = 0; k < b.n; ++k) b.s[k].wordStart -= first;
+        b.totalWords = last - first;
+        b.data = dwords + first;
+        b.idx = didx;
+        const uint32_t blocks = std::max<uint32_t>(1u, std::min<uint32_t>((b.totalWords + 255) / 256, uint32_t(ctx->sm_count) * 8u));
+        scatter_rows_batch_kernel<<<blocks, 256, 0, ctx->stream>>>(b);
+        ctx->launches++;
+        RVE_CUDA(cudaGetLastError());
+    }
     return 0;
 }
 

@@ -150,3 +150,16 @@ class SparseSet:
         if self.h:
             self.ctx.lib.rvs_sparse_set_destroy(self.h)
             self.h = None
+
+
+def encode_sync_batch(vectors, direct_min_rows: int = 256):
+    """rvs_vectors_encode_sync_batch: EncodeSync (packed) of several BufferedVRAMVector / SparseSet objects of one context - one
+    staging copy and one scatter launch for all of those whose changes are small. Returns one SyncStats per vector."""
+    if not vectors:
+        return []
+    lib = vectors[0].ctx.lib
+    hs = [lib.rvs_sparse_set_vector(v.h) if isinstance(v, SparseSet) else v.h for v in vectors]
+    arr = (C.c_void_p * len(hs))(*hs)
+    stats = (_abi.SyncStats * len(hs))()
+    _check(lib, lib.rvs_vectors_encode_sync_batch(arr, len(hs), direct_min_rows, stats))
+    return list(stats)

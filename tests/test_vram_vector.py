@@ -242,3 +242,70 @@ def test_forwarded_rows_land_in_the_owner_s_private_buffer(ctx, affine):
     helper.host_release(host_ptr, nbytes)
     helper.close()
     v.destroy()
+
+
+@pytest.mark.gpu
+def test_batched_sync_of_many_vectors_matches_their_host_buffers(ctx):
+    """rvs_vectors_encode_sync_batch: seven structures of different row sizes change a little per frame; those with small
+    changes share ONE staging copy and ONE scatter launch, the others (2-byte rows, affine rows, a long dirty run, a vector that
+    has never been synced) take their own EncodeSync - every private buffer must equal its host buffer after every frame, clean
+    vectors cost nothing, and the launch count shows the sharing."""
+    from ravengine_b200.vram_vector import BufferedVRAMVector, SparseSet, encode_sync_batch
+
+    rng = np.random.default_rng(31)
+    n = 20_000
+    specs = [(4, np.uint32, False), (16, np.float32, False), (64, np.float32, False), (12, np.float32, False), (2, np.uint16, False),
+             (48, np.float32, True)]
+    vecs, hosts = [], []
+    for eb, dt, affine in specs:
+        v = BufferedVRAMVector(ctx, eb, n, affine_rows=affine)
+        h = v.host(dt).reshape(n, eb // np.dtype(dt).itemsize)
+        h[:] = rng.integers(0, 1000, size=h.shape).astype(dt)
+        if affine:
+            h[:] = rng.random(h.shape, dtype=np.float32)
+        vecs.append(v)
+        hosts.append(h)
+    s = SparseSet(ctx)
+    s.emplace_many(np.arange(5000, dtype=np.uint32))
+    everything = vecs + [s]
+
+    def check():
+        for v, h, (eb, dt, affine) in zip(vecs, hosts, specs):
+            got = v.private_buffer.download(dt)
+            if affine:  # 48-B host rows land as 64-B mat4 rows: (0, 0, 0, 1) appended per column group - compare through the expansion rule
+                g = got.reshape(-1, 16)[:n]
+                exp = np.zeros((n, 16), np.float32)
+                exp.reshape(n, 4, 4)[:, :, :3] = h.reshape(n, 4, 3)
+                exp[:, 15] = 1.0
+                assert np.array_equal(g, exp)
+            else:
+                assert np.array_equal(got.reshape(-1, h.shape[1])[:n], h)
+        assert np.array_equal(s.private_buffer.download(np.uint32)[: len(s.dense())], s.dense())
+
+    encode_sync_batch(everything)  # first sync: everything is marked, nothing qualifies as small
+    ctx.synchronize()
+    check()
+    l0 = ctx.launch_count
+    sts = encode_sync_batch(everything)  # nothing changed
+    assert ctx.launch_count == l0 and all(st.ranges == 0 for st in sts)
+    for frame in range(4):
+        for v, h, (eb, dt, affine) in zip(vecs, hosts, specs):
+            idx = rng.choice(n, size=int(rng.integers(1, 200)), replace=False)
+            if frame == 2 and eb == 16:
+                idx = np.arange(3000, 3600)  # one long run: this vector leaves the batch for a direct copy
+            h[idx] = (rng.random((len(idx), h.shape[1])) * 100).astype(dt)
+            v.tracking()[idx] = 1
+        gone = rng.choice(s.dense(), size=40, replace=False)
+        s.erase_many(gone)
+        s.emplace_many((10_000 + frame * 100 + np.arange(40)).astype(np.uint32))
+        l0 = ctx.launch_count
+        sts = encode_sync_batch(everything)
+        ctx.synchronize()
+        shared = 5 if not (frame == 2) else 4  # 4-, 16-, 64-, 12-byte vectors + the set's list
+        assert sum(1 for st in sts if st.packed_rows) >= shared
+        # one launch for the shared block, one scatter each for the 2-byte and the affine vector (+ the long run's vector in frame 2: a copy, no launch)
+        assert ctx.launch_count - l0 == 3, (frame, ctx.launch_count - l0)
+        check()
+    for v in vecs:
+        v.destroy()
+    s.destroy()
