@@ -353,7 +353,24 @@ struct rvs_vector {
     cudaEvent_t stageFree = nullptr;  // upload of the previous staging block has completed
     bool stageBusy = false;
     std::vector<uint32_t> ranges;  // (begin, end) pairs of the last sync
+    // Indices flagged since the last sync, while every flag was set through SetValueAt / mark / Resize (touchedExact): the next
+    // sync derives the reference's ranges from them instead of scanning all flags - a 2.5 M-entity list with a few hundred
+    // changes costs microseconds of host time instead of ~0.4 ms. A caller holding the raw tracking pointer, or too many
+    // touches, turn it off until the next sync (which then scans).
+    std::vector<uint32_t> touched;
+    bool touchedExact = true;
+    bool rangesReady = false;  // `ranges` already holds this sync's ranges (computed by rvs_vectors_encode_sync_batch before it handed the vector on)
 };
+constexpr size_t kTouchedMax = size_t(1) << 16;
+static inline void note_touched(rvs_vector* v, uint32_t begin, uint32_t end) {
+    if (!v->touchedExact) return;
+    if (v->touched.size() + (end - begin) > kTouchedMax) {
+        v->touchedExact = false;
+        v->touched.clear();
+        return;
+    }
+    for (uint32_t i = begin; i < end; ++i) v->touched.push_back(i);
+}
 
 namespace {
 
@@ -422,6 +439,26 @@ int vec_reserve(rvs_vector* v, uint32_t newCap) {
 // The reference's range computation (src/BufferedVRAMVector.cpp:108-139); clean spans are skipped eight flags at a
 // time while no range is open (same result: they neither open nor close a range). The flags are cleared by the
 // caller, range by range (the reference clears them inside this loop; every set flag lies inside some range).
+// The same ranges from the list of flagged indices (ascending, unique, all < n, all with their flag still set): a range runs
+// from a flagged index to kMaxGapSize past the last flagged index that lies within kMaxGapSize of its predecessor, clipped at n -
+// exactly what the loop below produces (tests/test_vram_vector.py compares both with the restated reference loop).
+void ranges_from_indices(const std::vector<uint32_t>& idx, uint32_t n, std::vector<uint32_t>& out) {
+    out.clear();
+    size_t i = 0;
+    while (i < idx.size()) {
+        const uint32_t begin = idx[i];
+        uint32_t last = begin;
+        ++i;
+        while (i < idx.size() && idx[i] <= last + uint32_t(kMaxGapSize)) last = idx[i++];
+        const uint64_t end = uint64_t(last) + uint32_t(kMaxGapSize);
+        out.push_back(begin);
+        out.push_back(end < n ? uint32_t(end) : n);
+    }
+}
+
+// ranges of the vector's flags for a sync: from the touched list when it is exact, by the scan otherwise; restarts the list
+void vector_ranges(rvs_vector* v);
+
 void compute_ranges(const uint8_t* track, uint32_t n, std::vector<uint32_t>& out) {
     out.clear();
     int gap = 0;
@@ -453,6 +490,21 @@ void compute_ranges(const uint8_t* track, uint32_t n, std::vector<uint32_t>& out
         out.push_back(begin);
         out.push_back(n);
     }
+}
+
+void vector_ranges(rvs_vector* v) {
+    if (v->touchedExact) {
+        std::vector<uint32_t>& t = v->touched;
+        std::sort(t.begin(), t.end());
+        t.erase(std::unique(t.begin(), t.end()), t.end());
+        // a Resize below a flagged index cleared its flag; indices past the count are gone with it
+        t.erase(std::remove_if(t.begin(), t.end(), [v](uint32_t i) { return i >= v->count || !v->track[i]; }), t.end());
+        ranges_from_indices(t, v->count, v->ranges);
+    } else {
+        compute_ranges(v->track, v->count, v->ranges);
+    }
+    v->touched.clear();
+    v->touchedExact = true;
 }
 
 }  // namespace
@@ -535,6 +587,7 @@ int rvs_vector_resize(rvs_vector* v, uint32_t count) {
         std::memset(v->host + size_t(old) * v->elemBytes, 0, size_t(count - old) * v->elemBytes);
         std::memset(v->track + old, 1, count - old);
         v->anyDirty = true;
+        note_touched(v, old, count);
     } else {
         std::memset(v->track + count, 0, old - count);
     }
@@ -546,7 +599,9 @@ uint32_t rvs_vector_size(rvs_vector* v) { return v ? v->count : 0; }
 void* rvs_vector_host(rvs_vector* v) { return v ? v->host : nullptr; }
 uint8_t* rvs_vector_tracking(rvs_vector* v) {
     if (!v) return nullptr;
-    v->anyDirty = true;  // the caller may set flags through this pointer: the next sync looks at them
+    v->anyDirty = true;  // the caller may set flags through this pointer: the next sync looks at them ...
+    v->touchedExact = false;  // ... all of them: what it flags is not recorded
+    v->touched.clear();
     return v->track;
 }
 rve_buffer rvs_vector_private_buffer(rvs_vector* v) { return v ? v->priv : RVE_BUFFER_INVALID; }
@@ -556,6 +611,7 @@ int rvs_vector_set(rvs_vector* v, uint32_t index, const void* value) {
     if (!v || !value) return set_error(RVE_ERR_INVALID_ARGUMENT, "null argument");
     RVE_REQUIRE(index < v->count, "index out of range");
     std::memcpy(v->host + size_t(index) * v->elemBytes, value, v->elemBytes);
+    if (!v->track[index]) note_touched(v, index, index + 1);
     v->track[index] = 1;
     v->anyDirty = true;
     return 0;
@@ -566,7 +622,10 @@ int rvs_vector_mark(rvs_vector* v, uint32_t begin, uint32_t end) {
     if (!v) return set_error(RVE_ERR_INVALID_ARGUMENT, "null vector");
     RVE_REQUIRE(begin <= end && end <= v->count, "range out of bounds");
     std::memset(v->track + begin, 1, end - begin);
-    if (end > begin) v->anyDirty = true;
+    if (end > begin) {
+        v->anyDirty = true;
+        note_touched(v, begin, end);
+    }
     return 0;
 }
 
@@ -664,7 +723,11 @@ static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st, uint32_t 
     st->ranges = 1;
     v->ranges.assign({rowBegin, rowEnd});
     if (v->anyDirty) std::memset(v->track + rowBegin, 0, sub.count);
-    if (whole) v->anyDirty = false;
+    if (whole) {
+        v->anyDirty = false;
+        v->touched.clear();  // every flag was cleared
+        v->touchedExact = true;
+    }
     pyramid_note_buffer_write(ctx, v->priv);
     return 0;
 }
@@ -678,6 +741,8 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
     DeviceGuard g(ctx->device);
     rvs_sync_stats st{};
     const size_t eb = v->elemBytes, deb = v->devElemBytes;
+    const bool rangesReady = v->rangesReady && mode == RVS_SYNC_PACKED;
+    v->rangesReady = false;
 
     // private buffer follows the host buffer's size; old contents are carried over (:31-81)
     const size_t wantBytes = size_t(v->capacity) * deb;
@@ -737,13 +802,15 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
         v->pullBusy[v->cur] = false;
         v->track = v->trackBuf[v->cur];
         v->anyDirty = false;
+        v->touched.clear();  // the fresh flag block is clean
+        v->touchedExact = true;
         st.packed_bytes = uint64_t(v->count);  // flag bytes the kernel reads; row bytes depend on the flags (rvs_vector_pulled_rows)
         pyramid_note_buffer_write(ctx, v->priv);
         if (stats) *stats = st;
         return 0;
     }
 
-    compute_ranges(v->track, v->count, v->ranges);
+    if (!rangesReady) vector_ranges(v);
     v->anyDirty = false;
     const uint32_t nRanges = uint32_t(v->ranges.size() / 2);
     st.ranges = nRanges;
@@ -882,7 +949,8 @@ int rvs_vectors_encode_sync_batch(rvs_vector* const* vs, uint32_t n, uint32_t di
                      v->privBytes == size_t(v->capacity) * v->devElemBytes;
         uint64_t rows = 0;
         if (small && v->anyDirty) {
-            compute_ranges(v->track, v->count, v->ranges);
+            vector_ranges(v);  // consumes the touched list: should this vector fall back to its own sync below, that sync takes these ranges
+            v->rangesReady = true;
             for (size_t r = 0; r + 1 < v->ranges.size() && small; r += 2) {
                 if (v->ranges[r + 1] - v->ranges[r] >= direct_min_rows) small = false;
                 for (uint32_t k = v->ranges[r]; k < v->ranges[r + 1]; ++k) rows += v->track[k] ? 1u : 0u;
@@ -895,6 +963,7 @@ int rvs_vectors_encode_sync_batch(rvs_vector* const* vs, uint32_t n, uint32_t di
             continue;
         }
         if (!v->anyDirty || v->ranges.empty()) {  // clean: free, like the single-vector call
+            v->rangesReady = false;
             v->anyDirty = false;
             v->ranges.clear();
             continue;
@@ -953,6 +1022,7 @@ int rvs_vectors_encode_sync_batch(rvs_vector* const* vs, uint32_t n, uint32_t di
         st.packed_bytes = it.rows * (v->elemBytes + 4);
         if (stats) stats[it.i] = st;
         v->anyDirty = false;
+        v->rangesReady = false;
         pyramid_note_buffer_write(ctx, v->priv);
     }
     RVE_CUDA(cudaMemcpyAsync(ctx->sync_stage_dev, ctx->sync_stage_host, need, cudaMemcpyHostToDevice, ctx->stream));

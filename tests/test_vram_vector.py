@@ -309,3 +309,53 @@ def test_batched_sync_of_many_vectors_matches_their_host_buffers(ctx):
     for v in vecs:
         v.destroy()
     s.destroy()
+
+
+@pytest.mark.gpu
+def test_ranges_from_the_touched_list_equal_the_reference_scan(ctx):
+    """When every flag of a frame was set through SetValueAt / mark / Resize the sync derives its ranges from the list of touched
+    indices instead of scanning the flags: the ranges must be the reference loop's (src/BufferedVRAMVector.cpp:106-139) for
+    isolated touches, touches at every distance around maxGapSize, marks, growth, a shrink below touched rows, duplicates and
+    the end of the array; a frame that took the raw tracking pointer falls back to the scan, and the frame after it is exact again."""
+    from ravengine_b200.vram_vector import SYNC_PACKED, SYNC_RANGES, BufferedVRAMVector
+
+    rng = np.random.default_rng(77)
+    n = 30_000
+    v = BufferedVRAMVector(ctx, 16, n)
+    h = v.host(np.uint32).reshape(n, 4)
+    h[:] = rng.integers(0, 1 << 30, size=(n, 4), dtype=np.uint32)
+    v.encode_sync(SYNC_RANGES, 64)
+    for frame in range(12):
+        size = len(v)
+        flags = np.zeros(size, np.uint8)
+        if frame == 5:  # the raw pointer: not recorded, the sync scans
+            idx = rng.choice(size, size=300, replace=False)
+            v.tracking()[idx] = 1
+            flags[idx] = 1
+            h = v.host(np.uint32).reshape(size, 4)
+            h[idx] = rng.integers(0, 1 << 30, size=(len(idx), 4), dtype=np.uint32)
+        else:
+            base = rng.choice(size - 40, size=150, replace=False)
+            idx = np.unique(np.concatenate([base, base[:60] + rng.integers(1, 9, size=60), [0, size - 1, size - 3]]))  # gaps of 1..8 around maxGapSize 5
+            for i in idx.tolist() + idx[:10].tolist():  # duplicates too
+                v.set_value_at(int(i), rng.integers(0, 1 << 30, size=4, dtype=np.uint32))
+            flags[idx] = 1
+            if frame % 3 == 1:
+                b = int(rng.integers(0, size - 500))
+                v.mark(b, b + 37)
+                h = v.host(np.uint32).reshape(size, 4)
+                h[b:b + 37] = rng.integers(0, 1 << 30, size=(37, 4), dtype=np.uint32)
+                flags[b:b + 37] = 1
+            if frame % 4 == 2:  # shrink below touched rows, then grow past the old size: new rows start out modified
+                v.resize(size - 200)
+                v.resize(size + 100)
+                flags = np.concatenate([flags[: size - 200], np.ones(300, np.uint8)])
+        expect = host_tables.sync_ranges(flags.copy())
+        st = v.encode_sync(SYNC_PACKED if frame % 2 else SYNC_RANGES, 64)
+        assert np.array_equal(v.last_ranges(), expect), frame
+        assert st.ranges == len(expect)
+        m = len(v)
+        assert np.array_equal(v.private_buffer.download(np.uint32).reshape(-1, 4)[:m], v.host(np.uint32).reshape(m, 4)), frame
+        assert not v.tracking().any()
+        v.encode_sync(SYNC_RANGES, 64)  # (the tracking() call above switched recording off for this empty frame: scan, nothing to do)
+    v.destroy()

@@ -238,7 +238,7 @@ def live_churn_case(ctx, n, per_frame, frames, sort_lists):
     for _ in range(2):
         w.cull_static(cam.view_proj_cm, cam.pos, pyr)
     ctx.synchronize()
-    ts = []
+    ts, host = [], []
     for f in range(frames):
         for i, ss in enumerate(sets):
             members = ss.dense()
@@ -252,7 +252,9 @@ def live_churn_case(ctx, n, per_frame, frames, sort_lists):
         with torch.cuda.stream(st):
             torch.cuda._sleep(12_000_000)  # ~6 ms: the stream is busy while the host scans the sets' flags and enqueues the frame,
         a.record(st)                       # so the events bracket the GPU's execution of that work, not the host's preparation
+        t0 = time.perf_counter()
         w.cull_static(cam.view_proj_cm, cam.pos, pyr)
+        host.append((time.perf_counter() - t0) * 1e3)
         b.record(st)
         b.synchronize()
         ts.append(a.elapsed_time(b))
@@ -261,7 +263,7 @@ def live_churn_case(ctx, n, per_frame, frames, sort_lists):
     w.destroy()
     for ss in sets:
         ss.destroy()
-    return float(np.median(ts)), float(min(ts)), stats, vis
+    return float(np.median(ts)), float(min(ts)), stats, vis, float(np.median(host))
 
 
 def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
@@ -328,11 +330,12 @@ def run_stages(ctx, stream, reps=20, c3_objects=10_000, only=None, cpu=True):
     if want("c2live"):
         n_live, per_frame = 10_000_000, 500
         for sort_lists in (False, True):
-            med, best, stats, vis = live_churn_case(ctx, n_live, per_frame, max(reps, 8), sort_lists)
+            med, best, stats, vis, host_ms = live_churn_case(ctx, n_live, per_frame, max(reps, 8), sort_lists)
             yield line("frame_with_live_lists", f"C2 with sparse-set-backed lists that change every frame ({per_frame} erases + {per_frame} inserts per list and "
                        f"frame, after 10 % churn): set sync + " + ("sorted copies kept by deltas + cull of the copies" if sort_lists else "cull of the lists as they are")
                        + " - GPU time of the frame's enqueued work", med, best, n_live * 74 + vis * 4, "hbm",
                        {"instances": n_live, "visible": vis, "sorted_copy_full_rebuilds": stats[0], "sorted_copy_delta_updates": stats[1],
+                        "host_ms_per_frame_encode": host_ms,  # wall time of the rvs_cull_static call (set sync preparation, tables, enqueues)
                         "l2": "inputs exceed L2"})
 
     if want("pyramid"):
