@@ -1,3 +1,6 @@
+#!/usr/bin/env python
+"""Host-time split of a frame whose sparse-set-backed entity lists change (500 erases + 500 inserts per list): the set
+operations, the batched EncodeSync of the four sets, the rvs_cull_static encode.  python tools/live_probe.py [sorted]"""
 import sys, time
 sys.path.insert(0, ".")
 import numpy as np, torch
