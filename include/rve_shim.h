@@ -218,7 +218,7 @@ RVE_API int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct
 /* RVS_SYNC_FULL / RVS_SYNC_FULL_PULL restricted to rows [row_begin, row_end): the owner's share of a forwarded upload */
 /* EncodeSync of n vectors in one go (mode RVS_SYNC_PACKED): vectors with small changes share ONE staging copy and ONE scatter
  * launch per 16 vectors - a frame in which many BufferedVRAM structures change a little (entity lists, layers, attributes; the
- * reference syncs each one by itself, src/BufferedVRAMVector.cpp:89-160) pays one copy and one launch instead of one pair per
+ * reference syncs each one by itself, src/RenderEngine_Draw.cpp:112-146) pays one copy and one launch instead of one pair per
  * structure; the others take their own rvs_vector_encode_sync. stats: n entries or null. */
 RVE_API int rvs_vectors_encode_sync_batch(rvs_vector* const* vectors, uint32_t n, uint32_t direct_min_rows, rvs_sync_stats* stats);
 RVE_API int rvs_vector_encode_sync_rows(rvs_vector* v, uint32_t mode, uint32_t row_begin, uint32_t row_end, rvs_sync_stats* stats);
