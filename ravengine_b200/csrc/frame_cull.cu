@@ -54,7 +54,9 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
             if (src) return src;
             for (size_t i = 0; i < vecs.size(); ++i) {
                 auto& c = *owners[i];
-                if (sts[i].ranges) c.sortedValid = false;  // the list changed
+                // the list changed: by the set's version, not by this sync's statistics - the application may have synced the set itself
+                // (rvs_vectors_encode_sync_batch over all of a world's structures) before this call
+                if (sts[i].ranges || sparse_set_version(c.set) != c.sortedVersion) c.sortedValid = false;
                 c.entityIds = rvs_vector_private_buffer(vecs[i]);
                 c.count = rvs_sparse_set_dense_size(c.set);
             }
@@ -121,7 +123,7 @@ static int cull_static_impl(rvs_world* w, uint32_t nviews, const rvs_view* views
             c->sortedOf = c->entityIds;
             c->sortedCount = c->count;
             c->sortedValid = true;
-            if (c->set) c->bitmapValid = true, c->bitmapIdLimit = idLimit32;
+            if (c->set) c->bitmapValid = true, c->bitmapIdLimit = idLimit32, c->sortedVersion = sparse_set_version(c->set);
         }
     }
     // :1231-1244 — numCubos counts LODs (not commands); totalEntities sizes the dispatch

@@ -9,6 +9,7 @@
 namespace rve {
 // change log of a sparse set (csrc/sync.cu): off until switched on; take_changes returns the net ids that entered / left the
 // set since the last call and restarts the log - false when the log was off or overflowed (the consumer rebuilds from the list)
+uint64_t sparse_set_version(rvs_sparse_set* s);  // changes with every Emplace / Erase that altered the set
 // (`owner`: the one consumer the log is kept for - a second one is refused and keeps rebuilding)
 bool sparse_set_track_changes(rvs_sparse_set* s, uint64_t owner);
 bool sparse_set_take_changes(rvs_sparse_set* s, uint64_t owner, std::vector<uint32_t>* entered, std::vector<uint32_t>* left);
@@ -47,6 +48,7 @@ struct Command {
     uint32_t bitmapIdLimit = 0;
     bool bitmapValid = false;
     uint64_t sortOwnerId = 0;  // this command's identity towards the set's change log
+    uint64_t sortedVersion = ~0ull;  // version of the set the copy was made from
 };
 
 // MDICommandBase + MDIICommand (World.hpp:334-349)

@@ -1059,6 +1059,7 @@ struct rvs_sparse_set {
     std::vector<uint32_t> reverse;              // reverse_map: dense index -> sparse index
     // change log for a consumer that maintains something per VALUE (the shim's sorted device copy of the list): (value << 1) |
     // entered, in call order. Off until sparse_set_track_changes; gives up (overflow) past kChangeLogMax entries.
+    uint64_t version = 0;  // bumped by every Emplace / Erase that changes the set: consumers compare it instead of relying on a sync's statistics
     bool track = false, overflow = false;
     uint64_t logOwner = 0;  // the one consumer the log is kept for (taking it empties it: a second reader would miss changes)
     std::vector<uint64_t> log;
@@ -1066,6 +1067,8 @@ struct rvs_sparse_set {
 constexpr size_t kChangeLogMax = size_t(1) << 22;
 
 namespace rve {
+uint64_t sparse_set_version(rvs_sparse_set* s) { return s->version; }
+
 bool sparse_set_track_changes(rvs_sparse_set* s, uint64_t owner) {
     if (s->track && s->logOwner != owner) return false;  // somebody else's log: this consumer keeps rebuilding from the list
     s->track = true;
@@ -1098,6 +1101,7 @@ bool sparse_set_take_changes(rvs_sparse_set* s, uint64_t owner, std::vector<uint
 }  // namespace rve
 
 static void log_change(rvs_sparse_set* s, uint32_t value, bool entered) {
+    ++s->version;
     if (!s->track || s->overflow) return;
     if (s->log.size() >= kChangeLogMax) {
         s->overflow = true;

@@ -278,6 +278,8 @@ def test_sorted_copy_of_a_set_backed_list_follows_per_frame_churn_by_deltas(ctx)
         s.erase_many(gone)
         outside = np.setdiff1d(np.arange(n, dtype=np.uint32), s.dense())
         s.emplace_many(np.concatenate([rng.choice(outside, size=250, replace=False), gone[:50]]).astype(np.uint32))  # same size; 50 ids left and came back
+        if frame % 2:
+            s.encode_sync()  # the application syncs the set itself: the shim's own sync then finds nothing to do and must still see the change
         check()
         assert w.sorted_list_stats() == (1, frame + 1)
     s.emplace_many(rng.choice(np.setdiff1d(np.arange(n, dtype=np.uint32), s.dense()), size=500, replace=False).astype(np.uint32))  # the list grows
