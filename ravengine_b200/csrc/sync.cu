@@ -926,7 +926,7 @@ int rvs_vector_encode_sync(rvs_vector* v, uint32_t mode, uint32_t direct_min_row
 
 // EncodeSync of SEVERAL vectors at once. Frames in which many structures change a little (entity lists, layers, attributes: a
 // few hundred rows each) pay per vector one staging copy and one scatter launch - ~10 us of latency each. Here the modified
-// rows of all vectors whose changes are small (only short ranges, <= 64 Ki rows, 4-byte-multiple rows, no reallocation due)
+// rows of all vectors whose changes are small (<= 64 Ki modified rows, 4-byte-multiple rows, no reallocation due)
 // travel in ONE pinned staging block and ONE copy, and are scattered by ONE launch per 16 vectors; every other vector takes
 // its own rvs_vector_encode_sync(RVS_SYNC_PACKED). stats: one entry per vector (may be null).
 int rvs_vectors_encode_sync_batch(rvs_vector* const* vs, uint32_t n, uint32_t direct_min_rows, rvs_sync_stats* stats) {
@@ -951,10 +951,10 @@ int rvs_vectors_encode_sync_batch(rvs_vector* const* vs, uint32_t n, uint32_t di
         if (small && v->anyDirty) {
             vector_ranges(v);  // consumes the touched list: should this vector fall back to its own sync below, that sync takes these ranges
             v->rangesReady = true;
-            for (size_t r = 0; r + 1 < v->ranges.size() && small; r += 2) {
-                if (v->ranges[r + 1] - v->ranges[r] >= direct_min_rows) small = false;
+            // small = few modified rows in total, whatever the shape of their ranges (a run of appended rows is packed like the rest:
+            // direct_min_rows only steers the single-vector path of the vectors that are handed on)
+            for (size_t r = 0; r + 1 < v->ranges.size() && rows <= 65536; r += 2)
                 for (uint32_t k = v->ranges[r]; k < v->ranges[r + 1]; ++k) rows += v->track[k] ? 1u : 0u;
-            }
             if (rows > 65536) small = false;
         }
         if (!small) {
