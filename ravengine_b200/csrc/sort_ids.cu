@@ -173,27 +173,42 @@ __device__ __forceinline__ void st_release_u64(unsigned long long* p, unsigned l
     asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// One CTA covers kLbSub sub-blocks of 1024 bitmap words: shorter look-back chains against fewer, heavier CTAs. Measured on the
+// four churned lists of C2 (ncu, one launch): 47.5 us at 1, 38.4 us at 2, 41.8 us at 4 - the dense id range of a list keeps
+// only a quarter of its CTAs busy (busiest SM active 86 k cycles, mean 36 k), so fewer CTAs soon cost more than the chain saves.
+constexpr uint32_t kLbSub = 2;
 __global__ void __launch_bounds__(kSortBlock) ids_expand_lookback_kernel(const SortBatch b, uint32_t words, uint32_t blocks) {
     __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_blk, s_prefix;
+    __shared__ uint32_t s_blk, s_prefix, s_tot[kLbSub];
     const SortList& L = b.l[blockIdx.y];
     uint32_t* region = L.region;
     unsigned long long* state = reinterpret_cast<unsigned long long*>(region + size_t(blocks) * kSortBlock);  // (status << 32) | value; status 1 aggregate, 2 prefix
     uint32_t* ctl = region + size_t(blocks) * kSortBlock + 2u * blocks;
     if (threadIdx.x == 0) s_blk = atomicAdd(ctl, 1u);
     __syncthreads();
-    const uint32_t blk = s_blk;
-    const uint32_t w = blk * kSortBlock + threadIdx.x;
-    uint32_t bits = 0;
-    if (w < words) {
-        bits = region[w];
-        if (bits && !L.keep) region[w] = 0u;  // scratch bitmaps are clean again when this launch ends
-    }
-    const uint32_t n = uint32_t(__popc(bits));
-    const uint32_t incl = block_scan_1024(n, s_warp);
+    const uint32_t blk = s_blk;  // CTA index in start order: its predecessors have started
     const uint32_t lane = threadIdx.x & 31u;
-    if ((threadIdx.x >> 5) == 31u) {  // the last warp: its lane 31 holds the block total
-        const uint32_t total = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t bits[kLbSub], n[kLbSub], incl[kLbSub];
+#pragma unroll
+    for (uint32_t k = 0; k < kLbSub; ++k) {
+        const uint32_t w = (blk * kLbSub + k) * kSortBlock + threadIdx.x;
+        bits[k] = 0;
+        if (w < words) {
+            bits[k] = region[w];
+            if (bits[k] && !L.keep) region[w] = 0u;  // scratch bitmaps are clean again when this launch ends
+        }
+        n[k] = uint32_t(__popc(bits[k]));
+    }
+#pragma unroll
+    for (uint32_t k = 0; k < kLbSub; ++k) {
+        incl[k] = block_scan_1024(n[k], s_warp);
+        if (threadIdx.x == kSortBlock - 1) s_tot[k] = incl[k];
+    }
+    __syncthreads();
+    if ((threadIdx.x >> 5) == 31u) {  // the last warp does the look-back
+        uint32_t total = 0;
+#pragma unroll
+        for (uint32_t k = 0; k < kLbSub; ++k) total += s_tot[k];
         uint32_t prefix = 0;
         if (blk == 0) {
             if (lane == 0) st_release_u64(state, (2ull << 32) | total);
@@ -220,20 +235,25 @@ __global__ void __launch_bounds__(kSortBlock) ids_expand_lookback_kernel(const S
         if (lane == 0) s_prefix = prefix;
     }
     __syncthreads();
-    // expansion, a warp at a time over its 32 words: the lane whose bit is set writes that id at its rank inside the word, so
-    // the ids of one word leave as ONE coalesced store (a thread expanding its own word wrote 32 scattered sectors per store)
-    const uint32_t pos = s_prefix + incl - n;
-    const uint32_t wordBase = w - lane;
+    // expansion, a warp at a time over its 32 words of every sub-block: the lane whose bit is set writes that id at its rank inside
+    // the word, so the ids of one word leave as ONE coalesced store (a thread expanding its own word wrote 32 scattered sectors per store)
     uint32_t* __restrict__ out = L.out;
-    const uint32_t nonEmpty = __ballot_sync(0xffffffffu, bits != 0u);
-    for (uint32_t todo = nonEmpty; todo; todo &= todo - 1u) {
-        const uint32_t wi = uint32_t(__ffs(int(todo))) - 1u;
-        const uint32_t bw = __shfl_sync(0xffffffffu, bits, wi);
-        const uint32_t pw = __shfl_sync(0xffffffffu, pos, wi);
-        if ((bw >> lane) & 1u) {
-            const uint32_t at = pw + uint32_t(__popc(bw & ((1u << lane) - 1u)));
-            if (at < L.count) out[at] = ((wordBase + wi) << 5) + lane;
+    uint32_t before = s_prefix;
+#pragma unroll
+    for (uint32_t k = 0; k < kLbSub; ++k) {
+        const uint32_t pos = before + incl[k] - n[k];
+        const uint32_t wordBase = (blk * kLbSub + k) * kSortBlock + threadIdx.x - lane;
+        const uint32_t nonEmpty = __ballot_sync(0xffffffffu, bits[k] != 0u);
+        for (uint32_t todo = nonEmpty; todo; todo &= todo - 1u) {
+            const uint32_t wi = uint32_t(__ffs(int(todo))) - 1u;
+            const uint32_t bw = __shfl_sync(0xffffffffu, bits[k], wi);
+            const uint32_t pw = __shfl_sync(0xffffffffu, pos, wi);
+            if ((bw >> lane) & 1u) {
+                const uint32_t at = pw + uint32_t(__popc(bw & ((1u << lane) - 1u)));
+                if (at < L.count) out[at] = ((wordBase + wi) << 5) + lane;
+            }
         }
+        before += s_tot[k];
     }
 }
 
@@ -256,7 +276,7 @@ static int sort_batch(rve_ctx* ctx, SortBatch& batch, uint32_t n, uint32_t maxCo
     for (uint32_t i = 0; i < n; ++i) batch.l[i].region = scratch + size_t(i) * sort_region_words(blocks);
     const uint32_t setBlocks = std::max<uint32_t>(1u, std::min<uint32_t>((maxCount + 255) / 256, uint32_t(ctx->sm_count) * 8u / n + 1u));
     ids_set_bits_batch_kernel<<<dim3(setBlocks, n), 256, 0, ctx->stream>>>(batch, id_limit, blocks);
-    ids_expand_lookback_kernel<<<dim3(blocks, n), kSortBlock, 0, ctx->stream>>>(batch, words, blocks);
+    ids_expand_lookback_kernel<<<dim3((blocks + kLbSub - 1) / kLbSub, n), kSortBlock, 0, ctx->stream>>>(batch, words, blocks);
     ctx->launches += 2;
     RVE_CUDA(cudaGetLastError());
     ctx->sort_dirty = false;
@@ -324,7 +344,7 @@ int sort_lists_persistent(rve_ctx* ctx, const SortedListUpdate* u, uint32_t n_li
         }
         const uint32_t setBlocks = std::max<uint32_t>(1u, std::min<uint32_t>((maxWork + 255) / 256, uint32_t(ctx->sm_count) * 8u / n + 1u));
         ids_set_bits_batch_kernel<<<dim3(setBlocks, n), 256, 0, ctx->stream>>>(batch, id_limit, blocks);
-        ids_expand_lookback_kernel<<<dim3(blocks, n), kSortBlock, 0, ctx->stream>>>(batch, words, blocks);
+        ids_expand_lookback_kernel<<<dim3((blocks + kLbSub - 1) / kLbSub, n), kSortBlock, 0, ctx->stream>>>(batch, words, blocks);
         ctx->launches += 2;
         RVE_CUDA(cudaGetLastError());
     }
