@@ -249,6 +249,11 @@ RVE_API rve_buffer rvs_vector_private_buffer(rvs_vector* v);
 RVE_API uint64_t rvs_vector_pulled_rows(rvs_vector* v);
 /* (begin, end) pairs of the last sync, for inspection; returns their number */
 RVE_API uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max_pairs);
+/* The range derivation by itself, host only (no device needed): from a flag array by the reference's scan
+ * (src/BufferedVRAMVector.cpp:106-139, maxGapSize 5), and from the ascending list of flagged indices - the shortcut a sync
+ * takes when every flag of the frame went through SetValueAt / mark / Resize. Both return the number of (begin, end) pairs. */
+RVE_API uint32_t rvs_sync_ranges_from_flags(const uint8_t* flags, uint32_t count, uint32_t* out_pairs, uint32_t max_pairs);
+RVE_API uint32_t rvs_sync_ranges_from_indices(const uint32_t* indices, uint32_t n, uint32_t count, uint32_t* out_pairs, uint32_t max_pairs);
 
 /* ---- entity lists: BufferedVRAMSparseSet<entity_id_t, entity_id_t> (include/RavEngine/World.hpp:342,355: MDIICommand::command::
  * entities; include/RavEngine/SparseSet.hpp:6-104; include/RavEngine/BufferedVRAMVector.hpp:129-170). The dense array is what the

@@ -230,6 +230,8 @@ PROTOTYPES.update({
     "rvs_forward_rows": (C.c_int, [VP, VP, u32, u32, u64, u64, u32]),
     "rvs_vector_pulled_rows": (u64, [VP]),
     "rvs_vector_last_ranges": (u32, [VP, UP, u32]),
+    "rvs_sync_ranges_from_flags": (u32, [C.POINTER(C.c_uint8), u32, UP, u32]),
+    "rvs_sync_ranges_from_indices": (u32, [UP, u32, u32, UP, u32]),
 })
 
 PROTOTYPES.update({

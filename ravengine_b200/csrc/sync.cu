@@ -649,6 +649,22 @@ uint32_t rvs_vector_last_ranges(rvs_vector* v, uint32_t* out_pairs, uint32_t max
     return n;
 }
 
+// The two range derivations as plain host functions (no device, no vector): what a sync computes from a flag array by the
+// reference's scan, and from the ascending list of flagged indices. Returns the number of (begin, end) pairs; writes at most
+// max_pairs of them. For tests that compare the two with the restated reference loop without a GPU.
+uint32_t rvs_sync_ranges_from_flags(const uint8_t* flags, uint32_t count, uint32_t* out_pairs, uint32_t max_pairs) {
+    std::vector<uint32_t> r;
+    if (flags) compute_ranges(flags, count, r);
+    for (size_t i = 0; i < r.size() && i < size_t(max_pairs) * 2; ++i) out_pairs[i] = r[i];
+    return uint32_t(r.size() / 2);
+}
+uint32_t rvs_sync_ranges_from_indices(const uint32_t* indices, uint32_t n, uint32_t count, uint32_t* out_pairs, uint32_t max_pairs) {
+    std::vector<uint32_t> idx(indices, indices + (indices ? n : 0)), r;
+    ranges_from_indices(idx, count, r);
+    for (size_t i = 0; i < r.size() && i < size_t(max_pairs) * 2; ++i) out_pairs[i] = r[i];
+    return uint32_t(r.size() / 2);
+}
+
 // RVS_SYNC_FULL / RVS_SYNC_FULL_PULL: every row goes up, flags are not consulted (and cleared when any may be set)
 static int sync_full(rvs_vector* v, uint32_t mode, rvs_sync_stats* st, uint32_t rowBegin = 0, uint32_t rowEnd = 0xFFFFFFFFu) {
     rve_ctx* ctx = v->ctx;

@@ -33,6 +33,41 @@ def test_range_scan_clears_flags():
     assert not t.any()
 
 
+def test_library_range_derivations_equal_the_restated_reference_loop():
+    """CPU only (the two functions are plain host code of librve_b200.so): the scan the library runs over a flag array and the
+    shortcut from the list of flagged indices against the restated reference loop (oracle/host_tables.py::sync_ranges), over
+    random densities, clustered touches at every distance around maxGapSize, flags at both ends, empty and full arrays."""
+    import ctypes as C
+
+    from ravengine_b200 import _abi
+
+    lib = _abi.load_library()
+    rng = np.random.default_rng(5)
+    cases = [np.zeros(0, np.uint8), np.zeros(17, np.uint8), np.ones(9, np.uint8), np.array([0, 0, 1], np.uint8), np.array([1] + [0] * 7, np.uint8)]
+    for n in (1, 7, 64, 1000, 20_001):
+        for density in (0.0005, 0.01, 0.2, 0.7):
+            f = (rng.random(n) < density).astype(np.uint8)
+            cases.append(f)
+        f = np.zeros(n, np.uint8)
+        base = rng.integers(0, max(n - 12, 1), size=max(n // 50, 1))
+        for gap in range(1, 9):
+            f[np.minimum(base + gap * (rng.random(len(base)) < 0.5), n - 1)] = 1
+        f[[0, n - 1]] = 1
+        cases.append(f)
+    for f in cases:
+        n = len(f)
+        expect = host_tables.sync_ranges(f.copy())
+        out = np.zeros((n // 2 + 2, 2), np.uint32)
+        fl = np.ascontiguousarray(f)
+        got = lib.rvs_sync_ranges_from_flags(fl.ctypes.data_as(C.POINTER(C.c_uint8)) if n else None, n, out.ctypes.data_as(C.POINTER(C.c_uint32)), len(out))
+        assert got == len(expect) and np.array_equal(out[:got], expect)
+        idx = np.flatnonzero(f).astype(np.uint32)
+        out2 = np.zeros_like(out)
+        got2 = lib.rvs_sync_ranges_from_indices(idx.ctypes.data_as(C.POINTER(C.c_uint32)) if len(idx) else None, len(idx), n,
+                                                out2.ctypes.data_as(C.POINTER(C.c_uint32)), len(out2))
+        assert got2 == len(expect) and np.array_equal(out2[:got2], expect), (n, idx[:10])
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("elem_bytes,dtype", [(64, np.float32), (4, np.uint32), (2, np.uint16), (12, np.float32)])
 @pytest.mark.parametrize("density", [0.0, 0.001, 0.05, 0.6, 1.0])
